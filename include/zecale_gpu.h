@@ -1,0 +1,136 @@
+/* zecale_gpu.h — C ABI of the B200 (sm_100a) prover hot path for clearmatics/zecale.
+ *
+ * Drop-in boundary for the Groth16 prove step over BW6-761
+ * (libsnark r1cs_gg_ppzksnark_prover, r1cs_gg_ppzksnark.tcc:464-603). The reference's
+ * call sites are served by this library through the template specialisations in
+ * zecale_b200/hooks/zecale_gpu_hooks.hpp:
+ *
+ *   libff::multi_exp<G1|G2, Fr, BDLO12_signed, special>            multiexp.tcc:648-688
+ *   libff::multi_exp_filter_one_zero<G1, Fr, ...>                  multiexp.tcc:695-757
+ *   libsnark::kc_multi_exp_with_mixed_addition<G2, G1, Fr, ...>    kc_multiexp.tcc:31-113
+ *        -> zecale_gpu_msm_g1 / zecale_gpu_msm_g2
+ *   libfqfft::basic_radix2_domain<Fr>::{FFT,iFFT,cosetFFT,icosetFFT}
+ *        (basic_radix2_domain.tcc:55-88)                           -> zecale_gpu_ntt
+ *
+ * Conventions follow libff's existing FFI (libff/ffi/ffi.h:55-95): plain pointers and
+ * sizes, no C++ types, no exceptions across the boundary. Return value 0 = success,
+ * non-zero = error code (ZECALE_GPU_E_*); zecale_gpu_last_error() gives the text.
+ *
+ * Data formats are libff's in-memory formats on a little-endian host, read as-is:
+ *   Fr  : 6  x u64 limbs, Montgomery form, R = 2^384          (48 bytes)
+ *   Fq  : 12 x u64 limbs, Montgomery form, R = 2^768          (96 bytes)
+ *   G1/G2 point : {X, Y, Z} of Fq, homogeneous projective     (288 bytes)
+ *   MSM bases must be in libff "special" form: Z == Fq::one() or the zero point
+ *   (0, one, 0) — which is what every proving-key query holds
+ *   (r1cs_gg_ppzksnark.tcc:352-387 batch_to_special).
+ *   Results are written in special form too, so they can be memcpy'd into a
+ *   libff::bw6_761_G1 / G2 object.
+ *
+ * There is no CPU fallback: every entry point fails with ZECALE_GPU_E_CUDA when no
+ * sm_100 device is usable.
+ */
+#ifndef ZECALE_GPU_H
+#define ZECALE_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct zecale_gpu_ctx zecale_gpu_ctx;
+typedef struct zecale_gpu_bases zecale_gpu_bases;
+
+enum {
+    ZECALE_GPU_OK = 0,
+    ZECALE_GPU_E_ARG = 1,      /* null pointer / bad size / bad flags                  */
+    ZECALE_GPU_E_CUDA = 2,     /* CUDA runtime error (text in last_error)              */
+    ZECALE_GPU_E_FORM = 3,     /* an MSM base is not in special form (Z != one, != 0)  */
+    ZECALE_GPU_E_DOMAIN = 4,   /* log_m outside [1, 46 = Fr two-adicity] or too large  */
+    ZECALE_GPU_E_NOMEM = 5     /* device allocation failed                             */
+};
+
+/* NTT flags (zecale_gpu_ntt). */
+enum {
+    ZECALE_GPU_NTT_INVERSE = 1u, /* omega^-1 and multiply by m^-1 (libfqfft iFFT)       */
+    ZECALE_GPU_NTT_COSET = 2u    /* cosetFFT: a[i] *= g^i before the forward transform;
+                                    icosetFFT: a[i] *= g^-i after the inverse transform */
+};
+
+/* Groups (zecale_gpu_pin_bases). */
+enum { ZECALE_GPU_G1 = 1, ZECALE_GPU_G2 = 2 };
+
+/* ---- lifetime ------------------------------------------------------------------ */
+
+/* Create a context bound to devices[0] (multi-device contexts shard MSMs over all
+ * listed devices). devices == NULL means {current device}. */
+int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **ctx);
+void zecale_gpu_shutdown(zecale_gpu_ctx *ctx);
+const char *zecale_gpu_last_error(zecale_gpu_ctx *ctx);
+
+/* ---- MSM: replaces libff::multi_exp & friends ------------------------------------
+ * out = sum_{i<n} scalar(i) * base(i), where
+ *   base(i)   = *(point*)((char*)bases + i*base_stride)         (288 B read at that address)
+ *   scalar(i) = *(Fr*)((char*)scalars + j*scalar_stride), j = scalar_index ? scalar_index[i] : i
+ * base_stride is 288 for a libff::G1_vector and 576 for the values of a
+ * knowledge_commitment_vector<G2,G1> (G2 at byte 0, G1 at byte 288: pass bases+288 for
+ * the G1 half). scalar_index is how the sparse B_query walk of kc_multiexp.tcc:63-89
+ * is expressed: scalar_index[i] = B_query.indices[i].
+ * Zero scalars, scalars equal to one and zero points need no pre-filtering.
+ * All pointers are HOST pointers; out_point receives 288 bytes. */
+int zecale_gpu_msm_g1(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, const void *scalars,
+                      size_t scalar_stride, const size_t *scalar_index, size_t n, void *out_point);
+int zecale_gpu_msm_g2(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, const void *scalars,
+                      size_t scalar_stride, const size_t *scalar_index, size_t n, void *out_point);
+
+/* ---- NTT: replaces libfqfft::basic_radix2_domain<bw6_761_Fr> ---------------------
+ * In place on a[0 .. 2^log_m), natural order in and out, Montgomery form in and out.
+ * flags = 0: FFT; INVERSE: iFFT; COSET: cosetFFT(g); INVERSE|COSET: icosetFFT(g).
+ * coset_g: 48-byte Fr (Montgomery), required when COSET is set. `a` is a HOST pointer. */
+int zecale_gpu_ntt(zecale_gpu_ctx *ctx, void *a, unsigned log_m, unsigned flags, const void *coset_g);
+
+/* ---- residency (optional): keep the constant proving-key queries on the device ----
+ * The handle owns a device-side affine image of the n bases; the host memory is not
+ * retained. group is ZECALE_GPU_G1 or ZECALE_GPU_G2 (same arithmetic, kept for checks). */
+int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
+                         zecale_gpu_bases **handle);
+int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *handle);
+/* MSM over the first n pinned bases. */
+int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *handle, const void *scalars,
+                          size_t scalar_stride, const size_t *scalar_index, size_t n, void *out_point);
+
+/* ---- device-resident variants (inputs already in HBM; used by bench.py `value`) ---
+ * d_scalars / d_a / d_scalar_index are DEVICE pointers on the context's device;
+ * d_scalar_index holds u64. out_point is a HOST pointer. `elapsed_ms`, if not NULL,
+ * receives the CUDA-event time of the launched kernels on the context's stream. */
+int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *handle, const void *d_scalars,
+                              size_t scalar_stride, const uint64_t *d_scalar_index, size_t n, void *out_point,
+                              float *elapsed_ms);
+int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned flags, const void *coset_g,
+                       float *elapsed_ms);
+
+/* ---- introspection ----------------------------------------------------------------*/
+/* Number of kernel launches issued by this context so far (bench.py gpu_launches). */
+uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx);
+/* Window size c the MSM uses for n points (for the roofline op count). */
+unsigned zecale_gpu_msm_window_bits(size_t n);
+
+/* ---- unit-test / microbenchmark hooks (not used by the prover) --------------------
+ * Element-wise field and group operations on host arrays, executed by the same
+ * device functions the MSM/NTT kernels use. op codes:
+ *   field: 0 add, 1 sub, 2 mul, 3 sqr, 4 inverse, 5 neg, 6 from-Montgomery
+ *   group: 0 add (xyzz_add), 1 mixed add, 2 double, 3 normalise (to special)
+ * Points are 288-byte libff projective points in and (special form) out. */
+int zecale_gpu_test_fq(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n);
+int zecale_gpu_test_fr(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n);
+int zecale_gpu_test_group(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n);
+/* Fq Montgomery-product throughput: `threads` threads each run a dependent chain of
+ * `iters` products; returns the CUDA-event time in ms in *elapsed_ms. */
+int zecale_gpu_bench_fq_mul(zecale_gpu_ctx *ctx, unsigned blocks, unsigned threads_per_block, unsigned iters,
+                            float *elapsed_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZECALE_GPU_H */

@@ -1,0 +1,123 @@
+"""zecale_gpu_msm_g1/g2 through the C ABI vs libff::multi_exp (BDLO12_signed, special bases).
+
+Mirrors libff's test_multiexp.cpp (sizes 1..257, :204-283; edge case :337-383) for BW6-761,
+which the reference itself never instantiates."""
+import numpy as np
+import pytest
+
+import bw6_constants as C
+from oracle.ref import ints_to_limbs
+
+pytestmark = pytest.mark.gpu
+
+
+def _inf(one_limbs):
+    z = np.zeros(36, dtype=np.uint64)
+    z[12:24] = one_limbs
+    return z
+
+
+@pytest.mark.parametrize("group", [1, 2])
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 256, 257, 4096])
+def test_msm_sizes(gpu, ref, group, n):
+    bases = ref.bases_seq(n, group)
+    scalars = ref.fr_rng(1000 * n, n)
+    exp, _ = ref.msm(bases, scalars, group)
+    f = gpu.msm_g1 if group == 1 else gpu.msm_g2
+    assert np.array_equal(f(bases, scalars), exp)
+
+
+def test_msm_empty(gpu, ref):
+    bases = ref.bases_seq(1, 1)
+    got = gpu.msm_g1(bases[:0], ref.fr_rng(0, 1)[:0], n=0)
+    assert np.array_equal(got, _inf(bases[0][24:36]))
+
+
+@pytest.mark.parametrize("group", [1, 2])
+def test_msm_edge_cases(gpu, ref, group):
+    n = 600
+    bases = ref.bases_mul(ref.fr_rng(77, n), group)
+    one = bases[0][24:36].copy()
+    r = C.R
+    vals = [0, 1, r - 1, r - 2, 2, (1 << 376), (1 << 377) - 1 - ((1 << 377) - 1 - (r - 1)), (r - 1) // 2, (r + 1) // 2]
+    # top window digit negative + carry pattern (test_multiexp.cpp:337-383): all windows = 2^(c-1) for several c
+    for c in (13, 14, 15, 16):
+        v = sum((1 << (c - 1)) << (c * k) for k in range(377 // c + 1)) % r
+        vals.append(v)
+        vals.append(sum(((1 << c) - 1) << (c * k) for k in range(377 // c + 1)) % r)
+    scal_int = [vals[i % len(vals)] if i < 200 else None for i in range(n)]
+    rnd = ref.fr_rng(4242, n)
+    scalars = rnd.copy()
+    fixed = ref.fr_from_ints([v for v in scal_int if v is not None])
+    scalars[: fixed.shape[0]] = fixed
+    # zero points, duplicates, P / -P pairs with equal scalars (bucket P + (-P) and P + P)
+    bases[5] = _inf(one)
+    bases[6] = _inf(one)
+    bases[300] = bases[301]
+    scalars[300] = scalars[301]
+    bases[302] = ref.group_op(4, bases[303:304], None, group)[0]
+    scalars[302] = scalars[303]
+    bases[310:330] = bases[310]
+    scalars[310:330] = scalars[310]
+    exp, _ = ref.msm(bases, scalars, group)
+    f = gpu.msm_g1 if group == 1 else gpu.msm_g2
+    assert np.array_equal(f(bases, scalars), exp)
+    # filter_one_zero front-end of the prover gives the same element (multiexp.tcc:695-757)
+    exp2, _ = ref.msm(bases, scalars, group, method=1)
+    assert np.array_equal(exp2, exp)
+
+
+def test_msm_heavy_buckets(gpu, ref):
+    """Aggregator-like scalars: many zeros / ones / small values -> very uneven buckets."""
+    n = 5000
+    bases = ref.bases_mul(ref.fr_rng(9, n), 1)
+    scalars = ref.fr_rng(31337, n)
+    small = ref.fr_from_ints([0, 1, 1, 1, 2, 3, 65535, 1, 0, 1])
+    for i in range(0, 3000):
+        scalars[i] = small[i % 10]
+    exp, _ = ref.msm(bases, scalars, 1, method=1)
+    assert np.array_equal(gpu.msm_g1(bases, scalars), exp)
+
+
+def test_msm_kc_sparse(gpu, ref):
+    """B-query shape: sparse (G2,G1) pairs, stride 576, scalars picked through indices
+    (kc_multi_exp_with_mixed_addition, kc_multiexp.tcc:31-113)."""
+    n_scalars, nnz = 3000, 1100
+    rng = np.random.default_rng(3)
+    idx = np.sort(rng.choice(n_scalars, nnz, replace=False)).astype(np.uint64)
+    s = ref.fr_rng(555, nnz)
+    vals = np.zeros((nnz, 72), dtype=np.uint64)
+    vals[:, :36] = ref.bases_mul(s, 2)
+    vals[:, 36:] = ref.bases_mul(ref.fr_rng(556, nnz), 1)
+    scalars = ref.fr_rng(8080, n_scalars)
+    scalars[idx[3]] = 0
+    scalars[idx[4]] = ref.fr_from_ints([1])[0]
+    exp, _ = ref.msm_kc(vals, idx, n_scalars, scalars)
+    got_g2 = gpu.msm_g2(vals, scalars, index=idx)
+    got_g1 = gpu.msm_g1(vals, scalars, index=idx, base_offset_bytes=288)
+    assert np.array_equal(got_g2, exp[:36])
+    assert np.array_equal(got_g1, exp[36:])
+
+
+def test_msm_pinned_and_2_16(gpu, ref):
+    n = 1 << 16
+    bases = ref.bases_seq(n, 1)
+    scalars = ref.fr_rng(1 << 32, n)
+    exp, t = ref.msm(bases, scalars, 1)
+    pinned = gpu.pin_bases(bases)
+    try:
+        assert np.array_equal(gpu.msm_pinned(pinned, scalars), exp)
+        # prefix of the pinned set
+        exp2, _ = ref.msm(bases[:1000], scalars[:1000], 1)
+        assert np.array_equal(gpu.msm_pinned(pinned, scalars, n=1000), exp2)
+    finally:
+        pinned.release()
+
+
+def test_msm_rejects_non_special(gpu, ref):
+    import zecale_b200 as z
+    bases = ref.bases_seq(8, 1)
+    bad = ref.group_op(2, bases, None, 1)  # doubled: Z != one
+    with pytest.raises(z.ZecaleGpuError) as e:
+        gpu.msm_g1(bad, ref.fr_rng(1, 8))
+    assert e.value.code == 3

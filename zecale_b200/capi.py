@@ -1,0 +1,201 @@
+"""ctypes binding of the C ABI in include/zecale_gpu.h.
+
+The product path is the CUDA library only: if libzecale_gpu.so is missing this
+module raises at import, and every call raises ZecaleGpuError on a non-zero
+status. There is no CPU fallback anywhere in this package.
+
+Array conventions (numpy, little-endian host = libff's in-memory layout):
+  Fr vector   : uint64 array of shape (n, 6)     Montgomery form
+  points      : uint64 array of shape (n, 36)    {X, Y, Z}, 12 limbs each, special form
+  kc pairs    : uint64 array of shape (n, 72)    {G2 point, G1 point}
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libzecale_gpu.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        "zecale_b200: %s not found — build it with `python -m zecale_b200.build` "
+        "(nvcc, sm_100a). There is no CPU fallback." % LIB_PATH)
+
+_lib = ctypes.CDLL(LIB_PATH)
+
+_vp = ctypes.c_void_p
+_sz = ctypes.c_size_t
+_u = ctypes.c_uint
+_i = ctypes.c_int
+
+NTT_INVERSE = 1
+NTT_COSET = 2
+G1 = 1
+G2 = 2
+
+EXPORTS = {
+    "zecale_gpu_init": (_i, [ctypes.POINTER(_i), _i, ctypes.POINTER(_vp)]),
+    "zecale_gpu_shutdown": (None, [_vp]),
+    "zecale_gpu_last_error": (ctypes.c_char_p, [_vp]),
+    "zecale_gpu_msm_g1": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp]),
+    "zecale_gpu_msm_g2": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp]),
+    "zecale_gpu_ntt": (_i, [_vp, _vp, _u, _u, _vp]),
+    "zecale_gpu_pin_bases": (_i, [_vp, _vp, _sz, _sz, _i, ctypes.POINTER(_vp)]),
+    "zecale_gpu_unpin_bases": (_i, [_vp, _vp]),
+    "zecale_gpu_msm_pinned": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _vp]),
+    "zecale_gpu_msm_pinned_dev": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _vp, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_ntt_dev": (_i, [_vp, _vp, _u, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_launch_count": (ctypes.c_uint64, [_vp]),
+    "zecale_gpu_msm_window_bits": (_u, [_sz]),
+    "zecale_gpu_test_fq": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
+    "zecale_gpu_test_fr": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
+    "zecale_gpu_test_group": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
+    "zecale_gpu_bench_fq_mul": (_i, [_vp, _u, _u, _u, ctypes.POINTER(ctypes.c_float)]),
+}
+
+for _name, (_res, _args) in EXPORTS.items():
+    _f = getattr(_lib, _name)  # AttributeError here == header/library mismatch
+    _f.restype = _res
+    _f.argtypes = _args
+
+
+class ZecaleGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("zecale_gpu error %d: %s" % (code, msg))
+        self.code = code
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return ctypes.c_void_p(a)
+    assert a.flags["C_CONTIGUOUS"], "array must be C-contiguous"
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class PinnedBases:
+    def __init__(self, ctx, handle, n, group):
+        self.ctx, self.handle, self.n, self.group = ctx, handle, n, group
+
+    def release(self):
+        if self.handle is not None:
+            _lib.zecale_gpu_unpin_bases(self.ctx._h, self.handle)
+            self.handle = None
+
+
+class Context:
+    """One zecale_gpu_ctx (one device, one stream)."""
+
+    def __init__(self, device=None):
+        h = ctypes.c_void_p()
+        if device is None:
+            rc = _lib.zecale_gpu_init(None, 0, ctypes.byref(h))
+        else:
+            arr = (ctypes.c_int * 1)(device)
+            rc = _lib.zecale_gpu_init(arr, 1, ctypes.byref(h))
+        if rc != 0:
+            raise ZecaleGpuError(rc, "zecale_gpu_init failed (no usable sm_100 device?)")
+        self._h = h
+
+    def close(self):
+        if self._h is not None:
+            _lib.zecale_gpu_shutdown(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise ZecaleGpuError(rc, _lib.zecale_gpu_last_error(self._h).decode())
+
+    # -- MSM ------------------------------------------------------------------------
+    def _msm(self, fn, bases, scalars, index, n, base_offset_bytes):
+        out = np.zeros(36, dtype=np.uint64)
+        n = int(bases.shape[0] if n is None else n)
+        bstride = bases.strides[0] if bases.ndim == 2 else 288
+        sstride = scalars.strides[0] if scalars.ndim == 2 else 48
+        bptr = bases.ctypes.data + base_offset_bytes if n else 0
+        idx = None
+        if index is not None:
+            idx = np.ascontiguousarray(index, dtype=np.uint64)
+        self._ck(fn(self._h, ctypes.c_void_p(bptr), bstride, _ptr(scalars) if n else None, sstride, _ptr(idx), n, _ptr(out)))
+        return out
+
+    def msm_g1(self, bases, scalars, index=None, n=None, base_offset_bytes=0):
+        return self._msm(_lib.zecale_gpu_msm_g1, bases, scalars, index, n, base_offset_bytes)
+
+    def msm_g2(self, bases, scalars, index=None, n=None, base_offset_bytes=0):
+        return self._msm(_lib.zecale_gpu_msm_g2, bases, scalars, index, n, base_offset_bytes)
+
+    def pin_bases(self, bases, group=G1, base_offset_bytes=0):
+        h = ctypes.c_void_p()
+        n = int(bases.shape[0])
+        self._ck(_lib.zecale_gpu_pin_bases(self._h, ctypes.c_void_p(bases.ctypes.data + base_offset_bytes),
+                                           bases.strides[0], n, group, ctypes.byref(h)))
+        return PinnedBases(self, h, n, group)
+
+    def msm_pinned(self, pinned, scalars, index=None, n=None):
+        out = np.zeros(36, dtype=np.uint64)
+        n = pinned.n if n is None else int(n)
+        idx = None if index is None else np.ascontiguousarray(index, dtype=np.uint64)
+        self._ck(_lib.zecale_gpu_msm_pinned(self._h, pinned.handle, _ptr(scalars), scalars.strides[0], _ptr(idx), n, _ptr(out)))
+        return out
+
+    def msm_pinned_dev(self, pinned, d_scalars_ptr, n, scalar_stride=48, d_index_ptr=None):
+        """Scalars already on the device (raw pointer). Returns (point, kernel ms)."""
+        out = np.zeros(36, dtype=np.uint64)
+        ms = ctypes.c_float()
+        self._ck(_lib.zecale_gpu_msm_pinned_dev(self._h, pinned.handle, ctypes.c_void_p(d_scalars_ptr), scalar_stride,
+                                                ctypes.c_void_p(d_index_ptr) if d_index_ptr else None, int(n), _ptr(out),
+                                                ctypes.byref(ms)))
+        return out, ms.value
+
+    # -- NTT ------------------------------------------------------------------------
+    def ntt(self, a, flags=0, coset_g=None):
+        """In place on a host (m, 6) uint64 array; m must be a power of two."""
+        m = a.shape[0]
+        log_m = m.bit_length() - 1
+        if m == 0 or (1 << log_m) != m:
+            # libfqfft: basic_radix2_domain throws DomainSizeException (basic_radix2_domain.tcc:42-57)
+            raise ValueError("NTT size must be a power of two")
+        self._ck(_lib.zecale_gpu_ntt(self._h, _ptr(a), log_m, flags, _ptr(coset_g)))
+        return a
+
+    def ntt_dev(self, d_ptr, log_m, flags=0, coset_g=None):
+        ms = ctypes.c_float()
+        self._ck(_lib.zecale_gpu_ntt_dev(self._h, ctypes.c_void_p(d_ptr), log_m, flags, _ptr(coset_g), ctypes.byref(ms)))
+        return ms.value
+
+    # -- misc -----------------------------------------------------------------------
+    def launch_count(self):
+        return int(_lib.zecale_gpu_launch_count(self._h))
+
+    def test_fq(self, op, a, b=None):
+        out = np.zeros_like(a)
+        self._ck(_lib.zecale_gpu_test_fq(self._h, op, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
+        return out
+
+    def test_fr(self, op, a, b=None):
+        out = np.zeros_like(a)
+        self._ck(_lib.zecale_gpu_test_fr(self._h, op, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
+        return out
+
+    def test_group(self, op, a, b=None):
+        out = np.zeros_like(a)
+        self._ck(_lib.zecale_gpu_test_group(self._h, op, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
+        return out
+
+    def bench_fq_mul(self, blocks, threads_per_block, iters):
+        ms = ctypes.c_float()
+        self._ck(_lib.zecale_gpu_bench_fq_mul(self._h, blocks, threads_per_block, iters, ctypes.byref(ms)))
+        return ms.value
+
+
+def msm_window_bits(n):
+    return int(_lib.zecale_gpu_msm_window_bits(n))

@@ -1,0 +1,527 @@
+// C ABI of libzecale_gpu.so (see include/zecale_gpu.h). One translation unit: the
+// device functions are header-defined so that each kernel gets a single out-of-line
+// copy of fq_mul & co.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/zecale_gpu.h"
+#include "ec.cuh"
+#include "msm.cuh"
+#include "ntt.cuh"
+
+using namespace zecale;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct zecale_gpu_bases {
+    Affine *d = nullptr;
+    size_t n = 0;
+    int group = 0;
+};
+
+struct zecale_gpu_ctx {
+    int device = 0;
+    std::vector<int> devices;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::mutex mu;
+    std::string err;
+    uint64_t launches = 0;
+    DevBuf ws_msm, ws_in, ws_sc, ws_idx, ws_ntt, ws_tmp;
+    int *d_status = nullptr;
+    NttTables ntt;
+};
+
+namespace {
+
+int fail(zecale_gpu_ctx *ctx, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? ZECALE_GPU_E_NOMEM : ZECALE_GPU_E_CUDA, \
+                        "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));       \
+    } while (0)
+
+int reserve(zecale_gpu_ctx *ctx, DevBuf &b, size_t bytes)
+{
+    if (bytes <= b.cap) return 0;
+    if (b.p) CK(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes + bytes / 8 + 4096;
+    CK(cudaMalloc(&b.p, want));
+    b.cap = want;
+    return 0;
+}
+
+// Number of kernel launches of one MSM / NTT (kept next to the launch sequences).
+uint64_t msm_launches() { return 3 + 3 + 1 + 1 + 1 + 1 + 1 + 1 + 1; }
+
+int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n, Affine *d_out)
+{
+    // stage the raw libff array on the device, then convert (coalesced 16 B accesses)
+    size_t raw = (n - 1) * stride + sizeof(Proj);
+    int rc = reserve(ctx, ctx->ws_in, raw);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(ctx->ws_in.p, bases, raw, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->stream));
+    k_import_special<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>((const uint8_t *)ctx->ws_in.p, stride, 0,
+                                                                            (uint32_t)n, d_out, ctx->d_status);
+    ctx->launches++;
+    int st = 0;
+    CK(cudaMemcpyAsync(&st, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (st & 1) return fail(ctx, ZECALE_GPU_E_FORM, "MSM base not in special form (Z must be one or zero)");
+    return 0;
+}
+
+// d_bases: affine image on device; scalars: device pointer. Result -> host out (288 B).
+int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_scalars, size_t sstride,
+               const uint64_t *d_index, size_t n, void *out_point, float *elapsed_ms)
+{
+    if (n == 0) {
+        // empty sum = zero point (0, one, 0), as libff::multi_exp returns GroupT::zero()
+        Proj z;
+        memset(&z, 0, sizeof z);
+        uint32_t one[24];
+        CK(cudaMemcpyFromSymbol(one, FQ_ONE, sizeof one));
+        memcpy(z.Y.l, one, sizeof one);
+        memcpy(out_point, &z, sizeof z);
+        if (elapsed_ms) *elapsed_ms = 0.f;
+        return 0;
+    }
+    MsmPlan plan = msm_make_plan((uint32_t)n);
+    MsmBuffers lay = msm_layout(plan, nullptr);
+    int rc = reserve(ctx, ctx->ws_msm, lay.total);
+    if (rc) return rc;
+    MsmBuffers b = msm_layout(plan, (uint8_t *)ctx->ws_msm.p);
+    if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    CK(msm_launch(plan, b, d_bases, d_scalars, sstride, d_index, ctx->stream));
+    ctx->launches += msm_launches();
+    if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    CK(cudaMemcpyAsync(out_point, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    return 0;
+}
+
+int upload_scalars(zecale_gpu_ctx *ctx, const void *scalars, size_t sstride, const size_t *index, size_t n,
+                   const uint8_t **d_sc, const uint64_t **d_idx)
+{
+    // number of scalars touched: with an index the caller's scalar array extends to max(index)+1
+    size_t n_sc = n;
+    if (index) {
+        size_t mx = 0;
+        for (size_t i = 0; i < n; i++)
+            if (index[i] > mx) mx = index[i];
+        n_sc = mx + 1;
+    }
+    size_t bytes = (n_sc - 1) * sstride + sizeof(Fr);
+    int rc = reserve(ctx, ctx->ws_sc, bytes);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(ctx->ws_sc.p, scalars, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    *d_sc = (const uint8_t *)ctx->ws_sc.p;
+    *d_idx = nullptr;
+    if (index) {
+        static_assert(sizeof(size_t) == 8, "size_t");
+        rc = reserve(ctx, ctx->ws_idx, n * 8);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(ctx->ws_idx.p, index, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+        *d_idx = (const uint64_t *)ctx->ws_idx.p;
+    }
+    return 0;
+}
+
+int msm_host(zecale_gpu_ctx *ctx, const void *bases, size_t bstride, const void *scalars, size_t sstride,
+             const size_t *index, size_t n, void *out)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!out || (n && (!bases || !scalars)) || bstride < sizeof(Proj) || sstride < sizeof(Fr) || n >= (1ull << 31))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, nullptr, 0, out, nullptr);
+    int rc = reserve(ctx, ctx->ws_tmp, n * sizeof(Affine));
+    if (rc) return rc;
+    rc = import_bases(ctx, bases, bstride, n, (Affine *)ctx->ws_tmp.p);
+    if (rc) return rc;
+    const uint8_t *d_sc;
+    const uint64_t *d_idx;
+    rc = upload_scalars(ctx, scalars, sstride, index, n, &d_sc, &d_idx);
+    if (rc) return rc;
+    return msm_device(ctx, (const Affine *)ctx->ws_tmp.p, d_sc, sstride, d_idx, n, out, nullptr);
+}
+
+// ------------------------------------------------------------------ test kernels
+__global__ void k_test_fq(int op, const Fq *a, const Fq *b, Fq *out, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fq x, y, r;
+    fq_copy(x, a[i]);
+    if (b) fq_copy(y, b[i]);
+    switch (op) {
+    case 0: fq_add(r, x, y); break;
+    case 1: fq_sub(r, x, y); break;
+    case 2: fq_mul(r, x, y); break;
+    case 3: fq_sqr(r, x); break;
+    case 4: fq_inv(r, x); break;
+    case 5: fq_neg(r, x); break;
+    case 6: {
+        Fq one;
+        fq_set_zero(one);
+        one.l[0] = 1;
+        fq_mul(r, x, one);
+        break;
+    }
+    default: fq_set_zero(r);
+    }
+    fq_copy(out[i], r);
+}
+
+__global__ void k_test_fr(int op, const Fr *a, const Fr *b, Fr *out, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t x[12], y[12], r[12];
+    fr_load(x, a + i);
+    if (b)
+        fr_load(y, b + i);
+    else
+        fr_load(y, a + i);
+    switch (op) {
+    case 0: fr_add_regs(r, x, y); break;
+    case 1: fr_sub_regs(r, x, y); break;
+    case 2: fr_mul_regs(r, x, y); break;
+    case 3: fr_sqr_regs(r, x); break;
+    case 4: fr_inv(r, x); break;
+    case 5: {
+        uint32_t z[12];
+#pragma unroll
+        for (int k = 0; k < 12; k++) z[k] = 0;
+        fr_sub_regs(r, z, x);
+        break;
+    }
+    case 6: fr_from_mont(r, x); break;
+    default:
+#pragma unroll
+        for (int k = 0; k < 12; k++) r[k] = 0;
+    }
+    fr_store(out + i, r);
+}
+
+__global__ void k_test_group(int op, const Proj *a, const Proj *b, Proj *out, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    XYZZ acc;
+    xyzz_from_proj(acc, a[i]);
+    switch (op) {
+    case 0: {
+        XYZZ o;
+        xyzz_from_proj(o, b[i]);
+        xyzz_add(acc, o);
+        break;
+    }
+    case 1: {
+        Affine q; // b[i] is special: Z in {one, 0}
+        if (fq_is_zero(b[i].Z)) {
+            fq_set_zero(q.x);
+            fq_set_zero(q.y);
+        } else {
+            fq_copy(q.x, b[i].X);
+            fq_copy(q.y, b[i].Y);
+        }
+        xyzz_madd(acc, q, false);
+        break;
+    }
+    case 2: xyzz_dbl(acc); break;
+    default: break;
+    }
+    xyzz_to_special(out[i], acc);
+}
+
+__global__ void __launch_bounds__(128, 4) k_bench_fq_mul(Fq *sink, unsigned iters)
+{
+    Fq x, y;
+    unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < 24; i++) {
+        x.l[i] = FQ_R2[i] ^ (t * 2654435761u >> (i & 7));
+        y.l[i] = FQ_ONE[i] + t;
+    }
+    x.l[23] &= 0xffffff;
+    y.l[23] &= 0xffffff;
+    for (unsigned k = 0; k < iters; k++) fq_mul(x, x, y);
+    if (x.l[0] == 0x12345678u && x.l[5] == 77u) fq_copy(sink[0], x); // keep the chain alive
+}
+
+template <typename T>
+int test_elementwise(zecale_gpu_ctx *ctx, void (*launch)(int, const T *, const T *, T *, size_t, cudaStream_t), int op,
+                     const void *a, const void *b, void *out, size_t n)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!a || !out || !n) return fail(ctx, ZECALE_GPU_E_ARG, "test hook: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    size_t bytes = n * sizeof(T);
+    int rc = reserve(ctx, ctx->ws_tmp, bytes * 3);
+    if (rc) return rc;
+    T *da = (T *)ctx->ws_tmp.p, *db = da + n, *dout = db + n;
+    CK(cudaMemcpyAsync(da, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (b) CK(cudaMemcpyAsync(db, b, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    launch(op, da, b ? db : nullptr, dout, n, ctx->stream);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, dout, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+void launch_fq(int op, const Fq *a, const Fq *b, Fq *o, size_t n, cudaStream_t s)
+{
+    k_test_fq<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(op, a, b, o, n);
+}
+void launch_fr(int op, const Fr *a, const Fr *b, Fr *o, size_t n, cudaStream_t s)
+{
+    k_test_fr<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(op, a, b, o, n);
+}
+void launch_group(int op, const Proj *a, const Proj *b, Proj *o, size_t n, cudaStream_t s)
+{
+    k_test_group<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(op, a, b, o, n);
+}
+
+} // namespace
+
+// ====================================================================== C ABI
+extern "C" {
+
+int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
+{
+    if (!out) return ZECALE_GPU_E_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return ZECALE_GPU_E_CUDA;
+    zecale_gpu_ctx *ctx = new zecale_gpu_ctx();
+    if (devices && n_devices > 0) {
+        ctx->devices.assign(devices, devices + n_devices);
+    } else {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        ctx->devices.push_back(cur);
+    }
+    ctx->device = ctx->devices[0];
+    cudaDeviceProp prop;
+    if (cudaSetDevice(ctx->device) != cudaSuccess || cudaGetDeviceProperties(&prop, ctx->device) != cudaSuccess ||
+        prop.major < 10) {
+        delete ctx;
+        return ZECALE_GPU_E_CUDA; // sm_100a only: no fallback path
+    }
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+        cudaMalloc((void **)&ctx->d_status, sizeof(int)) != cudaSuccess) {
+        delete ctx;
+        return ZECALE_GPU_E_CUDA;
+    }
+    // deep call chains (fq_inv -> fq_mul) with ~1.5 KB frames
+    cudaDeviceSetLimit(cudaLimitStackSize, 8192);
+    *out = ctx;
+    return 0;
+}
+
+void zecale_gpu_shutdown(zecale_gpu_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (DevBuf *b : {&ctx->ws_msm, &ctx->ws_in, &ctx->ws_sc, &ctx->ws_idx, &ctx->ws_ntt, &ctx->ws_tmp})
+        if (b->p) cudaFree(b->p);
+    ntt_tables_free(ctx->ntt);
+    cudaFree(ctx->d_status);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *zecale_gpu_last_error(zecale_gpu_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int zecale_gpu_msm_g1(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, const void *scalars,
+                      size_t scalar_stride, const size_t *scalar_index, size_t n, void *out_point)
+{
+    return msm_host(ctx, bases, base_stride, scalars, scalar_stride, scalar_index, n, out_point);
+}
+
+// G2 lives over the same Fq with a = 0: identical arithmetic (ec.cuh header comment).
+int zecale_gpu_msm_g2(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, const void *scalars,
+                      size_t scalar_stride, const size_t *scalar_index, size_t n, void *out_point)
+{
+    return msm_host(ctx, bases, base_stride, scalars, scalar_stride, scalar_index, n, out_point);
+}
+
+int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
+                         zecale_gpu_bases **handle)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!bases || !handle || !n || base_stride < sizeof(Proj) || n >= (1ull << 31) ||
+        (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_pin_bases: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    zecale_gpu_bases *h = new zecale_gpu_bases();
+    h->n = n;
+    h->group = group;
+    cudaError_t e = cudaMalloc((void **)&h->d, n * sizeof(Affine));
+    if (e != cudaSuccess) {
+        delete h;
+        return fail(ctx, ZECALE_GPU_E_NOMEM, "pin_bases: %s", cudaGetErrorString(e));
+    }
+    int rc = import_bases(ctx, bases, base_stride, n, h->d);
+    if (rc) {
+        cudaFree(h->d);
+        delete h;
+        return rc;
+    }
+    *handle = h;
+    return 0;
+}
+
+int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *h)
+{
+    if (!ctx || !h) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(h->d);
+    delete h;
+    return 0;
+}
+
+int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, const void *scalars, size_t scalar_stride,
+                          const size_t *scalar_index, size_t n, void *out_point)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!h || !out_point || n > h->n || (n && !scalars) || scalar_stride < sizeof(Fr))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, nullptr, 0, out_point, nullptr);
+    const uint8_t *d_sc;
+    const uint64_t *d_idx;
+    int rc = upload_scalars(ctx, scalars, scalar_stride, scalar_index, n, &d_sc, &d_idx);
+    if (rc) return rc;
+    return msm_device(ctx, h->d, d_sc, scalar_stride, d_idx, n, out_point, nullptr);
+}
+
+int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, const void *d_scalars,
+                              size_t scalar_stride, const uint64_t *d_scalar_index, size_t n, void *out_point,
+                              float *elapsed_ms)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!h || !out_point || n > h->n || (n && !d_scalars) || scalar_stride < sizeof(Fr))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    return msm_device(ctx, h->d, (const uint8_t *)d_scalars, scalar_stride, d_scalar_index, n, out_point, elapsed_ms);
+}
+
+int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned flags, const void *coset_g,
+                       float *elapsed_ms)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!d_a || (flags & ~3u) || ((flags & ZECALE_GPU_NTT_COSET) && !coset_g))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt: bad argument");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    size_t m = (size_t)1 << log_m;
+    int rc = reserve(ctx, ctx->ws_ntt, m * sizeof(Fr));
+    if (rc) return rc;
+    if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    unsigned nl = 0;
+    CK(ntt_launch(ctx->ntt, (Fr *)d_a, (Fr *)ctx->ws_ntt.p, log_m, flags, (const Fr *)coset_g, ctx->stream, &nl));
+    ctx->launches += nl;
+    if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    return 0;
+}
+
+int zecale_gpu_ntt(zecale_gpu_ctx *ctx, void *a, unsigned log_m, unsigned flags, const void *coset_g)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    if (!a) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt: null vector");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt: log_m %u out of range", log_m);
+    size_t bytes = ((size_t)1 << log_m) * sizeof(Fr);
+    void *d = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        CK(cudaSetDevice(ctx->device));
+        int rc = reserve(ctx, ctx->ws_in, bytes);
+        if (rc) return rc;
+        d = ctx->ws_in.p;
+        CK(cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    int rc = zecale_gpu_ntt_dev(ctx, d, log_m, flags, coset_g, nullptr);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CK(cudaMemcpyAsync(a, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+unsigned zecale_gpu_msm_window_bits(size_t n) { return n ? msm_make_plan((uint32_t)n).c : 0; }
+
+int zecale_gpu_test_fq(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n)
+{
+    return test_elementwise<Fq>(ctx, launch_fq, op, a, b, out, n);
+}
+int zecale_gpu_test_fr(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n)
+{
+    return test_elementwise<Fr>(ctx, launch_fr, op, a, b, out, n);
+}
+int zecale_gpu_test_group(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n)
+{
+    return test_elementwise<Proj>(ctx, launch_group, op, a, b, out, n);
+}
+
+int zecale_gpu_bench_fq_mul(zecale_gpu_ctx *ctx, unsigned blocks, unsigned tpb, unsigned iters, float *elapsed_ms)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!blocks || !tpb || tpb > 128 || !elapsed_ms) return fail(ctx, ZECALE_GPU_E_ARG, "bench_fq_mul: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    int rc = reserve(ctx, ctx->ws_tmp, sizeof(Fq));
+    if (rc) return rc;
+    k_bench_fq_mul<<<blocks, tpb, 0, ctx->stream>>>((Fq *)ctx->ws_tmp.p, 8); // warm-up
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    k_bench_fq_mul<<<blocks, tpb, 0, ctx->stream>>>((Fq *)ctx->ws_tmp.p, iters);
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->launches += 2;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    return 0;
+}
+
+} // extern "C"
