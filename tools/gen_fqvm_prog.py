@@ -1,0 +1,293 @@
+#!/usr/bin/env python3
+"""Assemble the Fq-VM micro-programs (zecale_b200/csrc/fqvm_prog.cuh).
+
+The EC layer of the CUDA library is written for a tiny register machine whose
+registers ("slots") are 761-bit Fq elements held in per-thread local memory and
+whose instructions are whole field operations (see fqvm.cuh for why). This script
+holds the point-arithmetic formulas as assembly text and resolves labels.
+
+Formulas (EFD, short Weierstrass a = 0, XYZZ coordinates x = X/ZZ, y = Y/ZZZ):
+  madd-2008-s, mdbl-2008-s-1, add-2008-s, dbl-2008-s-1.
+They replace libff's homogeneous-projective bw6_761_G1/G2::mixed_add / operator+ / dbl
+(bw6_761_g1.cpp:111-358, bw6_761_g2.cpp:116-364) including their special cases
+(either operand zero, P == Q -> doubling, P == -Q -> zero); the coordinate system is
+free because parity is checked on the normalised affine point, which is unique.
+"""
+import os
+import re
+
+SLOTS = {"X": 0, "Y": 1, "ZZ": 2, "ZZZ": 3, "QX": 4, "QY": 5, "QZZ": 6, "QZZZ": 7,
+         "T0": 8, "T1": 9, "T2": 10, "T3": 11, "T4": 12, "RX": 13, "RY": 14, "RZZ": 15, "RZZZ": 16,
+         "K0": 17}
+NSLOT = 18
+
+OPS = {"MUL": 0, "ADD": 1, "SUB": 2, "MOV": 3, "ONE": 4, "ZERO": 5, "JZ": 6, "JMP": 7, "JBIT": 8,
+       "DECJNZ": 9, "SETCNT": 10, "CALL": 11, "RET": 12, "HOOK": 13, "HALT": 14}
+
+PROGRAM = r"""
+; ---------------------------------------------------------------- acc += (QX, QY) affine, not infinity
+madd:
+    JZ   ZZ, madd_accinf
+    MUL  T0, QX, ZZ         ; U2
+    MUL  T1, QY, ZZZ        ; S2
+    SUB  T0, T0, X          ; P = U2 - X1
+    SUB  T1, T1, Y          ; R = S2 - Y1
+    JZ   T0, madd_samex
+    MUL  T2, T0, T0         ; PP
+    MUL  T0, T0, T2         ; PPP
+    MUL  T3, X, T2          ; Q = X1*PP
+    MUL  ZZ, ZZ, T2         ; ZZ3
+    MUL  ZZZ, ZZZ, T0       ; ZZZ3
+    MUL  T2, T1, T1         ; R^2
+    SUB  T2, T2, T0
+    SUB  T2, T2, T3
+    SUB  X, T2, T3          ; X3 = R^2 - PPP - 2Q
+    SUB  T3, T3, X
+    MUL  T3, T1, T3
+    MUL  T2, Y, T0
+    SUB  Y, T3, T2          ; Y3 = R(Q - X3) - Y1*PPP
+    HOOK 0
+madd_accinf:
+    MOV  X, QX
+    MOV  Y, QY
+    ONE  ZZ
+    ONE  ZZZ
+    HOOK 0
+madd_samex:
+    JZ   T1, mdbl
+    JMP  set_inf
+mdbl:                       ; acc = 2*(QX, QY)
+    ADD  T0, QY, QY         ; U = 2 Y1
+    MUL  T1, T0, T0         ; V = U^2
+    MUL  T2, T0, T1         ; W = U V
+    MUL  T3, QX, T1         ; S = X1 V
+    MUL  T4, QX, QX
+    ADD  T0, T4, T4
+    ADD  T0, T0, T4         ; M = 3 X1^2
+    MUL  T4, T0, T0
+    SUB  T4, T4, T3
+    SUB  X, T4, T3          ; X3 = M^2 - 2S
+    SUB  T4, T3, X
+    MUL  T4, T0, T4
+    MUL  T0, T2, QY
+    SUB  Y, T4, T0          ; Y3 = M(S - X3) - W Y1
+    MOV  ZZ, T1
+    MOV  ZZZ, T2
+    HOOK 0
+; ---------------------------------------------------------------- acc -> affine (QX, QY); HOOK 1, or HOOK 2 if infinity
+toaff:
+    JZ   ZZ, toaff_inf
+    MOV  T1, ZZZ
+    CALL inv                ; T0 = 1/ZZZ
+    MUL  QY, Y, T0          ; y = Y/ZZZ
+    MUL  T2, T0, ZZ         ; ZZ/ZZZ = 1/Z
+    MUL  T2, T2, T2         ; 1/ZZ
+    MUL  QX, X, T2          ; x = X/ZZ
+    HOOK 1
+toaff_inf:
+    HOOK 2
+; T0 = T1^(q-2) (Fermat; libff uses mpn_gcdext, fp.tcc:680-727 -- the inverse is unique)
+inv:
+    MOV  T0, T1
+    SETCNT 759              ; q-2 has 761 bits; the top one is the MOV
+inv_loop:
+    MUL  T0, T0, T0
+    JBIT inv_mul
+inv_next:
+    DECJNZ inv_loop
+    RET
+inv_mul:
+    MUL  T0, T0, T1
+    JMP  inv_next
+; ---------------------------------------------------------------- Q = libff projective (QX, QY, QZZ = Z) -> XYZZ in Q
+fromproj:
+    JZ   QZZ, fromproj_inf
+    MUL  T0, QZZ, QZZ       ; Z^2
+    MUL  QX, QX, QZZ        ; X Z
+    MUL  QY, QY, T0         ; Y Z^2
+    MUL  QZZZ, T0, QZZ      ; Z^3
+    MOV  QZZ, T0
+    HOOK 0
+fromproj_inf:
+    ZERO QX
+    ONE  QY
+    ZERO QZZ
+    ZERO QZZZ
+    HOOK 0
+; ---------------------------------------------------------------- acc = Q
+movqa:
+    MOV  X, QX
+    MOV  Y, QY
+    MOV  ZZ, QZZ
+    MOV  ZZZ, QZZZ
+    HOOK 0
+; ---------------------------------------------------------------- batched inversion helpers (precompute normalisation)
+; T2 = running product; step: T3 = T2 (saved by hook), T2 *= ZZZ
+prodstep:
+    MUL  T2, T2, ZZZ
+    HOOK 0
+; T0 = 1/T2
+invprod:
+    MOV  T1, T2
+    CALL inv
+    HOOK 0
+; given T0 = 1/(prefix * ZZZ), T3 = prefix: T4 = T0*T3 = 1/ZZZ ; T0 = T0*ZZZ = 1/prefix ; then affine into QX,QY
+unstep:
+    MUL  T4, T0, T3         ; 1/ZZZ
+    MUL  T0, T0, ZZZ        ; inverse of the shorter prefix
+    MUL  QY, Y, T4
+    MUL  T4, T4, ZZ         ; 1/Z
+    MUL  T4, T4, T4         ; 1/ZZ
+    MUL  QX, X, T4
+    HOOK 0
+"""
+
+ADD_TEMPLATE = r"""
+; ---------------------------------------------------------------- {AX}.. += {BX}..   (general XYZZ addition)
+add{S}:
+    JZ   {BZZ}, add_done{S}
+    JZ   {AZZ}, add_accinf{S}
+    MUL  T0, {AX}, {BZZ}      ; U1
+    MUL  T1, {BX}, {AZZ}      ; U2
+    MUL  T2, {AY}, {BZZZ}     ; S1
+    MUL  T3, {BY}, {AZZZ}     ; S2
+    SUB  T1, T1, T0         ; P
+    SUB  T3, T3, T2         ; R
+    JZ   T1, add_samex{S}
+    MUL  T4, T1, T1         ; PP
+    MUL  T1, T1, T4         ; PPP
+    MUL  T0, T0, T4         ; Q = U1 PP
+    MUL  {AZZ}, {AZZ}, {BZZ}
+    MUL  {AZZ}, {AZZ}, T4       ; ZZ3
+    MUL  {AZZZ}, {AZZZ}, {BZZZ}
+    MUL  {AZZZ}, {AZZZ}, T1     ; ZZZ3
+    MUL  T4, T3, T3         ; R^2
+    SUB  T4, T4, T1
+    SUB  T4, T4, T0
+    SUB  {AX}, T4, T0         ; X3
+    SUB  T0, T0, {AX}
+    MUL  T0, T3, T0
+    MUL  T2, T2, T1
+    SUB  {AY}, T0, T2         ; Y3
+add_done{S}:
+    HOOK 0
+add_accinf{S}:
+    MOV  {AX}, {BX}
+    MOV  {AY}, {BY}
+    MOV  {AZZ}, {BZZ}
+    MOV  {AZZZ}, {BZZZ}
+    HOOK 0
+add_samex{S}:
+    JZ   T3, dbl{S}
+set_inf{S}:
+    ZERO {AX}
+    ONE  {AY}
+    ZERO {AZZ}
+    ZERO {AZZZ}
+    HOOK 0
+; ---------------------------------------------------------------- {AX}.. = 2 {AX}..
+dbl{S}:
+    JZ   {AZZ}, dbl_done{S}
+    ADD  T0, {AY}, {AY}         ; U
+    MUL  T1, T0, T0         ; V
+    MUL  T2, T0, T1         ; W
+    MUL  T3, {AX}, T1         ; S
+    MUL  T4, {AX}, {AX}
+    ADD  T0, T4, T4
+    ADD  T0, T0, T4         ; M
+    MUL  T4, T0, T0
+    SUB  T4, T4, T3
+    SUB  {AX}, T4, T3         ; X3
+    SUB  T4, T3, {AX}
+    MUL  T4, T0, T4
+    MUL  T0, T2, {AY}
+    SUB  {AY}, T4, T0         ; Y3
+    MUL  {AZZ}, T1, {AZZ}
+    MUL  {AZZZ}, T2, {AZZZ}
+dbl_done{S}:
+    HOOK 0
+"""
+
+ACC = dict(AX="X", AY="Y", AZZ="ZZ", AZZZ="ZZZ")
+PROGRAM += ADD_TEMPLATE.format(S="", BX="QX", BY="QY", BZZ="QZZ", BZZZ="QZZZ", **ACC)
+# second accumulator R += acc (running-sum bucket reduction)
+PROGRAM += ADD_TEMPLATE.format(S="_r", AX="RX", AY="RY", AZZ="RZZ", AZZZ="RZZZ", BX="X", BY="Y", BZZ="ZZ", BZZZ="ZZZ")
+
+ENTRY_POINTS = ["madd", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep"]
+
+
+def assemble(text):
+    lines = []
+    labels = {}
+    for raw in text.splitlines():
+        ln = raw.split(";")[0].strip()
+        if not ln:
+            continue
+        m = re.match(r"^([A-Za-z_][A-Za-z_0-9]*):$", ln)
+        if m:
+            labels[m.group(1)] = len(lines)
+            continue
+        lines.append(ln)
+    code = []
+    for ln in lines:
+        parts = ln.replace(",", " ").split()
+        op = parts[0]
+        args = parts[1:]
+        o = OPS[op]
+        d = a = b = 0
+        if op in ("MUL", "ADD", "SUB"):
+            d, a, b = (SLOTS[x] for x in args)
+            imm = a | (b << 8)
+        elif op == "MOV":
+            d, a = SLOTS[args[0]], SLOTS[args[1]]
+            imm = a
+        elif op in ("ONE", "ZERO"):
+            d = SLOTS[args[0]]
+            imm = 0
+        elif op == "JZ":
+            d = SLOTS[args[0]]
+            imm = labels[args[1]]
+        elif op in ("JMP", "JBIT", "DECJNZ", "CALL"):
+            imm = labels[args[0]]
+        elif op == "SETCNT":
+            imm = int(args[0])
+        elif op == "HOOK":
+            d = int(args[0])
+            imm = 0
+        elif op in ("RET", "HALT"):
+            imm = 0
+        else:
+            raise ValueError(ln)
+        assert 0 <= imm < 65536 and 0 <= d < 256
+        code.append(o | (d << 8) | (imm << 16))
+    return code, labels
+
+
+def main():
+    code, labels = assemble(PROGRAM)
+    o = "// GENERATED by tools/gen_fqvm_prog.py — do not edit by hand.\n"
+    o += "// Micro-programs of the Fq VM (fqvm.cuh): word = op | d << 8 | imm16 << 16.\n"
+    o += "#pragma once\n#include <cstdint>\nnamespace zecale {\n"
+    o += "enum : uint32_t {\n"
+    for k, v in OPS.items():
+        o += "    VOP_%s = %d,\n" % (k, v)
+    o += "};\nenum : uint32_t {\n"
+    for k, v in SLOTS.items():
+        o += "    VS_%s = %d,\n" % (k, v)
+    o += "    VS_COUNT = %d\n};\nenum : uint32_t {\n" % NSLOT
+    for k in ENTRY_POINTS:
+        o += "    VPC_%s = %d,\n" % (k.upper(), labels[k])
+    o += "};\n"
+    o += "static constexpr int FQVM_CODE_LEN = %d;\n" % len(code)
+    o += "__device__ __constant__ uint32_t FQVM_CODE[%d] = {\n" % len(code)
+    for i in range(0, len(code), 8):
+        o += "    " + ", ".join("0x%08xu" % w for w in code[i:i + 8]) + ",\n"
+    o += "};\n} // namespace zecale\n"
+    dst = os.path.join(os.path.dirname(__file__), "..", "zecale_b200", "csrc", "fqvm_prog.cuh")
+    with open(dst, "w") as f:
+        f.write(o)
+    print("wrote", os.path.abspath(dst), len(code), "uops")
+
+
+if __name__ == "__main__":
+    main()

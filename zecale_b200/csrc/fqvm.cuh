@@ -1,0 +1,273 @@
+// Fq VM: the EC layer's execution model on sm_100a.
+//
+// A BW6-761 base-field element is 24 x u32. A Montgomery product is 1152 wide MADs
+// (~2.4k SASS instructions, ~40 KB) and needs ~120 registers, so (a) point formulas
+// cannot keep their 10+ live Fq temporaries in registers and (b) inlining a product at
+// every use would make MSM kernels megabytes of SASS. Out-of-line device functions
+// taking pointers to stack temporaries were tried first and miscompile under warp
+// divergence (ptxas passes the uniform stack addresses in UR registers that the other
+// side of a divergent branch clobbers). So every kernel here contains exactly ONE copy
+// of the field arithmetic, inside a small interpreter:
+//
+//   * registers ("slots") are Fq elements in per-thread local memory (L1-resident,
+//     hardware-interleaved so a warp's access to word k of slot s is one 128 B line);
+//   * instructions are whole field operations   MUL/ADD/SUB/MOV/ONE/ZERO d, a, b
+//     plus a few control ops (JZ slot, JMP, CALL/RET, a counter loop for Fermat
+//     inversion) and HOOK n, which hands control to the kernel's own lambda (fetch the
+//     next bucket entry, store a result, choose the next program, or halt);
+//   * each thread has its own pc, so data-dependent special cases (accumulator at
+//     infinity, P == Q doubling, P == -Q) are ordinary SIMT divergence inside one
+//     switch — no calls, and in the common case the whole warp runs the same uop.
+//
+// Decode + 12 LDL.128 + 6 STL.128 per uop is < 3 % of the 1152 IMAD.WIDE of a MUL.
+// The programs (point add / mixed add / double / normalise) are in fqvm_prog.cuh,
+// assembled by tools/gen_fqvm_prog.py.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "field_asm.cuh"
+#include "field_consts.cuh"
+#include "fqvm_prog.cuh"
+
+namespace zecale {
+
+struct alignas(16) Fq {
+    uint32_t l[24];
+};
+struct alignas(16) Fr {
+    uint32_t l[12];
+};
+static_assert(sizeof(Fq) == 96 && sizeof(Fr) == 48, "field element layout");
+
+struct alignas(16) Affine {
+    Fq x, y;
+};
+struct alignas(16) XYZZ {
+    Fq x, y, zz, zzz;
+};
+// libff in-memory point: homogeneous projective {X, Y, Z}
+struct alignas(16) Proj {
+    Fq X, Y, Z;
+};
+static_assert(sizeof(Affine) == 192 && sizeof(XYZZ) == 384 && sizeof(Proj) == 288, "point layout");
+
+// Slot file: VS_COUNT Fq values as uint4[6] each.
+struct FqSlots {
+    uint4 w[VS_COUNT * 6];
+};
+
+__device__ __forceinline__ void vs_load(uint32_t (&x)[24], const FqSlots &S, uint32_t slot)
+{
+    const uint4 *p = S.w + slot * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        uint4 v = p[k];
+        x[4 * k] = v.x;
+        x[4 * k + 1] = v.y;
+        x[4 * k + 2] = v.z;
+        x[4 * k + 3] = v.w;
+    }
+}
+
+__device__ __forceinline__ void vs_store(FqSlots &S, uint32_t slot, const uint32_t (&x)[24])
+{
+    uint4 *p = S.w + slot * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) p[k] = make_uint4(x[4 * k], x[4 * k + 1], x[4 * k + 2], x[4 * k + 3]);
+}
+
+// slot <- global/shared/any 16-byte aligned Fq
+__device__ __forceinline__ void vs_set(FqSlots &S, uint32_t slot, const Fq *src)
+{
+    const uint4 *s = reinterpret_cast<const uint4 *>(src);
+    uint4 *p = S.w + slot * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) p[k] = s[k];
+}
+
+__device__ __forceinline__ void vs_get(Fq *dst, const FqSlots &S, uint32_t slot)
+{
+    uint4 *d = reinterpret_cast<uint4 *>(dst);
+    const uint4 *p = S.w + slot * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) d[k] = p[k];
+}
+
+__device__ __forceinline__ void vs_zero(FqSlots &S, uint32_t slot)
+{
+    uint4 *p = S.w + slot * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) p[k] = make_uint4(0, 0, 0, 0);
+}
+
+__device__ __forceinline__ void vs_one(FqSlots &S, uint32_t slot)
+{
+    uint4 *p = S.w + slot * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) p[k] = make_uint4(FQ_ONE[4 * k], FQ_ONE[4 * k + 1], FQ_ONE[4 * k + 2], FQ_ONE[4 * k + 3]);
+}
+
+__device__ __forceinline__ bool vs_is_zero(const FqSlots &S, uint32_t slot)
+{
+    const uint4 *p = S.w + slot * 6;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        uint4 v = p[k];
+        acc |= v.x | v.y | v.z | v.w;
+    }
+    return acc == 0;
+}
+
+// slot <- -(*src) mod q (0 stays 0); cf. fp.tcc:617-630
+__device__ __forceinline__ void vs_set_neg(FqSlots &S, uint32_t slot, const Fq *src)
+{
+    uint32_t a[24], z[24], r[24];
+    const uint4 *s = reinterpret_cast<const uint4 *>(src);
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        uint4 v = s[k];
+        a[4 * k] = v.x;
+        a[4 * k + 1] = v.y;
+        a[4 * k + 2] = v.z;
+        a[4 * k + 3] = v.w;
+        z[4 * k] = z[4 * k + 1] = z[4 * k + 2] = z[4 * k + 3] = 0;
+    }
+    fq_sub_regs(r, z, a);
+    vs_store(S, slot, r);
+}
+
+// Accumulator (slots X..ZZZ) <-> memory
+__device__ __forceinline__ void vs_store_acc(XYZZ *dst, const FqSlots &S)
+{
+    vs_get(&dst->x, S, VS_X);
+    vs_get(&dst->y, S, VS_Y);
+    vs_get(&dst->zz, S, VS_ZZ);
+    vs_get(&dst->zzz, S, VS_ZZZ);
+}
+__device__ __forceinline__ void vs_load_q(FqSlots &S, const XYZZ *src)
+{
+    vs_set(S, VS_QX, &src->x);
+    vs_set(S, VS_QY, &src->y);
+    vs_set(S, VS_QZZ, &src->zz);
+    vs_set(S, VS_QZZZ, &src->zzz);
+}
+__device__ __forceinline__ void vs_load_acc(FqSlots &S, const XYZZ *src)
+{
+    vs_set(S, VS_X, &src->x);
+    vs_set(S, VS_Y, &src->y);
+    vs_set(S, VS_ZZ, &src->zz);
+    vs_set(S, VS_ZZZ, &src->zzz);
+}
+__device__ __forceinline__ void vs_acc_inf(FqSlots &S)
+{
+    vs_zero(S, VS_X);
+    vs_one(S, VS_Y);
+    vs_zero(S, VS_ZZ);
+    vs_zero(S, VS_ZZZ);
+}
+__device__ __forceinline__ void xyzz_store_inf(XYZZ *dst)
+{
+    uint4 *d = reinterpret_cast<uint4 *>(dst);
+#pragma unroll
+    for (int k = 0; k < 24; k++) d[k] = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int k = 0; k < 6; k++) d[6 + k] = make_uint4(FQ_ONE[4 * k], FQ_ONE[4 * k + 1], FQ_ONE[4 * k + 2], FQ_ONE[4 * k + 3]);
+}
+
+// Run from `pc` until the hook returns false. hook(id, pc, S) may change pc.
+template <class Hook>
+__device__ __forceinline__ void fqvm_run(FqSlots &S, uint32_t pc, Hook &&hook)
+{
+    uint32_t ret = 0, cnt = 0;
+    for (;;) {
+        const uint32_t u = FQVM_CODE[pc++];
+        const uint32_t op = u & 0xffu, d = (u >> 8) & 0xffu, imm = u >> 16;
+        if (op <= VOP_SUB) {
+            uint32_t x[24], y[24], z[24];
+            vs_load(x, S, imm & 0xffu);
+            vs_load(y, S, imm >> 8);
+            if (op == VOP_MUL)
+                fq_mul_regs(z, x, y);
+            else if (op == VOP_ADD)
+                fq_add_regs(z, x, y);
+            else
+                fq_sub_regs(z, x, y);
+            vs_store(S, d, z);
+            continue;
+        }
+        switch (op) {
+        case VOP_MOV: {
+            const uint4 *s = S.w + imm * 6;
+            uint4 *p = S.w + d * 6;
+#pragma unroll
+            for (int k = 0; k < 6; k++) p[k] = s[k];
+            break;
+        }
+        case VOP_ONE: vs_one(S, d); break;
+        case VOP_ZERO: vs_zero(S, d); break;
+        case VOP_JZ:
+            if (vs_is_zero(S, d)) pc = imm;
+            break;
+        case VOP_JMP: pc = imm; break;
+        case VOP_JBIT:
+            if ((FQ_PM2[cnt >> 5] >> (cnt & 31u)) & 1u) pc = imm;
+            break;
+        case VOP_DECJNZ:
+            if (cnt != 0) {
+                cnt--;
+                pc = imm;
+            }
+            break;
+        case VOP_SETCNT: cnt = imm; break;
+        case VOP_CALL:
+            ret = pc;
+            pc = imm;
+            break;
+        case VOP_RET: pc = ret; break;
+        case VOP_HOOK:
+            if (!hook(d, pc, S)) return;
+            break;
+        default: return; // HALT
+        }
+    }
+}
+
+// ---------------------------------------------------------------- Fr (register form)
+__device__ __forceinline__ void fr_load(uint32_t (&r)[12], const Fr *p)
+{
+    const uint4 *s = reinterpret_cast<const uint4 *>(p);
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        uint4 v = s[i];
+        r[4 * i] = v.x;
+        r[4 * i + 1] = v.y;
+        r[4 * i + 2] = v.z;
+        r[4 * i + 3] = v.w;
+    }
+}
+
+__device__ __forceinline__ void fr_store(Fr *p, const uint32_t (&r)[12])
+{
+    uint4 *d = reinterpret_cast<uint4 *>(p);
+#pragma unroll
+    for (int i = 0; i < 3; i++) d[i] = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+}
+
+__device__ __forceinline__ void fr_set_const(uint32_t (&r)[12], const uint32_t *c)
+{
+#pragma unroll
+    for (int i = 0; i < 12; i++) r[i] = c[i];
+}
+
+// Montgomery -> plain integer (as_bigint, fp.tcc:270-281): multiply by 1.
+__device__ __forceinline__ void fr_from_mont(uint32_t (&r)[12], const uint32_t (&a)[12])
+{
+    uint32_t one[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) one[i] = (i == 0) ? 1u : 0u;
+    fr_mul_regs(r, a, one);
+}
+
+} // namespace zecale

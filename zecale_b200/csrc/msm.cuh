@@ -5,74 +5,97 @@
 // multi_exp_filter_one_zero (:695-757) / kc_multi_exp_with_mixed_addition
 // (libsnark knowledge_commitment/kc_multiexp.tcc:31-113).
 //
-// The reference processes one c-bit window at a time, top-down, on one OpenMP
-// chunk per thread. Here all windows are processed at once:
-//   1. k_digits      scalar -> plain integer (as_bigint) -> signed c-bit digits
-//                    (field_get_signed_digit semantics, field_utils.tcc:81-115),
-//                    histogram of (window, |digit|) with global atomics
-//   2. scan          exclusive prefix sum -> bucket offsets
-//   3. k_scatter     counting sort of (point, sign) into bucket order
-//   4. k_tasks_*     buckets larger than S entries are split into even sub-tasks
-//   5. k_accumulate  one thread per task: serial mixed additions into an XYZZ sum
-//   6. k_reduce1     per (window, segment of L buckets): fold task partials and run
-//                    the running-sum trick (multiexp_accumulate_buckets, :90-125)
-//   7. k_reduce2     per window: combine segments (suffix scan + tree), no serial pass
-//   8. k_final       Horner over windows (c doublings each, multiexp.tcc:612-629),
-//                    normalise to libff special form
+// The reference walks one c-bit window at a time, top-down, on one OpenMP chunk per
+// thread, with c doublings between windows. Here:
+//
+//   * the W signed c-bit windows of all scalars are decomposed at once (k_digits;
+//     field_get_signed_digit semantics, field_utils.tcc:81-115) and counting-sorted by
+//     bucket (histogram atomics -> scan -> k_scatter);
+//   * window w = g*V + v is served by base copy g (the pinned image holds
+//     2^(c*V*g) * P_i for g < G, computed once at pin time) and bucket set v, so only V
+//     bucket sets exist and the final Horner needs c*(V-1) doublings — none when the
+//     proving key is fully expanded (V = 1). An un-pinned call uses G = 1, V = W;
+//   * buckets are cut into tasks of <= S entries, tasks are sorted by length so the 32
+//     lanes of a warp run equally long chains of mixed additions (k_accumulate, one
+//     thread per task, XYZZ accumulator in the Fq VM);
+//   * sum_b (b+1) B_b is a log-depth blocked running sum: each level folds segments of
+//     L buckets with the running-sum trick (multiexp_accumulate_buckets, :90-125) and
+//     carries the per-level weighted sums upwards (k_reduce_level), so the serial chain
+//     is ~2L*log_L(NB) additions instead of 2*NB;
+//   * k_final: Horner over levels and bucket sets, normalise to libff special form.
+//
 // No 0/1 filter is needed: a zero scalar has all-zero digits, a one is an ordinary
-// bucket entry, and base points at infinity are skipped by the mixed addition.
+// bucket entry, and base points at infinity never produce entries.
 #pragma once
 #include <cstdint>
 #include <cstdio>
 
-#include "ec.cuh"
+#include "fqvm.cuh"
 
 namespace zecale {
 
+static constexpr int FR_SCALAR_BITS = 377;
+static constexpr int MSM_MAX_LEVELS = 24;
+static constexpr uint32_t MSM_MAX_TASKS_PER_BUCKET = 256;
+
 struct MsmPlan {
-    uint32_t n;        // points
-    uint32_t c;        // window bits
-    uint32_t W;        // windows
-    uint32_t NB;       // buckets per window = 2^(c-1)
-    uint32_t S;        // max entries per accumulate task
-    uint32_t L;        // buckets per reduce1 segment
-    uint32_t nseg;     // NB / L
-    uint64_t n_buckets;// W * NB
+    uint32_t n;            // (base, scalar) pairs
+    uint32_t c;            // window bits
+    uint32_t W;            // windows = ceil(378 / c)
+    uint32_t V;            // bucket sets
+    uint32_t G;            // base copies used = ceil(W / V)
+    uint32_t NB;           // buckets per set = 2^(c-1)
+    uint32_t S;            // max entries per accumulate task
+    uint32_t copy_stride;  // points per base copy
+    uint32_t n_levels;     // reduction levels
+    uint32_t lbits[MSM_MAX_LEVELS]; // log2 segment length per level
+    uint64_t n_buckets;    // V * NB
     uint64_t max_tasks;
 };
 
-static constexpr int FR_SCALAR_BITS = 377;
-
-inline MsmPlan msm_make_plan(uint32_t n, int force_c = 0)
+inline uint32_t msm_default_c(uint32_t n)
 {
-    MsmPlan p;
-    p.n = n;
     uint32_t lg = 0;
     while ((1ull << (lg + 1)) <= n) lg++;
     int c = (int)lg - 3;
     if (c < 4) c = 4;
     if (c > 16) c = 16;
-    if (force_c) c = force_c;
+    return (uint32_t)c;
+}
+
+// c, V fixed by the caller (pinned image) or defaulted (V = W).
+inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_stride)
+{
+    MsmPlan p{};
+    p.n = n;
     p.c = c;
     p.W = (FR_SCALAR_BITS + 1 + c - 1) / c;
+    p.V = V ? (V > p.W ? p.W : V) : p.W;
+    p.G = (p.W + p.V - 1) / p.V;
     p.NB = 1u << (c - 1);
-    uint32_t avg = (n + p.NB - 1) / p.NB;
-    p.S = avg * 2 < 16 ? 16 : avg * 2;
-    p.L = p.NB >= 16 ? 16 : p.NB;
-    p.nseg = p.NB / p.L;
-    p.n_buckets = (uint64_t)p.W * p.NB;
+    p.copy_stride = copy_stride;
+    uint64_t avg = ((uint64_t)n * p.W + (uint64_t)p.V * p.NB - 1) / ((uint64_t)p.V * p.NB);
+    p.S = (uint32_t)(avg * 2 < 16 ? 16 : avg * 2);
+    p.n_buckets = (uint64_t)p.V * p.NB;
     p.max_tasks = ((uint64_t)n * p.W) / p.S + p.n_buckets + 1;
+    uint32_t rem = c - 1;
+    p.n_levels = 0;
+    while (rem) {
+        uint32_t l = rem >= 2 ? 2 : rem;
+        p.lbits[p.n_levels++] = l;
+        rem -= l;
+    }
     return p;
 }
 
 // ------------------------------------------------------------------ import
-// libff special-form points (stride bytes apart, {X,Y,Z}) -> device affine image.
+// libff special-form points (stride bytes apart, {X,Y,Z}) -> device affine image + flags.
 // status bit0 is raised if a base is neither Z == one nor Z == 0.
-__global__ void k_import_special(const uint8_t *raw, size_t stride, size_t offset, uint32_t n, Affine *out, int *status)
+__global__ void k_import_special(const uint8_t *raw, size_t stride, uint32_t n, Affine *out, uint8_t *is_inf, int *status)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint4 *src = reinterpret_cast<const uint4 *>(raw + (size_t)i * stride + offset);
+    const uint4 *src = reinterpret_cast<const uint4 *>(raw + (size_t)i * stride);
     uint4 z[6];
     uint32_t zor = 0, zne = 0;
 #pragma unroll
@@ -85,22 +108,26 @@ __global__ void k_import_special(const uint8_t *raw, size_t stride, size_t offse
     if (zor == 0) {
 #pragma unroll
         for (int k = 0; k < 12; k++) dst[k] = make_uint4(0, 0, 0, 0);
+        is_inf[i] = 1;
         return;
     }
     if (zne != 0) atomicOr(status, 1);
+    is_inf[i] = 0;
 #pragma unroll
     for (int k = 0; k < 12; k++) dst[k] = src[k];
 }
 
 // ------------------------------------------------------------------ digits
 // One thread per scalar. scalars are Montgomery Fr, `sstride` bytes apart; the scalar of
-// base i is scalars[index ? index[i] : i].
-__global__ void k_digits(const uint8_t *scalars, size_t sstride, const uint64_t *index, MsmPlan p, int32_t *digits, uint32_t *counts)
+// base i is scalars[index ? index[i] : i]. digits[w*n + i] = signed digit of window w.
+__global__ void k_digits(const uint8_t *scalars, size_t sstride, const uint64_t *index, const uint8_t *is_inf, MsmPlan p,
+                         int32_t *digits, uint32_t *counts)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n) return;
     size_t si = index ? (size_t)index[i] : (size_t)i;
-    uint32_t m[12], v[13];
+    uint32_t m[12];
+    __align__(8) uint32_t v[14];
     fr_load(m, reinterpret_cast<const Fr *>(scalars + si * sstride));
     {
         uint32_t t[12];
@@ -108,7 +135,9 @@ __global__ void k_digits(const uint8_t *scalars, size_t sstride, const uint64_t 
 #pragma unroll
         for (int k = 0; k < 12; k++) v[k] = t[k];
         v[12] = 0;
+        v[13] = 0;
     }
+    const bool skip = is_inf[i] != 0;
     const uint32_t c = p.c;
     const uint32_t mask = (1u << c) - 1;
     const uint32_t half = 1u << (c - 1);
@@ -116,8 +145,7 @@ __global__ void k_digits(const uint8_t *scalars, size_t sstride, const uint64_t 
     for (uint32_t w = 0; w < p.W; w++) {
         uint32_t bit = w * c;
         uint32_t lo = bit >> 5, sh = bit & 31;
-        // v is indexed dynamically: keep it in local memory, 13 words
-        uint64_t two = (uint64_t)v[lo] | ((uint64_t)(lo + 1 < 13 ? v[lo + 1] : 0u) << 32);
+        uint64_t two = (uint64_t)v[lo] | ((uint64_t)v[lo + 1] << 32);
         uint32_t d = (uint32_t)(two >> sh) & mask;
         d += carry;
         int32_t sd;
@@ -128,10 +156,11 @@ __global__ void k_digits(const uint8_t *scalars, size_t sstride, const uint64_t 
             sd = (int32_t)d;
             carry = 0;
         }
+        if (skip) sd = 0;
         digits[(size_t)w * p.n + i] = sd;
         if (sd != 0) {
             uint32_t b = (sd < 0 ? (uint32_t)(-sd) : (uint32_t)sd) - 1;
-            atomicAdd(&counts[(size_t)w * p.NB + b], 1u);
+            atomicAdd(&counts[(size_t)(w % p.V) * p.NB + b], 1u);
         }
     }
 }
@@ -147,18 +176,16 @@ __global__ void k_scatter(MsmPlan p, const int32_t *digits, uint32_t *cursor, ui
     if (sd == 0) return;
     uint32_t neg = sd < 0;
     uint32_t b = (neg ? (uint32_t)(-sd) : (uint32_t)sd) - 1;
-    uint32_t pos = atomicAdd(&cursor[(size_t)w * p.NB + b], 1u);
-    entries[pos] = i | (neg << 31);
+    uint32_t pos = atomicAdd(&cursor[(size_t)(w % p.V) * p.NB + b], 1u);
+    entries[pos] = ((w / p.V) * p.copy_stride + i) | (neg << 31);
 }
 
 // ------------------------------------------------------------------ scan (uint32, exclusive)
-// 3-phase: per-block reduce, single-block scan of block sums, per-block scan + offset.
 static constexpr int SCAN_BLOCK = 1024;
 static constexpr int SCAN_ITEMS = 4; // per thread
 
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t *smem, uint32_t &total)
 {
-    // Hillis-Steele in shared memory over blockDim.x (<= 1024) values
     int tid = threadIdx.x;
     smem[tid] = v;
     __syncthreads();
@@ -188,7 +215,6 @@ __global__ void k_scan_reduce(const uint32_t *in, size_t n, uint32_t *block_sums
     if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
 }
 
-// in-place exclusive scan of block_sums (nb <= SCAN_BLOCK*SCAN_ITEMS*... handled by loop)
 __global__ void k_scan_sums(uint32_t *block_sums, size_t nb, uint32_t *grand_total)
 {
     __shared__ uint32_t sm[SCAN_BLOCK];
@@ -234,136 +260,304 @@ inline void exclusive_scan_u32(const uint32_t *in, size_t n, uint32_t *out, uint
 }
 
 // ------------------------------------------------------------------ tasks
+__device__ __forceinline__ uint32_t msm_bucket_tasks(uint32_t cnt, uint32_t S)
+{
+    uint32_t nt = (cnt + S - 1) / S;
+    return nt > MSM_MAX_TASKS_PER_BUCKET ? MSM_MAX_TASKS_PER_BUCKET : nt;
+}
+
 __global__ void k_task_count(MsmPlan p, const uint32_t *counts, uint32_t *ntasks)
 {
     size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= p.n_buckets) return;
-    uint32_t cnt = counts[b];
-    ntasks[b] = (cnt + p.S - 1) / p.S;
+    ntasks[b] = msm_bucket_tasks(counts[b], p.S);
 }
 
-__global__ void k_task_fill(MsmPlan p, const uint32_t *task_off, uint32_t *task_bucket)
+// Task t of bucket b covers entries [start, start+len). size_hist bins tasks by length
+// (capped) for the length sort.
+static constexpr uint32_t MSM_LEN_BINS = 1024;
+__device__ __forceinline__ uint32_t msm_len_bin(uint32_t len) { return len >= MSM_LEN_BINS ? 0u : MSM_LEN_BINS - len; }
+
+__global__ void k_task_fill(MsmPlan p, const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off,
+                            uint32_t *task_start, uint32_t *task_len, uint32_t *len_hist)
 {
     size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= p.n_buckets) return;
-    uint32_t t0 = task_off[b], t1 = task_off[b + 1];
-    for (uint32_t t = t0; t < t1; t++) task_bucket[t] = (uint32_t)b;
+    uint32_t t0 = task_off[b], nt = task_off[b + 1] - t0;
+    uint64_t cnt = counts[b];
+    uint32_t off = offsets[b];
+    for (uint32_t k = 0; k < nt; k++) {
+        uint32_t lo = (uint32_t)((cnt * k) / nt), hi = (uint32_t)((cnt * (k + 1)) / nt);
+        task_start[t0 + k] = off + lo;
+        task_len[t0 + k] = hi - lo;
+        atomicAdd(&len_hist[msm_len_bin(hi - lo)], 1u);
+    }
+}
+
+// order[pos] = task id, longest tasks first.
+__global__ void k_task_order(const uint32_t *task_off_total, const uint32_t *task_len, uint32_t *len_cursor, uint32_t *order)
+{
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *task_off_total) return;
+    uint32_t pos = atomicAdd(&len_cursor[msm_len_bin(task_len[t])], 1u);
+    order[pos] = t;
 }
 
 // ------------------------------------------------------------------ accumulate
-__global__ void __launch_bounds__(128, 4)
-k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *counts, const uint32_t *offsets,
-             const uint32_t *task_off, const uint32_t *task_bucket, const uint32_t *entries, XYZZ *partial)
+// One thread per task: partial[t] = sum of its entries (mixed additions).
+__global__ void __launch_bounds__(128, 2)
+k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint32_t *order, const uint32_t *task_start,
+             const uint32_t *task_len, const uint32_t *entries, XYZZ *partial)
 {
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t T = task_off[p.n_buckets];
-    if (t >= T) return;
-    uint32_t b = task_bucket[t];
-    uint32_t t0 = task_off[b];
-    uint32_t nt = task_off[b + 1] - t0;
-    uint32_t k = t - t0;
-    uint64_t cnt = counts[b];
-    uint32_t lo = offsets[b] + (uint32_t)((cnt * k) / nt);
-    uint32_t hi = offsets[b] + (uint32_t)((cnt * (k + 1)) / nt);
-    XYZZ acc;
-    xyzz_set_inf(acc);
-    for (uint32_t e = lo; e < hi; e++) {
-        uint32_t ent = entries[e];
-        xyzz_madd(acc, bases[ent & 0x7fffffffu], (ent >> 31) != 0);
-    }
-    xyzz_copy(partial[t], acc);
+    uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= *n_tasks) return;
+    const uint32_t t = order[pos];
+    uint32_t e = task_start[t];
+    const uint32_t end = e + task_len[t];
+    FqSlots S;
+    vs_acc_inf(S);
+    auto fetch = [&](uint32_t &pc, FqSlots &S_) -> bool {
+        if (e >= end) {
+            vs_store_acc(partial + t, S_);
+            return false;
+        }
+        uint32_t ent = entries[e++];
+        const Affine *pt = bases + (ent & 0x7fffffffu);
+        vs_set(S_, VS_QX, &pt->x);
+        if (ent >> 31)
+            vs_set_neg(S_, VS_QY, &pt->y);
+        else
+            vs_set(S_, VS_QY, &pt->y);
+        pc = VPC_MADD;
+        return true;
+    };
+    uint32_t pc = 0;
+    if (!fetch(pc, S)) return;
+    fqvm_run(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); });
+}
+
+// Buckets that were cut into several tasks: fold the partials into the first one.
+__global__ void __launch_bounds__(128, 2)
+k_fold(MsmPlan p, const uint32_t *task_off, XYZZ *partial)
+{
+    size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= p.n_buckets) return;
+    const uint32_t t0 = task_off[b], t1 = task_off[b + 1];
+    if (t1 - t0 < 2) return;
+    FqSlots S;
+    vs_load_acc(S, partial + t0);
+    uint32_t t = t0 + 1;
+    vs_load_q(S, partial + t);
+    fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        if (++t >= t1) {
+            vs_store_acc(partial + t0, S_);
+            return false;
+        }
+        vs_load_q(S_, partial + t);
+        pc = VPC_ADD;
+        return true;
+    });
 }
 
 // ------------------------------------------------------------------ reduce
-// One thread per (window, segment of L buckets): bucket value = sum of its task
-// partials; running sum gives seg_sum = sum B_i and seg_acc = sum (i+1) B_i.
-__global__ void __launch_bounds__(128, 4)
-k_reduce1(MsmPlan p, const uint32_t *task_off, const XYZZ *partial, XYZZ *seg_sum, XYZZ *seg_acc)
+// One level of the blocked running sum. Arrays are "item arrays" of XYZZ:
+//   A      : n_in items (per bucket set: n_in_per_set, segments never straddle sets)
+//   C[a]   : k carried arrays of n_in items, stored back to back
+// Thread (a, s), s < n_out = n_in >> l:
+//   a == 0 : running sum over A[s*L .. s*L+L): outA[s] = sum_j A_j, outC[0][s] = sum_j (j + w0) A_j
+//            (w0 = 1 at level 0, where bucket b has weight b+1; 0 above)
+//   a >= 1 : outC[a][s] = plain sum of C[a-1][s*L .. s*L+L)
+// At level 0 the items are bucket values looked up through task_off (empty bucket = infinity).
+struct ReduceLevel {
+    uint32_t l;        // log2 L
+    uint32_t k;        // carried arrays on input
+    uint32_t n_in;     // items per array on input (all sets)
+    uint32_t level0;   // 1: A is addressed through task_off into partial
+};
+
+__global__ void __launch_bounds__(128, 2)
+k_reduce_level(ReduceLevel r, const uint32_t *task_off, const XYZZ *inA, const XYZZ *inC, XYZZ *outA, XYZZ *outC)
 {
-    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; // global segment id = w*nseg + s
-    if (g >= p.W * p.nseg) return;
-    size_t b0 = (size_t)g * p.L;
-    XYZZ run, acc;
-    xyzz_set_inf(run);
-    xyzz_set_inf(acc);
-    for (int i = (int)p.L - 1; i >= 0; i--) {
-        uint32_t t0 = task_off[b0 + i], t1 = task_off[b0 + i + 1];
-        for (uint32_t t = t0; t < t1; t++) xyzz_add(run, partial[t]);
-        xyzz_add(acc, run);
+    const uint32_t n_out = r.n_in >> r.l;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= (r.k + 1) * n_out) return;
+    const uint32_t a = tid / n_out, s = tid - a * n_out;
+    const uint32_t L = 1u << r.l;
+    FqSlots S;
+    if (a == 0) {
+        // running sum, top item first: acc = run, R = weighted sum
+        int j = (int)L - 1;
+        uint32_t phase = 0; // 0: acc += item j ; 1: R += acc
+        vs_acc_inf(S);
+        vs_zero(S, VS_RX);
+        vs_one(S, VS_RY);
+        vs_zero(S, VS_RZZ);
+        vs_zero(S, VS_RZZZ);
+        auto load_item = [&](FqSlots &S_, uint32_t idx) {
+            if (r.level0) {
+                uint32_t t0 = task_off[idx], t1 = task_off[idx + 1];
+                if (t0 == t1) {
+                    vs_zero(S_, VS_QZZ); // infinity: the add program only tests QZZ
+                    return;
+                }
+                vs_load_q(S_, inA + t0);
+            } else {
+                vs_load_q(S_, inA + idx);
+            }
+        };
+        load_item(S, s * L + j);
+        fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+            if (phase == 0) {
+                // acc now holds run_j
+                if (j > 0 || r.level0) {
+                    phase = 1;
+                    pc = VPC_ADD_R;
+                    return true;
+                }
+            }
+            // after R += acc (or skipped): next item
+            phase = 0;
+            if (--j < 0) {
+                vs_store_acc(outA + s, S_);
+                XYZZ *o = outC + s;
+                vs_get(&o->x, S_, VS_RX);
+                vs_get(&o->y, S_, VS_RY);
+                vs_get(&o->zz, S_, VS_RZZ);
+                vs_get(&o->zzz, S_, VS_RZZZ);
+                return false;
+            }
+            load_item(S_, s * L + j);
+            pc = VPC_ADD;
+            return true;
+        });
+    } else {
+        const XYZZ *src = inC + (size_t)(a - 1) * r.n_in + (size_t)s * L;
+        uint32_t j = 1;
+        vs_load_acc(S, src);
+        vs_load_q(S, src + 1);
+        fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+            if (++j >= L) {
+                vs_store_acc(outC + (size_t)a * n_out + s, S_);
+                return false;
+            }
+            vs_load_q(S_, src + j);
+            pc = VPC_ADD;
+            return true;
+        });
     }
-    xyzz_copy(seg_sum[g], run);
-    xyzz_copy(seg_acc[g], acc);
 }
 
-// One block per window. window_sum = sum_s seg_acc[s] + L * sum_s s*seg_sum[s];
-// sum_s s*S_s = sum_{j>=1} suffix_j  (suffix scan, Hillis-Steele, ping-pong in global).
-__global__ void __launch_bounds__(256, 1)
-k_reduce2(MsmPlan p, XYZZ *seg_sum, XYZZ *seg_acc, XYZZ *scratch, XYZZ *window_sum)
-{
-    const uint32_t w = blockIdx.x;
-    const uint32_t ns = p.nseg;
-    XYZZ *A = seg_acc + (size_t)w * ns;
-    XYZZ *Y0 = seg_sum + (size_t)w * ns;
-    XYZZ *Y1 = scratch + (size_t)w * ns;
-    XYZZ tmp;
-    // suffix scan of seg_sum
-    for (uint32_t d = 1; d < ns; d <<= 1) {
-        for (uint32_t i = threadIdx.x; i < ns; i += blockDim.x) {
-            xyzz_copy(tmp, Y0[i]);
-            if (i + d < ns) xyzz_add(tmp, Y0[i + d]);
-            xyzz_copy(Y1[i], tmp);
-        }
-        __syncthreads();
-        XYZZ *t = Y0;
-        Y0 = Y1;
-        Y1 = t;
-    }
-    // Y0[i] = sum_{j>=i} S_j. Drop i = 0 (weight 0) by overwriting it with infinity.
-    if (threadIdx.x == 0) xyzz_set_inf(Y0[0]);
-    __syncthreads();
-    // tree sums of Y0[0..ns) and A[0..ns)
-    for (uint32_t d = 1; d < ns; d <<= 1) {
-        for (uint32_t i = threadIdx.x * 2 * d; i + d < ns; i += blockDim.x * 2 * d) {
-            xyzz_copy(tmp, Y0[i]);
-            xyzz_add(tmp, Y0[i + d]);
-            xyzz_copy(Y0[i], tmp);
-            xyzz_copy(tmp, A[i]);
-            xyzz_add(tmp, A[i + d]);
-            xyzz_copy(A[i], tmp);
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        xyzz_copy(tmp, Y0[0]);
-        for (uint32_t l = 1; l < p.L; l <<= 1) xyzz_dbl(tmp);
-        xyzz_add(tmp, A[0]);
-        xyzz_copy(window_sum[w], tmp);
-    }
-}
-
-// Horner over the windows, top-down, then normalise. One thread.
-__global__ void k_final(MsmPlan p, const XYZZ *window_sum, Proj *out)
+// After the last level every array has V items (one per bucket set). For set v:
+//   R_v = T_0 + L_0 (T_1 + L_1 (T_2 + ...)),  T_i = C[n_levels-1-i][v]
+// result = sum_v 2^(c v) R_v (Horner, top set first), normalised to libff special form
+// (to_special, bw6_761_g1.cpp:58-77). One thread.
+__global__ void __launch_bounds__(32, 1) k_final(MsmPlan p, const XYZZ *C, Proj *out)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    XYZZ r;
-    xyzz_copy(r, window_sum[p.W - 1]);
-    for (int w = (int)p.W - 2; w >= 0; w--) {
-        for (uint32_t k = 0; k < p.c; k++) xyzz_dbl(r);
-        xyzz_add(r, window_sum[w]);
-    }
-    xyzz_to_special(*out, r);
+    FqSlots S;
+    const uint32_t nl = p.n_levels, V = p.V;
+    int v = (int)V - 1;
+    // state machine: for each set v (top first): acc = c doublings of acc (skip for the top set),
+    // then inner Horner into R (kept in ACC via Q adds): we compute R_v in the R slots? Simpler:
+    // keep the overall result in ACC and build R_v by Horner *inside ACC* using linearity:
+    //   result = (((prev * 2^c) + stuff)) -- not linear in that way, so R_v is built in ACC after
+    // saving prev to `out` scratch... Instead: build R_v first in ACC, then add 2^c * prev kept in R:
+    //   R slots hold prev (already multiplied); sequence per set: R = 2^c R (dbl_r x c); ACC = R_v; R += ACC.
+    vs_zero(S, VS_RX);
+    vs_one(S, VS_RY);
+    vs_zero(S, VS_RZZ);
+    vs_zero(S, VS_RZZZ);
+    uint32_t stage = 0;   // 0: doubling R (c times)  1: inner Horner doubling  2: inner add  3: R += ACC  4: normalise
+    uint32_t dbl_left = 0; // doublings left in the current run
+    int lev = 0;           // current level in the inner Horner (from nl-1 down to 0)
+    // kick off: first set needs no doublings of R (R = inf)
+    auto start_set = [&](uint32_t &pc, FqSlots &S_) {
+        // ACC = T_{nl-1} = C[0][v]
+        vs_load_acc(S_, C + (size_t)0 * V + v);
+        lev = (int)nl - 1;
+        // next: multiply by L_{lev-1}... handled by stage 1
+        if (lev == 0) {
+            stage = 3;
+            pc = VPC_ADD_R;
+        } else {
+            stage = 1;
+            dbl_left = p.lbits[lev - 1];
+            pc = VPC_DBL;
+        }
+    };
+    uint32_t pc0 = 0;
+    start_set(pc0, S);
+    fqvm_run(S, pc0, [&](uint32_t id, uint32_t &pc, FqSlots &S_) {
+        if (stage == 4) {
+            // id 1: affine in QX, QY ; id 2: infinity
+            if (id == 2) {
+                uint4 *d = reinterpret_cast<uint4 *>(out);
+                for (int k = 0; k < 18; k++) d[k] = make_uint4(0, 0, 0, 0);
+                vs_one(S_, VS_T0);
+                vs_get(&out->Y, S_, VS_T0);
+            } else {
+                vs_get(&out->X, S_, VS_QX);
+                vs_get(&out->Y, S_, VS_QY);
+                vs_one(S_, VS_T0);
+                vs_get(&out->Z, S_, VS_T0);
+            }
+            return false;
+        }
+        if (stage == 1) { // inner doubling run
+            if (--dbl_left > 0) {
+                pc = VPC_DBL;
+                return true;
+            }
+            // ACC = L_{lev-1} * (...) ; add T_{lev-1} = C[nl-1-(lev-1)][v]
+            lev--;
+            vs_load_q(S_, C + (size_t)(nl - 1 - lev) * V + v);
+            stage = 2;
+            pc = VPC_ADD;
+            return true;
+        }
+        if (stage == 2) {
+            if (lev == 0) {
+                stage = 3;
+                pc = VPC_ADD_R; // R += ACC
+            } else {
+                stage = 1;
+                dbl_left = p.lbits[lev - 1];
+                pc = VPC_DBL;
+            }
+            return true;
+        }
+        if (stage == 3) { // R += R_v done
+            if (--v < 0) {
+                // result = R -> ACC, normalise
+                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_X * 6]), S_, VS_RX);
+                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_Y * 6]), S_, VS_RY);
+                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_ZZ * 6]), S_, VS_RZZ);
+                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_ZZZ * 6]), S_, VS_RZZZ);
+                stage = 4;
+                pc = VPC_TOAFF;
+                return true;
+            }
+            stage = 0;
+            dbl_left = p.c;
+            pc = VPC_DBL_R;
+            return true;
+        }
+        // stage 0: doubling R
+        if (--dbl_left > 0) {
+            pc = VPC_DBL_R;
+            return true;
+        }
+        start_set(pc, S_);
+        return true;
+    });
 }
 
 // ------------------------------------------------------------------ workspace
-struct MsmWorkspace {
-    void *buf = nullptr;
-    size_t cap = 0;
-};
-
 struct MsmBuffers {
     int32_t *digits;
-    uint32_t *counts, *offsets, *cursor, *ntasks, *task_off, *task_bucket, *entries, *scan_tmp;
-    XYZZ *partial, *seg_sum, *seg_acc, *scratch, *window_sum;
+    uint32_t *counts, *offsets, *cursor, *ntasks, *task_off, *task_start, *task_len, *order, *len_hist, *len_cursor,
+        *entries, *scan_tmp;
+    XYZZ *partial, *lvlA[2], *lvlC[2];
     Proj *result;
     size_t total;
 };
@@ -387,28 +581,43 @@ inline MsmBuffers msm_layout(const MsmPlan &p, uint8_t *base)
     b.cursor = (uint32_t *)take((nbk + 1) * 4);
     b.ntasks = (uint32_t *)take((nbk + 1) * 4);
     b.task_off = (uint32_t *)take((nbk + 1) * 4);
-    b.task_bucket = (uint32_t *)take(p.max_tasks * 4);
+    b.task_start = (uint32_t *)take(p.max_tasks * 4);
+    b.task_len = (uint32_t *)take(p.max_tasks * 4);
+    b.order = (uint32_t *)take(p.max_tasks * 4);
+    b.len_hist = (uint32_t *)take((MSM_LEN_BINS + 2) * 4);
+    b.len_cursor = (uint32_t *)take((MSM_LEN_BINS + 2) * 4);
     b.entries = (uint32_t *)take(nd * 4);
     b.scan_tmp = (uint32_t *)take((nbk / (SCAN_BLOCK * SCAN_ITEMS) + 2) * 4);
     b.partial = (XYZZ *)take(p.max_tasks * sizeof(XYZZ));
-    size_t nsegs = (size_t)p.W * p.nseg;
-    b.seg_sum = (XYZZ *)take(nsegs * sizeof(XYZZ));
-    b.seg_acc = (XYZZ *)take(nsegs * sizeof(XYZZ));
-    b.scratch = (XYZZ *)take(nsegs * sizeof(XYZZ));
-    b.window_sum = (XYZZ *)take((size_t)p.W * sizeof(XYZZ));
+    // level arrays: after level 0 there are n_buckets >> l0 items per array and up to n_levels arrays
+    size_t n1 = nbk >> p.lbits[0];
+    size_t carry_items = 0, items = n1;
+    for (uint32_t k = 0; k < p.n_levels; k++) {
+        size_t need = (size_t)(k + 1) * items;
+        if (need > carry_items) carry_items = need;
+        if (k + 1 < p.n_levels) items >>= p.lbits[k + 1];
+    }
+    for (int i = 0; i < 2; i++) {
+        b.lvlA[i] = (XYZZ *)take(n1 * sizeof(XYZZ));
+        b.lvlC[i] = (XYZZ *)take(carry_items * sizeof(XYZZ));
+    }
     b.result = (Proj *)take(sizeof(Proj));
     b.total = off;
     return b;
 }
 
-// Launch the whole MSM on `st`. d_bases: affine image; d_scalars: Fr Montgomery.
-// Result (libff special form, 288 B) is left in buffers.result on the device.
-inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affine *d_bases, const uint8_t *d_scalars,
-                              size_t sstride, const uint64_t *d_index, cudaStream_t st)
+// Number of kernel launches msm_launch issues for plan p.
+inline uint64_t msm_launch_count(const MsmPlan &p) { return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 1 + p.n_levels + 1; }
+
+// Launch the whole MSM on `st`. d_bases: affine image (G copies of copy_stride points);
+// d_scalars: Fr Montgomery. Result (libff special form, 288 B) is left in buffers.result.
+inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affine *d_bases, const uint8_t *d_is_inf,
+                              const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, cudaStream_t st)
 {
     const uint32_t n = p.n;
     cudaMemsetAsync(b.counts, 0, (p.n_buckets + 1) * 4, st);
-    k_digits<<<(n + 127) / 128, 128, 0, st>>>(d_scalars, sstride, d_index, p, b.digits, b.counts);
+    cudaMemsetAsync(b.len_hist, 0, (MSM_LEN_BINS + 2) * 4, st);
+    k_digits<<<(n + 127) / 128, 128, 0, st>>>(d_scalars, sstride, d_index, d_is_inf, p, b.digits, b.counts);
     exclusive_scan_u32(b.counts, p.n_buckets, b.offsets, b.scan_tmp, st);
     cudaMemcpyAsync(b.cursor, b.offsets, (p.n_buckets + 1) * 4, cudaMemcpyDeviceToDevice, st);
     size_t nd = (size_t)n * p.W;
@@ -416,13 +625,30 @@ inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affin
     unsigned gb = (unsigned)((p.n_buckets + 255) / 256);
     k_task_count<<<gb, 256, 0, st>>>(p, b.counts, b.ntasks);
     exclusive_scan_u32(b.ntasks, p.n_buckets, b.task_off, b.scan_tmp, st);
-    k_task_fill<<<gb, 256, 0, st>>>(p, b.task_off, b.task_bucket);
-    k_accumulate<<<(unsigned)((p.max_tasks + 127) / 128), 128, 0, st>>>(p, d_bases, b.counts, b.offsets, b.task_off,
-                                                                         b.task_bucket, b.entries, b.partial);
-    uint32_t nsegs = p.W * p.nseg;
-    k_reduce1<<<(nsegs + 127) / 128, 128, 0, st>>>(p, b.task_off, b.partial, b.seg_sum, b.seg_acc);
-    k_reduce2<<<p.W, 256, 0, st>>>(p, b.seg_sum, b.seg_acc, b.scratch, b.window_sum);
-    k_final<<<1, 32, 0, st>>>(p, b.window_sum, b.result);
+    k_task_fill<<<gb, 256, 0, st>>>(p, b.counts, b.offsets, b.task_off, b.task_start, b.task_len, b.len_hist);
+    exclusive_scan_u32(b.len_hist, MSM_LEN_BINS + 1, b.len_cursor, b.scan_tmp, st);
+    const uint32_t *n_tasks = b.task_off + p.n_buckets;
+    k_task_order<<<(unsigned)((p.max_tasks + 255) / 256), 256, 0, st>>>(n_tasks, b.task_len, b.len_cursor, b.order);
+    k_accumulate<<<(unsigned)((p.max_tasks + 127) / 128), 128, 0, st>>>(p, d_bases, n_tasks, b.order, b.task_start,
+                                                                         b.task_len, b.entries, b.partial);
+    k_fold<<<(unsigned)((p.n_buckets + 127) / 128), 128, 0, st>>>(p, b.task_off, b.partial);
+    // reduction levels
+    ReduceLevel r{};
+    r.n_in = (uint32_t)p.n_buckets;
+    const XYZZ *inA = b.partial, *inC = nullptr;
+    for (uint32_t k = 0; k < p.n_levels; k++) {
+        r.l = p.lbits[k];
+        r.k = k;
+        r.level0 = k == 0;
+        XYZZ *outA = b.lvlA[k & 1], *outC = b.lvlC[k & 1];
+        uint32_t n_out = r.n_in >> r.l;
+        uint32_t threads = (k + 1) * n_out;
+        k_reduce_level<<<(threads + 127) / 128, 128, 0, st>>>(r, b.task_off, inA, inC, outA, outC);
+        inA = outA;
+        inC = outC;
+        r.n_in = n_out;
+    }
+    k_final<<<1, 32, 0, st>>>(p, inC, b.result);
     return cudaGetLastError();
 }
 

@@ -24,7 +24,7 @@
 #include <utility>
 #include <vector>
 
-#include "field.cuh"
+#include "fqvm.cuh"
 
 namespace zecale {
 
@@ -38,7 +38,7 @@ __device__ __forceinline__ void fr_neg_regs(uint32_t (&r)[12], const uint32_t (&
 }
 
 // r = a^e for a 64-bit exponent (square and multiply, MSB first).
-__device__ __noinline__ void fr_pow_u64(uint32_t (&r)[12], const uint32_t (&a)[12], uint64_t e)
+__device__ __forceinline__ void fr_pow_u64(uint32_t (&r)[12], const uint32_t (&a)[12], uint64_t e)
 {
     uint32_t acc[12];
     fr_set_const(acc, FR_ONE);
@@ -51,7 +51,7 @@ __device__ __noinline__ void fr_pow_u64(uint32_t (&r)[12], const uint32_t (&a)[1
 }
 
 // r = a^(r-2) (Fermat inverse); 0 -> 0.
-__device__ __noinline__ void fr_inv(uint32_t (&r)[12], const uint32_t (&a)[12])
+__device__ __forceinline__ void fr_inv(uint32_t (&r)[12], const uint32_t (&a)[12])
 {
     uint32_t acc[12];
     fr_set_const(acc, FR_ONE);

@@ -9,7 +9,6 @@
 #include <vector>
 
 #include "../../include/zecale_gpu.h"
-#include "ec.cuh"
 #include "msm.cuh"
 #include "ntt.cuh"
 
@@ -21,9 +20,11 @@ struct DevBuf {
 };
 
 struct zecale_gpu_bases {
-    Affine *d = nullptr;
+    Affine *d = nullptr;      // G copies of n points: copy g holds 2^(c*V*g) * P_i
+    uint8_t *is_inf = nullptr; // n flags
     size_t n = 0;
     int group = 0;
+    uint32_t c = 0, V = 0;    // window bits / bucket sets the image was expanded for (V = 0: not expanded)
 };
 
 struct zecale_gpu_ctx {
@@ -72,10 +73,7 @@ int reserve(zecale_gpu_ctx *ctx, DevBuf &b, size_t bytes)
     return 0;
 }
 
-// Number of kernel launches of one MSM / NTT (kept next to the launch sequences).
-uint64_t msm_launches() { return 3 + 3 + 1 + 1 + 1 + 1 + 1 + 1 + 1; }
-
-int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n, Affine *d_out)
+int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n, Affine *d_out, uint8_t *d_inf)
 {
     // stage the raw libff array on the device, then convert (coalesced 16 B accesses)
     size_t raw = (n - 1) * stride + sizeof(Proj);
@@ -83,8 +81,8 @@ int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n
     if (rc) return rc;
     CK(cudaMemcpyAsync(ctx->ws_in.p, bases, raw, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->stream));
-    k_import_special<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>((const uint8_t *)ctx->ws_in.p, stride, 0,
-                                                                            (uint32_t)n, d_out, ctx->d_status);
+    k_import_special<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>((const uint8_t *)ctx->ws_in.p, stride,
+                                                                            (uint32_t)n, d_out, d_inf, ctx->d_status);
     ctx->launches++;
     int st = 0;
     CK(cudaMemcpyAsync(&st, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
@@ -94,8 +92,9 @@ int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n
 }
 
 // d_bases: affine image on device; scalars: device pointer. Result -> host out (288 B).
-int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_scalars, size_t sstride,
-               const uint64_t *d_index, size_t n, void *out_point, float *elapsed_ms)
+int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf, uint32_t c, uint32_t V,
+               uint32_t copy_stride, const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, size_t n,
+               void *out_point, float *elapsed_ms)
 {
     if (n == 0) {
         // empty sum = zero point (0, one, 0), as libff::multi_exp returns GroupT::zero()
@@ -108,14 +107,14 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_scal
         if (elapsed_ms) *elapsed_ms = 0.f;
         return 0;
     }
-    MsmPlan plan = msm_make_plan((uint32_t)n);
+    MsmPlan plan = msm_make_plan((uint32_t)n, c ? c : msm_default_c((uint32_t)n), V, copy_stride);
     MsmBuffers lay = msm_layout(plan, nullptr);
     int rc = reserve(ctx, ctx->ws_msm, lay.total);
     if (rc) return rc;
     MsmBuffers b = msm_layout(plan, (uint8_t *)ctx->ws_msm.p);
     if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    CK(msm_launch(plan, b, d_bases, d_scalars, sstride, d_index, ctx->stream));
-    ctx->launches += msm_launches();
+    CK(msm_launch(plan, b, d_bases, d_inf, d_scalars, sstride, d_index, ctx->stream));
+    ctx->launches += msm_launch_count(plan);
     if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
     CK(cudaMemcpyAsync(out_point, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -155,46 +154,63 @@ int msm_host(zecale_gpu_ctx *ctx, const void *bases, size_t bstride, const void 
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
-    if (!out || (n && (!bases || !scalars)) || bstride < sizeof(Proj) || sstride < sizeof(Fr) || n >= (1ull << 31))
+    if (!out || (n && (!bases || !scalars)) || bstride < sizeof(Proj) || sstride < sizeof(Fr) || n >= (1ull << 26))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm: bad argument");
     CK(cudaSetDevice(ctx->device));
-    if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, nullptr, 0, out, nullptr);
-    int rc = reserve(ctx, ctx->ws_tmp, n * sizeof(Affine));
+    if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, 0, 0, nullptr, 0, nullptr, 0, out, nullptr);
+    int rc = reserve(ctx, ctx->ws_tmp, n * sizeof(Affine) + n);
     if (rc) return rc;
-    rc = import_bases(ctx, bases, bstride, n, (Affine *)ctx->ws_tmp.p);
+    Affine *d_aff = (Affine *)ctx->ws_tmp.p;
+    uint8_t *d_inf = (uint8_t *)(d_aff + n);
+    rc = import_bases(ctx, bases, bstride, n, d_aff, d_inf);
     if (rc) return rc;
     const uint8_t *d_sc;
     const uint64_t *d_idx;
     rc = upload_scalars(ctx, scalars, sstride, index, n, &d_sc, &d_idx);
     if (rc) return rc;
-    return msm_device(ctx, (const Affine *)ctx->ws_tmp.p, d_sc, sstride, d_idx, n, out, nullptr);
+    return msm_device(ctx, d_aff, d_inf, 0, 0, (uint32_t)n, d_sc, sstride, d_idx, n, out, nullptr);
 }
 
 // ------------------------------------------------------------------ test kernels
-__global__ void k_test_fq(int op, const Fq *a, const Fq *b, Fq *out, size_t n)
+__global__ void __launch_bounds__(64, 1) k_test_fq(int op, const Fq *a, const Fq *b, Fq *out, size_t n)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Fq x, y, r;
-    fq_copy(x, a[i]);
-    if (b) fq_copy(y, b[i]);
+    FqSlots S;
+    vs_set(S, VS_QX, a + i);
+    vs_set(S, VS_QY, b ? b + i : a + i);
+    if (op == 4) { // inverse through the VM's Fermat loop; 0 -> 0
+        vs_set(S, VS_T2, a + i);
+        fqvm_run(S, VPC_INVPROD, [&](uint32_t, uint32_t &, FqSlots &) { return false; });
+        vs_get(out + i, S, VS_T0);
+        return;
+    }
+    uint32_t x[24], y[24], r[24];
+    vs_load(x, S, VS_QX);
+    vs_load(y, S, VS_QY);
     switch (op) {
-    case 0: fq_add(r, x, y); break;
-    case 1: fq_sub(r, x, y); break;
-    case 2: fq_mul(r, x, y); break;
-    case 3: fq_sqr(r, x); break;
-    case 4: fq_inv(r, x); break;
-    case 5: fq_neg(r, x); break;
-    case 6: {
-        Fq one;
-        fq_set_zero(one);
-        one.l[0] = 1;
-        fq_mul(r, x, one);
+    case 0: fq_add_regs(r, x, y); break;
+    case 1: fq_sub_regs(r, x, y); break;
+    case 2: fq_mul_regs(r, x, y); break;
+    case 3: fq_sqr_regs(r, x); break;
+    case 5: {
+#pragma unroll
+        for (int k = 0; k < 24; k++) y[k] = 0;
+        fq_sub_regs(r, y, x);
         break;
     }
-    default: fq_set_zero(r);
+    case 6: {
+#pragma unroll
+        for (int k = 0; k < 24; k++) y[k] = k == 0 ? 1u : 0u;
+        fq_mul_regs(r, x, y);
+        break;
     }
-    fq_copy(out[i], r);
+    default:
+#pragma unroll
+        for (int k = 0; k < 24; k++) r[k] = 0;
+    }
+    vs_store(S, VS_T0, r);
+    vs_get(out + i, S, VS_T0);
 }
 
 __global__ void k_test_fr(int op, const Fr *a, const Fr *b, Fr *out, size_t n)
@@ -228,50 +244,90 @@ __global__ void k_test_fr(int op, const Fr *a, const Fr *b, Fr *out, size_t n)
     fr_store(out + i, r);
 }
 
-__global__ void k_test_group(int op, const Proj *a, const Proj *b, Proj *out, size_t n)
+// acc = a[i] (any projective), then op with b[i], result normalised to special form.
+__global__ void __launch_bounds__(64, 1) k_test_group(int op, const Proj *a, const Proj *b, Proj *out, size_t n)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    XYZZ acc;
-    xyzz_from_proj(acc, a[i]);
-    switch (op) {
-    case 0: {
-        XYZZ o;
-        xyzz_from_proj(o, b[i]);
-        xyzz_add(acc, o);
-        break;
-    }
-    case 1: {
-        Affine q; // b[i] is special: Z in {one, 0}
-        if (fq_is_zero(b[i].Z)) {
-            fq_set_zero(q.x);
-            fq_set_zero(q.y);
-        } else {
-            fq_copy(q.x, b[i].X);
-            fq_copy(q.y, b[i].Y);
+    FqSlots S;
+    auto load_proj = [&](const Proj *p) {
+        vs_set(S, VS_QX, &p->X);
+        vs_set(S, VS_QY, &p->Y);
+        vs_set(S, VS_QZZ, &p->Z);
+    };
+    load_proj(a + i);
+    uint32_t stage = 0;
+    fqvm_run(S, VPC_FROMPROJ, [&](uint32_t id, uint32_t &pc, FqSlots &S_) {
+        switch (stage++) {
+        case 0: pc = VPC_MOVQA; return true;       // acc = a
+        case 1:
+            if (op == 2) {
+                pc = VPC_DBL;
+                stage = 3;
+                return true;
+            }
+            if (op == 3) {
+                pc = VPC_TOAFF;
+                stage = 4;
+                return true;
+            }
+            load_proj(b + i);
+            if (op == 1) { // mixed: b is special (Z = one or 0); infinity is filtered by the callers of madd
+                if (vs_is_zero(S_, VS_QZZ)) {
+                    pc = VPC_TOAFF;
+                    stage = 4;
+                } else {
+                    pc = VPC_MADD;
+                    stage = 3;
+                }
+                return true;
+            }
+            pc = VPC_FROMPROJ;
+            return true;
+        case 2: pc = VPC_ADD; return true;
+        case 3: pc = VPC_TOAFF; return true;
+        default: break;
         }
-        xyzz_madd(acc, q, false);
-        break;
-    }
-    case 2: xyzz_dbl(acc); break;
-    default: break;
-    }
-    xyzz_to_special(out[i], acc);
+        Proj *o = out + i;
+        if (id == 2) {
+            vs_zero(S_, VS_T0);
+            vs_get(&o->X, S_, VS_T0);
+            vs_get(&o->Z, S_, VS_T0);
+            vs_one(S_, VS_T0);
+            vs_get(&o->Y, S_, VS_T0);
+        } else {
+            vs_get(&o->X, S_, VS_QX);
+            vs_get(&o->Y, S_, VS_QY);
+            vs_one(S_, VS_T0);
+            vs_get(&o->Z, S_, VS_T0);
+        }
+        return false;
+    });
 }
 
-__global__ void __launch_bounds__(128, 4) k_bench_fq_mul(Fq *sink, unsigned iters)
+// `iters` dependent Montgomery products per thread through the VM (local-memory operands,
+// same code path as the MSM kernels).
+__global__ void __launch_bounds__(128, 2) k_bench_fq_mul(Fq *sink, unsigned iters)
 {
-    Fq x, y;
+    FqSlots S;
     unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x[24], y[24];
 #pragma unroll
     for (int i = 0; i < 24; i++) {
-        x.l[i] = FQ_R2[i] ^ (t * 2654435761u >> (i & 7));
-        y.l[i] = FQ_ONE[i] + t;
+        x[i] = FQ_R2[i] ^ (t * 2654435761u >> (i & 7));
+        y[i] = FQ_ONE[i] + t;
     }
-    x.l[23] &= 0xffffff;
-    y.l[23] &= 0xffffff;
-    for (unsigned k = 0; k < iters; k++) fq_mul(x, x, y);
-    if (x.l[0] == 0x12345678u && x.l[5] == 77u) fq_copy(sink[0], x); // keep the chain alive
+    x[23] &= 0xffffff;
+    y[23] &= 0xffffff;
+    vs_store(S, VS_ZZZ, x);
+    vs_store(S, VS_T2, y);
+    unsigned k = 0;
+    fqvm_run(S, VPC_PRODSTEP, [&](uint32_t, uint32_t &pc, FqSlots &) {
+        pc = VPC_PRODSTEP;
+        return ++k < iters;
+    });
+    vs_load(x, S, VS_T2);
+    if (x[0] == 0x12345678u && x[5] == 77u) vs_get(sink, S, VS_T2); // keep the chain alive
 }
 
 template <typename T>
@@ -342,8 +398,6 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
         delete ctx;
         return ZECALE_GPU_E_CUDA;
     }
-    // deep call chains (fq_inv -> fq_mul) with ~1.5 KB frames
-    cudaDeviceSetLimit(cudaLimitStackSize, 8192);
     *out = ctx;
     return 0;
 }
@@ -371,7 +425,7 @@ int zecale_gpu_msm_g1(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride
     return msm_host(ctx, bases, base_stride, scalars, scalar_stride, scalar_index, n, out_point);
 }
 
-// G2 lives over the same Fq with a = 0: identical arithmetic (ec.cuh header comment).
+// G2 lives over the same Fq with a = 0: identical arithmetic (tools/gen_fqvm_prog.py docstring).
 int zecale_gpu_msm_g2(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, const void *scalars,
                       size_t scalar_stride, const size_t *scalar_index, size_t n, void *out_point)
 {
@@ -383,7 +437,7 @@ int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_str
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
-    if (!bases || !handle || !n || base_stride < sizeof(Proj) || n >= (1ull << 31) ||
+    if (!bases || !handle || !n || base_stride < sizeof(Proj) || n >= (1ull << 26) ||
         (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_pin_bases: bad argument");
     CK(cudaSetDevice(ctx->device));
@@ -391,13 +445,16 @@ int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_str
     h->n = n;
     h->group = group;
     cudaError_t e = cudaMalloc((void **)&h->d, n * sizeof(Affine));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&h->is_inf, n);
     if (e != cudaSuccess) {
+        cudaFree(h->d);
         delete h;
         return fail(ctx, ZECALE_GPU_E_NOMEM, "pin_bases: %s", cudaGetErrorString(e));
     }
-    int rc = import_bases(ctx, bases, base_stride, n, h->d);
+    int rc = import_bases(ctx, bases, base_stride, n, h->d, h->is_inf);
     if (rc) {
         cudaFree(h->d);
+        cudaFree(h->is_inf);
         delete h;
         return rc;
     }
@@ -412,6 +469,7 @@ int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *h)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaFree(h->d);
+    cudaFree(h->is_inf);
     delete h;
     return 0;
 }
@@ -424,12 +482,13 @@ int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, const 
     if (!h || !out_point || n > h->n || (n && !scalars) || scalar_stride < sizeof(Fr))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned: bad argument");
     CK(cudaSetDevice(ctx->device));
-    if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, nullptr, 0, out_point, nullptr);
+    if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, 0, 0, nullptr, 0, nullptr, 0, out_point, nullptr);
     const uint8_t *d_sc;
     const uint64_t *d_idx;
     int rc = upload_scalars(ctx, scalars, scalar_stride, scalar_index, n, &d_sc, &d_idx);
     if (rc) return rc;
-    return msm_device(ctx, h->d, d_sc, scalar_stride, d_idx, n, out_point, nullptr);
+    return msm_device(ctx, h->d, h->is_inf, h->c, h->V, (uint32_t)h->n, d_sc, scalar_stride, d_idx, n, out_point,
+                      nullptr);
 }
 
 int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, const void *d_scalars,
@@ -441,7 +500,8 @@ int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, co
     if (!h || !out_point || n > h->n || (n && !d_scalars) || scalar_stride < sizeof(Fr))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: bad argument");
     CK(cudaSetDevice(ctx->device));
-    return msm_device(ctx, h->d, (const uint8_t *)d_scalars, scalar_stride, d_scalar_index, n, out_point, elapsed_ms);
+    return msm_device(ctx, h->d, h->is_inf, h->c, h->V, (uint32_t)h->n, (const uint8_t *)d_scalars, scalar_stride,
+                      d_scalar_index, n, out_point, elapsed_ms);
 }
 
 int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned flags, const void *coset_g,
@@ -491,7 +551,7 @@ int zecale_gpu_ntt(zecale_gpu_ctx *ctx, void *a, unsigned log_m, unsigned flags,
 
 uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
-unsigned zecale_gpu_msm_window_bits(size_t n) { return n ? msm_make_plan((uint32_t)n).c : 0; }
+unsigned zecale_gpu_msm_window_bits(size_t n) { return n ? msm_default_c((uint32_t)n) : 0; }
 
 int zecale_gpu_test_fq(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n)
 {
@@ -510,7 +570,7 @@ int zecale_gpu_bench_fq_mul(zecale_gpu_ctx *ctx, unsigned blocks, unsigned tpb, 
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
-    if (!blocks || !tpb || tpb > 128 || !elapsed_ms) return fail(ctx, ZECALE_GPU_E_ARG, "bench_fq_mul: bad argument");
+    if (!blocks || !tpb || tpb > 128 || !elapsed_ms || !iters) return fail(ctx, ZECALE_GPU_E_ARG, "bench_fq_mul: bad argument");
     CK(cudaSetDevice(ctx->device));
     int rc = reserve(ctx, ctx->ws_tmp, sizeof(Fq));
     if (rc) return rc;
