@@ -1,0 +1,462 @@
+#!/usr/bin/env python3
+"""bench.py — BW6-761 Groth16 aggregator prove hot path at batch 8 (BASELINE.json metric).
+
+One "step" = the device work of ONE batch-8 aggregator proof as the hooked reference
+prover would issue it (libsnark r1cs_gg_ppzksnark_prover, r1cs_gg_ppzksnark.tcc:464-603):
+    H polynomial  : 3 x (iFFT, cosetFFT) + pointwise + icosetFFT over Fr, m = 2^18
+    MSM A  (G1)   : 237 801 bases x witness
+    MSM B  (G2,G1): 87 966 sparse pairs x witness[indices]
+    MSM H  (G1)   : 262 143 bases x coefficients_for_H
+    MSM L  (G1)   : 237 790 bases x witness[11:]
+with the sizes of the real batch-8 circuit (SURVEY.md §8 [probe]); bases are synthetic
+distinct curve points (k_i * generator), the witness an aggregator-like mix, all seeded.
+
+    value : proofs/s, inputs resident in HBM, timed with CUDA events (max over ranks)
+    e2e   : proofs/s through the host-pointer C ABI (pinned host buffers, H2D/D2H inside)
+    --impl reference : the reference's own libff/libfqfft code (oracle/_ref) on the host cores
+
+N > 1: one process per GPU, each proving its own stream of proofs (replicas; no data-path
+collective) -> weak scaling, value = N * proofs / max-over-ranks time.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+# batch-8 aggregator circuit (SURVEY.md §0 / §8 [probe])
+LOG_M = 18
+N_VARS = 237800          # assignment has N_VARS + 1 entries (constant one first)
+N_INPUTS = 10
+N_A = N_VARS + 1
+N_B = 87966              # non-zero entries of pk.B_query
+N_H = (1 << LOG_M) - 1
+N_L = N_VARS - N_INPUTS
+METRIC = "bw6_761_groth16_batch8_proofs_per_s"
+UNIT = "proofs/s"
+FR_TOP = 0x01AE3A4617C510EA  # top 64-bit limb of r: a random value with a smaller top limb is < r
+PRODUCTS_PER_FQ_MUL = 1176   # 24*24 (a*b) + 24*24 (m*q) + 24 (m) 32x32 products, SURVEY.md §8(d)
+FQ_MUL_PER_MADD = 10         # madd-2008-s: 8M + 2S, every S done as M
+
+
+def random_fr(rng, n):
+    a = rng.integers(0, 1 << 63, size=(n, 6), dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=(n, 6), dtype=np.uint64)
+    a[:, 5] = rng.integers(0, FR_TOP, size=n, dtype=np.uint64)
+    return a
+
+
+def witness_like(rng, n):
+    """Aggregator-like assignment in Montgomery form: 1 % zeros, 0.02 % ones, 20 % values
+    below 2^16, the rest uniform (SURVEY.md §8(d) filter statistics)."""
+    import bw6_constants as C
+    w = random_fr(rng, n)
+    kind = rng.random(n)
+    Rm = (1 << C.FR_RBITS) % C.R
+    small = np.nonzero(kind < 0.20)[0]
+    vals = rng.integers(2, 1 << 16, size=small.shape[0])
+    for i, v in zip(small.tolist(), vals.tolist()):
+        x = v * Rm % C.R
+        for k in range(6):
+            w[i, k] = (x >> (64 * k)) & 0xFFFFFFFFFFFFFFFF
+    w[(kind >= 0.20) & (kind < 0.21)] = 0
+    one = [(Rm >> (64 * k)) & 0xFFFFFFFFFFFFFFFF for k in range(6)]
+    w[(kind >= 0.21) & (kind < 0.2102)] = np.array(one, dtype=np.uint64)
+    w[0] = np.array(one, dtype=np.uint64)
+    return w
+
+
+def fr_generator():
+    import bw6_constants as C
+    x = C.FR_GENERATOR * ((1 << C.FR_RBITS) % C.R) % C.R
+    return np.array([(x >> (64 * k)) & 0xFFFFFFFFFFFFFFFF for k in range(6)], dtype=np.uint64)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+class Workload:
+    """Synthetic batch-8 proving key image + witness, on one GPU."""
+
+    def __init__(self, device, seed=1):
+        import torch
+        import zecale_b200 as z
+        self.torch, self.z = torch, z
+        self.dev = device
+        torch.cuda.set_device(device)
+        self.ctx = z.Context(device)
+        rng = np.random.default_rng(seed)
+        ctx = self.ctx
+        # proving-key queries: distinct curve points, pinned (device-resident) once, like a loaded pk
+        self.pk = {}
+        for name, n, grp, sd in (("A", N_A, z.G1, 11), ("B1", N_B, z.G1, 12), ("B2", N_B, z.G2, 13),
+                                 ("H", N_H, z.G1, 14), ("L", N_L, z.G1, 15)):
+            pts = ctx.synth_bases(n, grp, seed=sd + 100 * seed)
+            self.pk[name] = ctx.pin_bases(pts, grp)
+            del pts
+        self.b_index = np.sort(rng.choice(N_A, N_B, replace=False)).astype(np.uint64)
+        self.g = fr_generator()
+        # host inputs (pinned) of one proof
+        def pinned(a):
+            t = torch.from_numpy(a.view(np.int64)).pin_memory()
+            return t, t.numpy().view(np.uint64)
+        m = 1 << LOG_M
+        self.t_w, self.h_w = pinned(witness_like(rng, N_A))
+        self.t_abc, self.h_abc = [], []
+        for _ in range(3):
+            t, h = pinned(random_fr(rng, m))
+            self.t_abc.append(t)
+            self.h_abc.append(h)
+        # device-resident copies
+        self.d_w = self.t_w.cuda()
+        self.d_abc0 = [t.cuda() for t in self.t_abc]
+        self.d_abc = [torch.empty_like(t) for t in self.d_abc0]
+        self.d_idx = torch.from_numpy(self.b_index.view(np.int64)).cuda()
+        torch.cuda.synchronize()
+        self.last = None
+
+    def step_resident(self):
+        """One proof's device work with every input already in HBM."""
+        ctx = self.ctx
+        for dst, src in zip(self.d_abc, self.d_abc0):
+            dst.copy_(src)
+        self.torch.cuda.current_stream().synchronize()
+        ctx.qap_h_dev(self.d_abc[0].data_ptr(), self.d_abc[1].data_ptr(), self.d_abc[2].data_ptr(), LOG_M, self.g)
+        w = self.d_w.data_ptr()
+        out = [ctx.msm_pinned_dev(self.pk["A"], w, N_A)[0],
+               ctx.msm_pinned_dev(self.pk["B2"], w, N_B, d_index_ptr=self.d_idx.data_ptr())[0],
+               ctx.msm_pinned_dev(self.pk["B1"], w, N_B, d_index_ptr=self.d_idx.data_ptr())[0],
+               ctx.msm_pinned_dev(self.pk["H"], self.d_abc[0].data_ptr(), N_H)[0],
+               ctx.msm_pinned_dev(self.pk["L"], w + 48 * (N_INPUTS + 1), N_L)[0]]
+        self.last = out
+        return out
+
+    def step_e2e(self):
+        """The same proof through the host-pointer C ABI (what the hooked reference calls)."""
+        ctx = self.ctx
+        h = ctx.qap_h(self.h_abc[0], self.h_abc[1], self.h_abc[2], self.g)
+        w = self.h_w
+        out = [ctx.msm_pinned(self.pk["A"], w, n=N_A),
+               ctx.msm_pinned(self.pk["B2"], w, index=self.b_index, n=N_B),
+               ctx.msm_pinned(self.pk["B1"], w, index=self.b_index, n=N_B),
+               ctx.msm_pinned(self.pk["H"], h, n=N_H),
+               ctx.msm_pinned(self.pk["L"], w[N_INPUTS + 1:], n=N_L)]
+        return out
+
+    E2E_H2D = 3 * (1 << LOG_M) * 48 + 4 * N_A * 48 + N_H * 48 + 2 * N_B * 8
+    E2E_D2H = ((1 << LOG_M)) * 48 + 5 * 288
+
+    def algorithmic_madds(self):
+        """Mixed additions one step's five bucket-accumulation launches execute: bucket entries
+        (non-zero signed digits of points that are not at infinity) minus accumulate tasks (the
+        first entry of a task is a copy), read back from the library after an untimed step."""
+        ctx = self.ctx
+        w = self.d_w.data_ptr()
+        for dst, src in zip(self.d_abc, self.d_abc0):
+            dst.copy_(src)
+        self.torch.cuda.current_stream().synchronize()
+        ctx.qap_h_dev(self.d_abc[0].data_ptr(), self.d_abc[1].data_ptr(), self.d_abc[2].data_ptr(), LOG_M, self.g)
+        tot, shapes = 0, {}
+        calls = (("A", w, N_A, None), ("B2", w, N_B, self.d_idx.data_ptr()), ("B1", w, N_B, self.d_idx.data_ptr()),
+                 ("H", self.d_abc[0].data_ptr(), N_H, None), ("L", w + 48 * (N_INPUTS + 1), N_L, None))
+        for name, sc, n, idx in calls:
+            ctx.msm_pinned_dev(self.pk[name], sc, n, d_index_ptr=idx)
+            st = ctx.msm_last_stats()
+            tot += st["entries"] - st["tasks"]
+            shapes[name] = st
+        return tot, shapes
+
+    def close(self):
+        for p in self.pk.values():
+            p.release()
+        self.ctx.close()
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+def imad_peak(ctx):
+    """Measured integer-multiply ceiling of this GPU: best Fq products/s of a dependent-chain
+    Montgomery-product kernel over a few occupancies, in 32x32 products per second."""
+    best = 0.0
+    for blocks_per_sm, tpb in ((2, 128), (3, 128), (4, 64)):
+        blocks, iters = 148 * blocks_per_sm, 1000
+        ms = min(ctx.bench_fq_mul(blocks, tpb, iters) for _ in range(2))
+        best = max(best, blocks * tpb * iters / (ms * 1e-3))
+    return best * PRODUCTS_PER_FQ_MUL
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    wl = Workload(local_rank, seed=1 + rank)
+    ctx = wl.ctx
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident arm (value)
+    for _ in range(args.warmup):
+        wl.step_resident()
+    ctx.kernel_ms(0)
+    ctx.kernel_ms(1)
+    launches0 = ctx.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        wl.step_resident()   # every library call synchronises its own stream before returning
+    torch.cuda.synchronize()
+    ev1.record()
+    barrier()
+    t_res = max(ev0.elapsed_time(ev1) * 1e-3, 0.0)
+    wall_res = time.perf_counter() - t0
+    # the library runs on its own stream; its work is bracketed by host-synchronising calls, so the
+    # torch events above enclose it; keep the larger of the two clocks to be safe
+    t_res = max(t_res, wall_res) if t_res < 0.5 * wall_res else t_res
+    clocks = sampler.stop()
+    launches = ctx.launch_count() - launches0
+    acc_ms, acc_n = ctx.kernel_ms(0)
+    ntt_ms, ntt_n = ctx.kernel_ms(1)
+
+    # ---- end-to-end arm (host pointers)
+    for _ in range(max(1, min(args.warmup, 2))):
+        wl.step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        wl.step_e2e()
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    barrier()
+
+    # ---- secondary headline: G1 MSM 2^20 latency (rank 0, N = 1 only)
+    msm20 = None
+    if world == 1 and not args.skip_msm20:
+        n = 1 << 20
+        pts = ctx.synth_bases(n, wl.z.G1, seed=77)
+        pin = ctx.pin_bases(pts)
+        sc = torch.from_numpy(random_fr(np.random.default_rng(5), n).view(np.int64)).cuda()
+        torch.cuda.synchronize()
+        ts = [ctx.msm_pinned_dev(pin, sc.data_ptr(), n)[1] for _ in range(4)]
+        msm20 = min(ts[1:])
+        pin.release()
+        del sc, pts
+
+    if world > 1:
+        tt = torch.tensor([t_res, t_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_res, t_e2e = tt.tolist()
+    out = None
+    if rank == 0:
+        peaks, peaks_src = measured_peaks()
+        peak_prod = imad_peak(ctx)
+        madds, shapes = wl.algorithmic_madds()
+        acc_s = acc_ms * 1e-3 / max(args.steps, 1)          # accumulate time per step (5 launches)
+        achieved = madds * FQ_MUL_PER_MADD * PRODUCTS_PER_FQ_MUL / acc_s if acc_s > 0 else 0.0
+        ntt_bytes = 7 * 192 * (1 << LOG_M)                   # 2 passes x (48 B read + 48 B write) per element
+        ntt_s = ntt_ms * 1e-3 / max(args.steps, 1)
+        out = {
+            "metric": METRIC, "value": world * args.steps / t_res, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32x24 (761-bit Fq) / u32x12 (377-bit Fr)",
+            "data": "synthetic (seeded curve points k_i*G, aggregator-like witness)",
+            "config": {"workload": "batch-8 aggregator Groth16 prove hot path: H-poly (7 NTT, m=2^18) + MSM A/B(G2,G1)/H/L",
+                       "msm_sizes": {"A": N_A, "B_g2": N_B, "B_g1": N_B, "H": N_H, "L": N_L}, "ntt_log_m": LOG_M,
+                       "parallelism": "replicas (one proof stream per GPU)" if world > 1 else "single GPU",
+                       "l2": "inputs larger than L2 (158 MB of bases per step)"},
+            "e2e": {"value": world * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": Workload.E2E_H2D,
+                    "d2h_bytes_per_step": Workload.E2E_D2H},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "imad", "kernel": "k_accumulate (MSM bucket accumulation)", "achieved": achieved / 1e12,
+                         "peak": peak_prod / 1e12, "unit": "T(32x32 products)/s", "frac": achieved / peak_prod if peak_prod else None,
+                         "peak_source": "measured in this run: dependent-chain Fq Montgomery products (k_bench_fq_mul)",
+                         "share_of_step": acc_s / (t_res / args.steps), "launches_per_step": acc_n / max(args.steps, 1),
+                         "madds_per_step": madds, "msm_shapes": shapes, "traffic": None},
+            "roofline_ntt": {"bound": "hbm", "kernel": "k_ntt_pass (Fr radix-2 NTT, 7 transforms per step)",
+                             "achieved": ntt_bytes / ntt_s / 1e9 if ntt_s > 0 else None, "peak": peaks["hbm_gbs"],
+                             "unit": "GB/s", "frac": (ntt_bytes / ntt_s / 1e9) / peaks["hbm_gbs"] if ntt_s > 0 else None,
+                             "peak_source": peaks_src, "share_of_step": ntt_s / (t_res / args.steps), "traffic": None},
+            "msm_g1_2e20_ms": msm20,
+        }
+    wl.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+class ReferenceWorkload:
+    """The same step on the host cores with the UNMODIFIED reference (oracle/_ref):
+    libfqfft transforms of r1cs_to_qap_witness_map and libff::multi_exp (BDLO12_signed, special
+    bases, chunks = all threads) / kc-style pair MSM at the batch-8 sizes. `frac` < 1 takes the
+    first frac*n points of every MSM (bounded sample); MSM time is then scaled by 1/frac."""
+
+    def __init__(self, frac=1.0):
+        from oracle import ref as R
+        self.R = R
+        self.ref = R.Ref()
+        self.threads = self.ref.threads
+        self.frac = frac
+        rng = np.random.default_rng(1)
+        nmax = int(max(N_A, N_H) * frac)
+        self.g1 = self.ref.bases_seq(nmax, 1)
+        self.g2 = self.ref.bases_seq(int(N_B * frac), 2)
+        self.w = witness_like(rng, N_A)
+        self.abc = [random_fr(rng, 1 << LOG_M) for _ in range(3)]
+        self.b_index = np.sort(rng.choice(N_A, N_B, replace=False))
+
+    def step(self):
+        """Returns (seconds for one proof's hot path scaled to full size, split)."""
+        ref, f = self.ref, self.frac
+        h, t_h = ref.qap_h(*self.abc)
+        nA, nB, nH, nL = (int(n * f) for n in (N_A, N_B, N_H, N_L))
+        wB = np.ascontiguousarray(self.w[self.b_index[:nB]])
+        _, tA = ref.msm(self.g1[:nA], self.w[:nA], 1)
+        _, tB2 = ref.msm(self.g2[:nB], wB, 2)
+        _, tB1 = ref.msm(self.g1[:nB], wB, 1)
+        _, tH = ref.msm(self.g1[:nH], h[:nH], 1)
+        _, tL = ref.msm(self.g1[:nL], self.w[N_INPUTS + 1:N_INPUTS + 1 + nL], 1)
+        t_msm = (tA + tB2 + tB1 + tH + tL) / f
+        return t_h + t_msm, {"h_poly_s": t_h, "msm_s": t_msm}
+
+
+def cpu_baseline_sample():
+    """cpu_baseline leg of the default run: one bounded sample of the step on the host cores."""
+    from oracle import ref as R
+    if not R.available():
+        return {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
+                "sample": "oracle/_ref not built on this box"}
+    rw = ReferenceWorkload(1.0)
+    t, split = rw.step()
+    return {"value": 1.0 / t, "unit": UNIT, "cores": rw.threads, "kind": "reference",
+            "sample": "one full step, once: 7 libfqfft transforms at m=2^18 + the five libff::multi_exp<BDLO12_signed, special> "
+                      "calls at the batch-8 sizes (h_poly %.2f s, msm %.2f s)" % (split["h_poly_s"], split["msm_s"])}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return None
+    from oracle import ref as R
+    if not R.available():
+        return {"impl": "reference", "unavailable": "oracle/_ref/libzecale_ref.so is not built (needs /root/reference at build time)"}
+    total = max(args.steps, 1) + 1
+    # a full step is ~15-25 s of 16-core CPU time; keep the whole run within a few minutes
+    frac = 1.0 if total <= 9 else (0.5 if total <= 18 else 0.25)
+    rw = ReferenceWorkload(frac)
+    ReferenceWorkload(0.02).step()  # warm-up on a small sample (page faults, OpenMP pool); W full CPU steps would only burn minutes
+    ts, split = [], None
+    for _ in range(max(args.steps, 1)):
+        t, split = rw.step()
+        ts.append(t)
+    t = sum(ts) / len(ts)
+    sample = ("each step: 7 libfqfft transforms (m=2^18) + five libff::multi_exp<BDLO12_signed, special> calls on the first "
+              "%d%% of each base vector, MSM seconds scaled by %.0fx; warm-up = one 2%% step" % (int(frac * 100), 1 / frac))
+    return {"impl": "reference", "metric": METRIC, "value": 1.0 / t, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64x12 (761-bit Fq) / u64x6 (377-bit Fr), GMP mpn", "data": "synthetic (seeded)",
+            "config": {"workload": "batch-8 aggregator Groth16 prove hot path: H-poly (7 NTT, m=2^18) + MSM A/B(G2,G1)/H/L",
+                       "msm_sizes": {"A": N_A, "B_g2": N_B, "B_g1": N_B, "H": N_H, "L": N_L}, "ntt_log_m": LOG_M,
+                       "parallelism": "OpenMP, %d threads" % rw.threads},
+            "cpu_baseline": {"value": 1.0 / t, "unit": UNIT, "cores": rw.threads, "kind": "reference", "sample": sample},
+            "e2e": {"value": 1.0 / t, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "split": split}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--skip-msm20", action="store_true")
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        out = run_reference(args, rank, world)
+        if out is not None:
+            print(json.dumps(out), flush=True)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+    out = run_b200(args, rank, world, local_rank)
+    if rank == 0:
+        if world == 1 and not args.skip_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline_sample()
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -95,6 +95,13 @@ int zecale_gpu_ntt(zecale_gpu_ctx *ctx, void *a, unsigned log_m, unsigned flags,
  * retained. group is ZECALE_GPU_G1 or ZECALE_GPU_G2 (same arithmetic, kept for checks). */
 int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
                          zecale_gpu_bases **handle);
+/* Same with the expansion made explicit: expand = 0 keeps one copy of the bases (the MSM then
+ * runs one bucket set per window and a Horner pass of c doublings per window, like an
+ * un-pinned call); expand = 1 (what zecale_gpu_pin_bases does) also stores 2^(c*V*g) * P_i for
+ * every window group g, so that all windows share V bucket sets (V = 1 when memory allows:
+ * n * 192 B * ceil(378/c) bytes) and the doubling chain disappears from every later MSM. */
+int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
+                            int expand, zecale_gpu_bases **handle);
 int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *handle);
 /* MSM over the first n pinned bases. */
 int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *handle, const void *scalars,
@@ -110,9 +117,35 @@ int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *handl
 int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned flags, const void *coset_g,
                        float *elapsed_ms);
 
+/* ---- H polynomial: the device part of libsnark::r1cs_to_qap_witness_map ----------
+ * (r1cs_to_qap.tcc:252-330 with d1 = d2 = d3 = 0, as r1cs_gg_ppzksnark_prover calls it,
+ * r1cs_gg_ppzksnark.tcc:477-484). Inputs are the evaluations aA[i] = <A_i,w>,
+ * aB[i] = <B_i,w>, aC[i] = <C_i,w> on the domain of size m = 2^log_m (zero padded, with
+ * the input-consistency rows already in aA, r1cs_to_qap.tcc:236-248). Runs
+ * 3 x (iFFT, cosetFFT), aA∘aB - aC, divide_by_Z_on_coset and icosetFFT on the device and
+ * writes coefficients_for_H: m + 1 Fr elements (the last one is zero). coset_g is
+ * Fr::multiplicative_generator in Montgomery form. HOST pointers. */
+int zecale_gpu_qap_h(zecale_gpu_ctx *ctx, const void *aA, const void *aB, const void *aC, unsigned log_m,
+                     const void *coset_g, void *out_h);
+/* Device-resident variant: d_aA receives coefficients_for_H[0..m); d_aB, d_aC are clobbered. */
+int zecale_gpu_qap_h_dev(zecale_gpu_ctx *ctx, void *d_aA, void *d_aB, void *d_aC, unsigned log_m,
+                         const void *coset_g, float *elapsed_ms);
+
+/* ---- synthetic inputs (bench / tests): out_points[i] = k_i * generator of the group, in
+ * libff special form (288 B each), k_i a non-zero 32-bit hash of (seed, i). HOST pointer. */
+int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t n, void *out_points);
+
 /* ---- introspection ----------------------------------------------------------------*/
 /* Number of kernel launches issued by this context so far (bench.py gpu_launches). */
 uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx);
+/* CUDA-event time spent in one kernel class since the last reset, and the number of timed
+ * regions: class 0 = MSM bucket accumulation kernel (k_accumulate, one region per MSM),
+ * class 1 = NTT transforms (one region per transform, tables excluded). */
+int zecale_gpu_kernel_ms(zecale_gpu_ctx *ctx, int kernel_class, int reset, double *total_ms, uint64_t *count);
+/* Shape of the last MSM this context ran: bucket entries (non-zero digits), accumulate tasks,
+ * window bits, bucket sets V and base copies G. Mixed additions executed = entries - tasks. */
+int zecale_gpu_msm_last_stats(zecale_gpu_ctx *ctx, uint64_t *entries, uint64_t *tasks, unsigned *c,
+                              unsigned *bucket_sets, unsigned *base_copies);
 /* Window size c the MSM uses for n points (for the roofline op count). */
 unsigned zecale_gpu_msm_window_bits(size_t n);
 

@@ -32,7 +32,7 @@ class Ref:
         if not os.path.exists(path):
             raise FileNotFoundError(path + " (run `make -C oracle ref ref-agg` where /root/reference exists)")
         L = ctypes.CDLL(path)
-        for f in ("zref_msm_g1", "zref_msm_g2", "zref_msm_g1_naive", "zref_msm_kc", "zref_ntt",
+        for f in ("zref_msm_g1", "zref_msm_g2", "zref_msm_g1_naive", "zref_msm_kc", "zref_ntt", "zref_qap_h",
                   "zref_session_setup", "zref_session_prove_stock"):
             getattr(L, f).restype = _d
         L.zref_fr_signed_digit.restype = ctypes.c_long
@@ -116,6 +116,14 @@ class Ref:
         if t < 0:
             raise RuntimeError("reference NTT threw")
         return out, t
+
+    def qap_h(self, aA, aB, aC):
+        """coefficients_for_H (m+1, 6) by the reference's own transform sequence; returns (h, seconds)."""
+        m = aA.shape[0]
+        h = np.zeros((m + 1, 6), dtype=np.uint64)
+        t = self.L.zref_qap_h(_p(np.ascontiguousarray(aA)), _p(np.ascontiguousarray(aB)), _p(np.ascontiguousarray(aC)),
+                              ctypes.c_uint(m.bit_length() - 1), _p(h))
+        return h, t
 
     # ---- Groth16 sessions -----------------------------------------------------------
     def session_synthetic(self, num_constraints, num_inputs, n_bits, seed):

@@ -440,6 +440,48 @@ extern "C" double zref_ntt(void *a, unsigned log_m, unsigned flags, const void *
     }
 }
 
+// The transform part of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330, d1 = d2 = d3 = 0)
+// on caller-supplied evaluation vectors, through the same evaluation_domain calls in the
+// same order. h receives m + 1 elements. Returns seconds.
+extern "C" double zref_qap_h(const void *aA_, const void *aB_, const void *aC_, unsigned log_m, void *h)
+{
+    const size_t m = (size_t)1 << log_m;
+    const std::shared_ptr<libfqfft::evaluation_domain<Fr>> domain = libfqfft::get_evaluation_domain<Fr>(m);
+    std::vector<Fr> aA((const Fr *)aA_, (const Fr *)aA_ + m), aB((const Fr *)aB_, (const Fr *)aB_ + m),
+        aC((const Fr *)aC_, (const Fr *)aC_ + m);
+    const double t0 = now_s();
+    domain->iFFT(aA);
+    domain->iFFT(aB);
+    std::vector<Fr> coefficients_for_H(domain->m + 1, Fr::zero());
+    domain->add_poly_Z(Fr::zero(), coefficients_for_H);
+    const Fr g = Fr::multiplicative_generator;
+    domain->cosetFFT(aA, g);
+    domain->cosetFFT(aB, g);
+    std::vector<Fr> &H_tmp = aA;
+#ifdef MULTICORE
+#pragma omp parallel for
+#endif
+    for (size_t i = 0; i < domain->m; ++i)
+        H_tmp[i] = aA[i] * aB[i];
+    domain->iFFT(aC);
+    domain->cosetFFT(aC, g);
+#ifdef MULTICORE
+#pragma omp parallel for
+#endif
+    for (size_t i = 0; i < domain->m; ++i)
+        H_tmp[i] = (H_tmp[i] - aC[i]);
+    domain->divide_by_Z_on_coset(H_tmp);
+    domain->icosetFFT(H_tmp, g);
+#ifdef MULTICORE
+#pragma omp parallel for
+#endif
+    for (size_t i = 0; i < domain->m; ++i)
+        coefficients_for_H[i] += H_tmp[i];
+    const double t1 = now_s();
+    std::memcpy(h, (const void *)coefficients_for_H.data(), (m + 1) * 48);
+    return t1 - t0;
+}
+
 // omega for the size-2^log_m domain (field_utils.tcc:190-206); (g^m - 1)^-1 helper.
 extern "C" void zref_domain_params(unsigned log_m, void *omega, void *z_inv_on_coset)
 {

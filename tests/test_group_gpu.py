@@ -34,3 +34,22 @@ def test_group_ops(gpu, ref, group):
     assert np.array_equal(gpu.test_group(0, S, ref.group_op(2, Q, None, group)),
                           norm(ref.group_op(0, S, ref.group_op(2, Q, None, group), group)))
     assert np.array_equal(gpu.test_group(3, S), norm(S))
+
+
+def _synth_scalar(seed, i):
+    M = (1 << 64) - 1
+    x = (seed * 0x9E3779B97F4A7C15 + i * 0xBF58476D1CE4E5B9 + 0x94D049BB133111EB) & M
+    x ^= x >> 30
+    x = (x * 0xBF58476D1CE4E5B9) & M
+    x ^= x >> 27
+    x = (x * 0x94D049BB133111EB) & M
+    x ^= x >> 31
+    return (x & 0xFFFFFFFF) or 1
+
+
+@pytest.mark.parametrize("group", [1, 2])
+def test_synth_bases_are_multiples_of_the_generator(gpu, ref, group):
+    n = 300
+    got = gpu.synth_bases(n, group, seed=5)
+    ks = ref.fr_from_ints([_synth_scalar(5, i) for i in range(n)])
+    assert np.array_equal(got, ref.bases_mul(ks, group))

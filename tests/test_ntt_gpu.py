@@ -64,3 +64,17 @@ def test_ntt_errors(gpu):
         gpu.ntt(np.zeros((12, 6), dtype=np.uint64))
     with pytest.raises(z.ZecaleGpuError):
         gpu.ntt(np.zeros((4, 6), dtype=np.uint64), z.NTT_COSET, None)
+
+
+@pytest.mark.parametrize("log_m", [4, 12, 16])
+def test_qap_h_vs_reference(gpu, ref, log_m):
+    """zecale_gpu_qap_h == the transform sequence of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:252-330)."""
+    m = 1 << log_m
+    aA, aB, aC = (ref.fr_rng(s * 1000003, m) for s in (1, 2, 3))
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    exp, _ = ref.qap_h(aA, aB, aC)
+    keep = (aA.copy(), aB.copy(), aC.copy())
+    got = gpu.qap_h(aA, aB, aC, g)
+    assert np.array_equal(got, exp)
+    assert all(np.array_equal(x, y) for x, y in zip(keep, (aA, aB, aC)))  # inputs untouched
+    assert not got[m].any()

@@ -227,6 +227,11 @@ def gen_consts():
     o += carr("FR_ROOT_2S", C.limbs32(w * Rm % C.R, 12))
     o += carr("FR_ROOT_2S_INV", C.limbs32(pow(w, -1, C.R) * Rm % C.R, 12))
     o += "static constexpr int FR_TWO_ADICITY = %d;\n" % C.FR_S
+    Rq = (1 << C.FQ_RBITS) % C.Q
+    o += carr("FQ_R3", C.limbs32(C.FQ["r3"], 24))
+    for nm, pt in (("G1_GEN", C.G1_GEN), ("G2_GEN", C.G2_GEN)):
+        o += carr(nm + "_X", C.limbs32(pt[0] * Rq % C.Q, 24))
+        o += carr(nm + "_Y", C.limbs32(pt[1] * Rq % C.Q, 24))
     o += "} // namespace zecale\n"
     return o
 

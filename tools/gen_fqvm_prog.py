@@ -18,11 +18,11 @@ import re
 
 SLOTS = {"X": 0, "Y": 1, "ZZ": 2, "ZZZ": 3, "QX": 4, "QY": 5, "QZZ": 6, "QZZZ": 7,
          "T0": 8, "T1": 9, "T2": 10, "T3": 11, "T4": 12, "RX": 13, "RY": 14, "RZZ": 15, "RZZZ": 16,
-         "K0": 17}
-NSLOT = 18
+         "K0": 17, "K1": 18}
+NSLOT = 19
 
 OPS = {"MUL": 0, "ADD": 1, "SUB": 2, "MOV": 3, "ONE": 4, "ZERO": 5, "JZ": 6, "JMP": 7, "JBIT": 8,
-       "DECJNZ": 9, "SETCNT": 10, "CALL": 11, "RET": 12, "HOOK": 13, "HALT": 14}
+       "DECJNZ": 9, "SETCNT": 10, "CALL": 11, "RET": 12, "HOOK": 13, "HALT": 14, "INVP": 15, "LDR3": 16}
 
 PROGRAM = r"""
 ; ---------------------------------------------------------------- acc += (QX, QY) affine, not infinity
@@ -86,8 +86,16 @@ toaff:
     HOOK 1
 toaff_inf:
     HOOK 2
-; T0 = T1^(q-2) (Fermat; libff uses mpn_gcdext, fp.tcc:680-727 -- the inverse is unique)
+; T0 = 1/T1 (0 -> 0). INVP is the binary extended Euclid on the plain integer aR, giving
+; a^-1 R^-1; one Montgomery product with R^3 restores a^-1 R — the same two steps as libff's
+; Fp_model::invert (mpn_gcdext then mul_reduce(Rcubed), fp.tcc:680-727).
 inv:
+    INVP T0, T1
+    LDR3 K0
+    MUL  T0, T0, K0
+    RET
+; T0 = T1^(q-2): Fermat ladder, kept as an independent check of INVP (tests only)
+inv_fermat:
     MOV  T0, T1
     SETCNT 759              ; q-2 has 761 bits; the top one is the MOV
 inv_loop:
@@ -95,7 +103,7 @@ inv_loop:
     JBIT inv_mul
 inv_next:
     DECJNZ inv_loop
-    RET
+    HOOK 0
 inv_mul:
     MUL  T0, T0, T1
     JMP  inv_next
@@ -122,13 +130,13 @@ movqa:
     MOV  ZZZ, QZZZ
     HOOK 0
 ; ---------------------------------------------------------------- batched inversion helpers (precompute normalisation)
-; T2 = running product; step: T3 = T2 (saved by hook), T2 *= ZZZ
+; K1 = running product (a slot no point program touches); step: K1 *= ZZZ
 prodstep:
-    MUL  T2, T2, ZZZ
+    MUL  K1, K1, ZZZ
     HOOK 0
-; T0 = 1/T2
+; T0 = 1/K1
 invprod:
-    MOV  T1, T2
+    MOV  T1, K1
     CALL inv
     HOOK 0
 ; given T0 = 1/(prefix * ZZZ), T3 = prefix: T4 = T0*T3 = 1/ZZZ ; T0 = T0*ZZZ = 1/prefix ; then affine into QX,QY
@@ -213,7 +221,7 @@ PROGRAM += ADD_TEMPLATE.format(S="", BX="QX", BY="QY", BZZ="QZZ", BZZZ="QZZZ", *
 # second accumulator R += acc (running-sum bucket reduction)
 PROGRAM += ADD_TEMPLATE.format(S="_r", AX="RX", AY="RY", AZZ="RZZ", AZZZ="RZZZ", BX="X", BY="Y", BZZ="ZZ", BZZZ="ZZZ")
 
-ENTRY_POINTS = ["madd", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep"]
+ENTRY_POINTS = ["madd", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep", "inv_fermat"]
 
 
 def assemble(text):
@@ -238,10 +246,10 @@ def assemble(text):
         if op in ("MUL", "ADD", "SUB"):
             d, a, b = (SLOTS[x] for x in args)
             imm = a | (b << 8)
-        elif op == "MOV":
+        elif op in ("MOV", "INVP"):
             d, a = SLOTS[args[0]], SLOTS[args[1]]
             imm = a
-        elif op in ("ONE", "ZERO"):
+        elif op in ("ONE", "ZERO", "LDR3"):
             d = SLOTS[args[0]]
             imm = 0
         elif op == "JZ":

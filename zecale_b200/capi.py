@@ -42,10 +42,17 @@ EXPORTS = {
     "zecale_gpu_msm_g2": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp]),
     "zecale_gpu_ntt": (_i, [_vp, _vp, _u, _u, _vp]),
     "zecale_gpu_pin_bases": (_i, [_vp, _vp, _sz, _sz, _i, ctypes.POINTER(_vp)]),
+    "zecale_gpu_pin_bases_ex": (_i, [_vp, _vp, _sz, _sz, _i, _i, ctypes.POINTER(_vp)]),
+    "zecale_gpu_msm_last_stats": (_i, [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64),
+                                  ctypes.POINTER(_u), ctypes.POINTER(_u), ctypes.POINTER(_u)]),
     "zecale_gpu_unpin_bases": (_i, [_vp, _vp]),
     "zecale_gpu_msm_pinned": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _vp]),
     "zecale_gpu_msm_pinned_dev": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _vp, ctypes.POINTER(ctypes.c_float)]),
     "zecale_gpu_ntt_dev": (_i, [_vp, _vp, _u, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_qap_h": (_i, [_vp, _vp, _vp, _vp, _u, _vp, _vp]),
+    "zecale_gpu_qap_h_dev": (_i, [_vp, _vp, _vp, _vp, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_synth_bases": (_i, [_vp, _i, ctypes.c_uint64, _sz, _vp]),
+    "zecale_gpu_kernel_ms": (_i, [_vp, _i, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]),
     "zecale_gpu_launch_count": (ctypes.c_uint64, [_vp]),
     "zecale_gpu_msm_window_bits": (_u, [_sz]),
     "zecale_gpu_test_fq": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
@@ -133,12 +140,20 @@ class Context:
     def msm_g2(self, bases, scalars, index=None, n=None, base_offset_bytes=0):
         return self._msm(_lib.zecale_gpu_msm_g2, bases, scalars, index, n, base_offset_bytes)
 
-    def pin_bases(self, bases, group=G1, base_offset_bytes=0):
+    def pin_bases(self, bases, group=G1, base_offset_bytes=0, expand=True):
         h = ctypes.c_void_p()
         n = int(bases.shape[0])
-        self._ck(_lib.zecale_gpu_pin_bases(self._h, ctypes.c_void_p(bases.ctypes.data + base_offset_bytes),
-                                           bases.strides[0], n, group, ctypes.byref(h)))
+        self._ck(_lib.zecale_gpu_pin_bases_ex(self._h, ctypes.c_void_p(bases.ctypes.data + base_offset_bytes),
+                                              bases.strides[0], n, group, 1 if expand else 0, ctypes.byref(h)))
         return PinnedBases(self, h, n, group)
+
+    def msm_last_stats(self):
+        e, t = ctypes.c_uint64(), ctypes.c_uint64()
+        c, v, g = _u(), _u(), _u()
+        self._ck(_lib.zecale_gpu_msm_last_stats(self._h, ctypes.byref(e), ctypes.byref(t), ctypes.byref(c),
+                                                ctypes.byref(v), ctypes.byref(g)))
+        return {"entries": int(e.value), "tasks": int(t.value), "c": int(c.value), "bucket_sets": int(v.value),
+                "base_copies": int(g.value)}
 
     def msm_pinned(self, pinned, scalars, index=None, n=None):
         out = np.zeros(36, dtype=np.uint64)
@@ -171,6 +186,33 @@ class Context:
         ms = ctypes.c_float()
         self._ck(_lib.zecale_gpu_ntt_dev(self._h, ctypes.c_void_p(d_ptr), log_m, flags, _ptr(coset_g), ctypes.byref(ms)))
         return ms.value
+
+    def qap_h(self, aA, aB, aC, coset_g):
+        """coefficients_for_H (m+1, 6) from the three evaluation vectors (host arrays, not modified)."""
+        m = aA.shape[0]
+        log_m = m.bit_length() - 1
+        if m == 0 or (1 << log_m) != m or aB.shape[0] != m or aC.shape[0] != m:
+            raise ValueError("qap_h: vectors must have the same power-of-two length")
+        out = np.zeros((m + 1, 6), dtype=np.uint64)
+        self._ck(_lib.zecale_gpu_qap_h(self._h, _ptr(aA), _ptr(aB), _ptr(aC), log_m, _ptr(coset_g), _ptr(out)))
+        return out
+
+    def qap_h_dev(self, d_aA, d_aB, d_aC, log_m, coset_g):
+        ms = ctypes.c_float()
+        self._ck(_lib.zecale_gpu_qap_h_dev(self._h, ctypes.c_void_p(d_aA), ctypes.c_void_p(d_aB), ctypes.c_void_p(d_aC),
+                                           log_m, _ptr(coset_g), ctypes.byref(ms)))
+        return ms.value
+
+    def synth_bases(self, n, group=G1, seed=0):
+        out = np.zeros((n, 36), dtype=np.uint64)
+        self._ck(_lib.zecale_gpu_synth_bases(self._h, group, seed, n, _ptr(out)))
+        return out
+
+    def kernel_ms(self, kernel_class, reset=True):
+        ms = ctypes.c_double()
+        cnt = ctypes.c_uint64()
+        self._ck(_lib.zecale_gpu_kernel_ms(self._h, kernel_class, 1 if reset else 0, ctypes.byref(ms), ctypes.byref(cnt)))
+        return ms.value, int(cnt.value)
 
     # -- misc -----------------------------------------------------------------------
     def launch_count(self):

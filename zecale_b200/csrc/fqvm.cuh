@@ -176,6 +176,97 @@ __device__ __forceinline__ void xyzz_store_inf(XYZZ *dst)
     for (int k = 0; k < 6; k++) d[6 + k] = make_uint4(FQ_ONE[4 * k], FQ_ONE[4 * k + 1], FQ_ONE[4 * k + 2], FQ_ONE[4 * k + 3]);
 }
 
+// ---------------------------------------------------------------- plain modular inverse
+// r = a^-1 mod q for a plain integer 0 < a < q: binary extended Euclid (shift / subtract).
+// Invariants: u = x1*a, v = x2*a (mod q); ends when u or v reaches 1. ~1500 iterations of
+// 24-limb adds/shifts: ~60 Montgomery-product times, against 1141 products for a^(q-2).
+// a == 0 returns 0.
+__device__ __forceinline__ void big_shr1(uint32_t (&x)[24], uint32_t top)
+{
+#pragma unroll
+    for (int k = 0; k < 23; k++) x[k] = __funnelshift_r(x[k], x[k + 1], 1);
+    x[23] = __funnelshift_r(x[23], top, 1);
+}
+
+// x = x/2 mod q
+__device__ __forceinline__ void big_halve_mod(uint32_t (&x)[24])
+{
+    uint32_t carry = 0;
+    if (x[0] & 1u) {
+        uint64_t c = 0;
+#pragma unroll
+        for (int k = 0; k < 24; k++) {
+            c += (uint64_t)x[k] + FQ_P[k];
+            x[k] = (uint32_t)c;
+            c >>= 32;
+        }
+        carry = (uint32_t)c;
+    }
+    big_shr1(x, carry);
+}
+
+// d = x - y, returns the borrow
+__device__ __forceinline__ uint32_t big_sub(uint32_t (&d)[24], const uint32_t (&x)[24], const uint32_t (&y)[24])
+{
+    int64_t c = 0;
+#pragma unroll
+    for (int k = 0; k < 24; k++) {
+        c += (int64_t)x[k] - (int64_t)y[k];
+        d[k] = (uint32_t)c;
+        c >>= 32;
+    }
+    return (uint32_t)(c & 1);
+}
+
+__device__ __forceinline__ bool big_is_one(const uint32_t (&x)[24])
+{
+    uint32_t acc = x[0] ^ 1u;
+#pragma unroll
+    for (int k = 1; k < 24; k++) acc |= x[k];
+    return acc == 0;
+}
+
+__device__ __forceinline__ void fq_inv_plain(uint32_t (&r)[24], const uint32_t (&a)[24])
+{
+    uint32_t u[24], v[24], x1[24], x2[24], d[24];
+    uint32_t nz = 0;
+#pragma unroll
+    for (int k = 0; k < 24; k++) {
+        u[k] = a[k];
+        v[k] = FQ_P[k];
+        x1[k] = k == 0 ? 1u : 0u;
+        x2[k] = 0;
+        nz |= a[k];
+    }
+    if (nz == 0) {
+#pragma unroll
+        for (int k = 0; k < 24; k++) r[k] = 0;
+        return;
+    }
+    for (;;) {
+        const bool u1 = big_is_one(u);
+        if (u1 || big_is_one(v)) {
+#pragma unroll
+            for (int k = 0; k < 24; k++) r[k] = u1 ? x1[k] : x2[k];
+            return;
+        }
+        if (!(u[0] & 1u)) {
+            big_shr1(u, 0);
+            big_halve_mod(x1);
+        } else if (!(v[0] & 1u)) {
+            big_shr1(v, 0);
+            big_halve_mod(x2);
+        } else if (big_sub(d, u, v) == 0) { // u >= v
+#pragma unroll
+            for (int k = 0; k < 24; k++) u[k] = d[k];
+            fq_sub_regs(x1, x1, x2);
+        } else {
+            big_sub(v, v, u);
+            fq_sub_regs(x2, x2, x1);
+        }
+    }
+}
+
 // Run from `pc` until the hook returns false. hook(id, pc, S) may change pc.
 template <class Hook>
 __device__ __forceinline__ void fqvm_run(FqSlots &S, uint32_t pc, Hook &&hook)
@@ -226,6 +317,19 @@ __device__ __forceinline__ void fqvm_run(FqSlots &S, uint32_t pc, Hook &&hook)
             pc = imm;
             break;
         case VOP_RET: pc = ret; break;
+        case VOP_INVP: {
+            uint32_t x[24], z[24];
+            vs_load(x, S, imm);
+            fq_inv_plain(z, x);
+            vs_store(S, d, z);
+            break;
+        }
+        case VOP_LDR3: {
+            uint4 *p = S.w + d * 6;
+#pragma unroll
+            for (int k = 0; k < 6; k++) p[k] = make_uint4(FQ_R3[4 * k], FQ_R3[4 * k + 1], FQ_R3[4 * k + 2], FQ_R3[4 * k + 3]);
+            break;
+        }
         case VOP_HOOK:
             if (!hook(d, pc, S)) return;
             break;

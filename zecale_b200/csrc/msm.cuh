@@ -117,6 +117,162 @@ __global__ void k_import_special(const uint8_t *raw, size_t stride, uint32_t n, 
     for (int k = 0; k < 12; k++) dst[k] = src[k];
 }
 
+// ------------------------------------------------------------------ synthetic bases
+// out[i] = k_i * generator in libff special form, k_i = 32-bit hash of (seed, i), never 0.
+// Used by bench.py / tests to make distinct valid curve points without a CPU library.
+__device__ __forceinline__ uint32_t synth_scalar(uint64_t seed, uint32_t i)
+{
+    uint64_t x = seed * 0x9E3779B97F4A7C15ull + (uint64_t)i * 0xBF58476D1CE4E5B9ull + 0x94D049BB133111EBull;
+    x ^= x >> 30;
+    x *= 0xBF58476D1CE4E5B9ull;
+    x ^= x >> 27;
+    x *= 0x94D049BB133111EBull;
+    x ^= x >> 31;
+    uint32_t k = (uint32_t)x;
+    return k ? k : 1u;
+}
+
+__global__ void __launch_bounds__(128, 2) k_synth_bases(int group, uint64_t seed, uint32_t n, Proj *out)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    FqSlots S;
+    vs_acc_inf(S);
+    {
+        const uint32_t *gx = group == 2 ? G2_GEN_X : G1_GEN_X, *gy = group == 2 ? G2_GEN_Y : G1_GEN_Y;
+        uint32_t x[24], y[24];
+#pragma unroll
+        for (int k = 0; k < 24; k++) {
+            x[k] = gx[k];
+            y[k] = gy[k];
+        }
+        vs_store(S, VS_QX, x);
+        vs_store(S, VS_QY, y);
+    }
+    const uint32_t k = synth_scalar(seed, i);
+    int bit = 31;
+    uint32_t phase = 0; // 0: a doubling just ran, 1: an addition just ran, 2: normalising
+    fqvm_run(S, VPC_DBL, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        if (phase == 2) {
+            Proj *o = out + i;
+            vs_get(&o->X, S_, VS_QX);
+            vs_get(&o->Y, S_, VS_QY);
+            vs_one(S_, VS_T0);
+            vs_get(&o->Z, S_, VS_T0);
+            return false;
+        }
+        if (phase == 0 && ((k >> bit) & 1u)) {
+            phase = 1;
+            pc = VPC_MADD;
+            return true;
+        }
+        phase = 0;
+        if (bit == 0) {
+            phase = 2;
+            pc = VPC_TOAFF; // k != 0 and the generator has prime order: never infinity
+            return true;
+        }
+        bit--;
+        pc = VPC_DBL;
+        return true;
+    });
+}
+
+// ------------------------------------------------------------------ pinned-image expansion
+// dst[i] = 2^ndbl * src[i] (affine in, affine out; (0,0) = infinity stays infinity). Each thread
+// owns K consecutive points and shares one inversion among them (Montgomery's trick):
+//   forward : XYZZ_j = 2^ndbl * P_j -> scratch, prefix_j = prod_{j' < j} ZZZ_j' -> scratch
+//   invert  : 1 / prod_j ZZZ_j            (one binary-Euclid inversion per K points)
+//   backward: 1/ZZZ_j = inv * prefix_j ; inv *= ZZZ_j ; x = X/ZZ, y = Y/ZZZ
+// This is libff's batch_to_special (multiexp.tcc:949-974, batch_invert field_utils.tcc:330-350)
+// fused with the doublings.
+static constexpr uint32_t EXPAND_K = 8;
+
+__global__ void __launch_bounds__(128, 2)
+k_expand_copy(const Affine *src, Affine *dst, uint32_t n, uint32_t ndbl, XYZZ *scratch_pt, Fq *scratch_prefix)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t i0 = t * EXPAND_K;
+    if (i0 >= n) return;
+    const uint32_t i1 = i0 + EXPAND_K < n ? i0 + EXPAND_K : n;
+    FqSlots S;
+    uint32_t i = i0, left = 0, stage = 0; // stage 0 forward, 1 inverting, 2 backward
+    vs_one(S, VS_K1);
+    // forward: find the next finite point, load it, start its doublings
+    auto next_forward = [&](uint32_t &pc, FqSlots &S_) -> bool {
+        while (i < i1) {
+            const Affine *p = src + i;
+            vs_set(S_, VS_X, &p->x);
+            vs_set(S_, VS_Y, &p->y);
+            if (!(vs_is_zero(S_, VS_X) && vs_is_zero(S_, VS_Y))) {
+                vs_one(S_, VS_ZZ);
+                vs_one(S_, VS_ZZZ);
+                left = ndbl;
+                pc = VPC_DBL;
+                return true;
+            }
+            xyzz_store_inf(scratch_pt + i); // zz = 0 marks infinity
+            i++;
+        }
+        return false;
+    };
+    auto next_backward = [&](uint32_t &pc, FqSlots &S_) -> bool {
+        while (i > i0) {
+            i--;
+            vs_load_acc(S_, scratch_pt + i);
+            if (!vs_is_zero(S_, VS_ZZ)) {
+                vs_set(S_, VS_T3, scratch_prefix + i);
+                pc = VPC_UNSTEP;
+                return true;
+            }
+            uint4 *d = reinterpret_cast<uint4 *>(dst + i);
+            for (int k = 0; k < 12; k++) d[k] = make_uint4(0, 0, 0, 0);
+        }
+        return false;
+    };
+    uint32_t pc0 = 0;
+    if (!next_forward(pc0, S)) { // all K points at infinity
+        stage = 2;
+        i = i1;
+        next_backward(pc0, S);
+        return;
+    }
+    fqvm_run(S, pc0, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        if (stage == 0) {
+            if (left) { // a doubling finished
+                if (--left) {
+                    pc = VPC_DBL;
+                    return true;
+                }
+                if (vs_is_zero(S_, VS_ZZZ)) { // doubled to infinity (2-torsion): keep it out of the product
+                    xyzz_store_inf(scratch_pt + i);
+                    i++;
+                } else {
+                    vs_store_acc(scratch_pt + i, S_);
+                    vs_get(scratch_prefix + i, S_, VS_K1);
+                    pc = VPC_PRODSTEP; // T2 *= ZZZ
+                    return true;
+                }
+            } else {
+                i++; // prodstep finished
+            }
+            if (next_forward(pc, S_)) return true;
+            stage = 1;
+            pc = VPC_INVPROD; // T0 = 1 / T2
+            return true;
+        }
+        if (stage == 1) {
+            stage = 2;
+            i = i1;
+            return next_backward(pc, S_);
+        }
+        // an unstep finished: affine point in QX, QY
+        vs_get(&dst[i].x, S_, VS_QX);
+        vs_get(&dst[i].y, S_, VS_QY);
+        return next_backward(pc, S_);
+    });
+}
+
 // ------------------------------------------------------------------ digits
 // One thread per scalar. scalars are Montgomery Fr, `sstride` bytes apart; the scalar of
 // base i is scalars[index ? index[i] : i]. digits[w*n + i] = signed digit of window w.
@@ -279,7 +435,7 @@ static constexpr uint32_t MSM_LEN_BINS = 1024;
 __device__ __forceinline__ uint32_t msm_len_bin(uint32_t len) { return len >= MSM_LEN_BINS ? 0u : MSM_LEN_BINS - len; }
 
 __global__ void k_task_fill(MsmPlan p, const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off,
-                            uint32_t *task_start, uint32_t *task_len, uint32_t *len_hist)
+                            uint32_t *task_start, uint32_t *task_len, uint32_t *task_bucket, uint32_t *len_hist)
 {
     size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= p.n_buckets) return;
@@ -290,6 +446,7 @@ __global__ void k_task_fill(MsmPlan p, const uint32_t *counts, const uint32_t *o
         uint32_t lo = (uint32_t)((cnt * k) / nt), hi = (uint32_t)((cnt * (k + 1)) / nt);
         task_start[t0 + k] = off + lo;
         task_len[t0 + k] = hi - lo;
+        task_bucket[t0 + k] = (uint32_t)b;
         atomicAdd(&len_hist[msm_len_bin(hi - lo)], 1u);
     }
 }
@@ -321,13 +478,21 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
             vs_store_acc(partial + t, S_);
             return false;
         }
-        uint32_t ent = entries[e++];
-        const Affine *pt = bases + (ent & 0x7fffffffu);
-        vs_set(S_, VS_QX, &pt->x);
-        if (ent >> 31)
-            vs_set_neg(S_, VS_QY, &pt->y);
-        else
-            vs_set(S_, VS_QY, &pt->y);
+        for (;;) {
+            uint32_t ent = entries[e++];
+            const Affine *pt = bases + (ent & 0x7fffffffu);
+            vs_set(S_, VS_QX, &pt->x);
+            if (ent >> 31)
+                vs_set_neg(S_, VS_QY, &pt->y);
+            else
+                vs_set(S_, VS_QY, &pt->y);
+            // (0,0) encodes infinity in the affine image (only an expanded copy of a 2-torsion point)
+            if (!(vs_is_zero(S_, VS_QX) && vs_is_zero(S_, VS_QY))) break;
+            if (e >= end) {
+                vs_store_acc(partial + t, S_);
+                return false;
+            }
+        }
         pc = VPC_MADD;
         return true;
     };
@@ -336,26 +501,24 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
     fqvm_run(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); });
 }
 
-// Buckets that were cut into several tasks: fold the partials into the first one.
+// Buckets that were cut into several tasks: pairwise tree fold of their partials into the
+// first one. Level j: partial[t] += partial[t + 2^j] for tasks whose index inside the bucket
+// is a multiple of 2^(j+1). log2(MSM_MAX_TASKS_PER_BUCKET) launches, one addition deep each.
 __global__ void __launch_bounds__(128, 2)
-k_fold(MsmPlan p, const uint32_t *task_off, XYZZ *partial)
+k_fold_level(uint32_t j, const uint32_t *n_tasks, const uint32_t *task_off, const uint32_t *task_bucket, XYZZ *partial)
 {
-    size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= p.n_buckets) return;
-    const uint32_t t0 = task_off[b], t1 = task_off[b + 1];
-    if (t1 - t0 < 2) return;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *n_tasks) return;
+    const uint32_t b = task_bucket[t];
+    const uint32_t t0 = task_off[b], nt = task_off[b + 1] - t0;
+    const uint32_t i = t - t0, step = 1u << j;
+    if ((i & (2 * step - 1)) != 0 || i + step >= nt) return;
     FqSlots S;
-    vs_load_acc(S, partial + t0);
-    uint32_t t = t0 + 1;
-    vs_load_q(S, partial + t);
-    fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
-        if (++t >= t1) {
-            vs_store_acc(partial + t0, S_);
-            return false;
-        }
-        vs_load_q(S_, partial + t);
-        pc = VPC_ADD;
-        return true;
+    vs_load_acc(S, partial + t);
+    vs_load_q(S, partial + t + step);
+    fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &, FqSlots &S_) {
+        vs_store_acc(partial + t, S_);
+        return false;
     });
 }
 
@@ -555,7 +718,7 @@ __global__ void __launch_bounds__(32, 1) k_final(MsmPlan p, const XYZZ *C, Proj 
 // ------------------------------------------------------------------ workspace
 struct MsmBuffers {
     int32_t *digits;
-    uint32_t *counts, *offsets, *cursor, *ntasks, *task_off, *task_start, *task_len, *order, *len_hist, *len_cursor,
+    uint32_t *counts, *offsets, *cursor, *ntasks, *task_off, *task_start, *task_len, *task_bucket, *order, *len_hist, *len_cursor,
         *entries, *scan_tmp;
     XYZZ *partial, *lvlA[2], *lvlC[2];
     Proj *result;
@@ -583,6 +746,7 @@ inline MsmBuffers msm_layout(const MsmPlan &p, uint8_t *base)
     b.task_off = (uint32_t *)take((nbk + 1) * 4);
     b.task_start = (uint32_t *)take(p.max_tasks * 4);
     b.task_len = (uint32_t *)take(p.max_tasks * 4);
+    b.task_bucket = (uint32_t *)take(p.max_tasks * 4);
     b.order = (uint32_t *)take(p.max_tasks * 4);
     b.len_hist = (uint32_t *)take((MSM_LEN_BINS + 2) * 4);
     b.len_cursor = (uint32_t *)take((MSM_LEN_BINS + 2) * 4);
@@ -607,12 +771,13 @@ inline MsmBuffers msm_layout(const MsmPlan &p, uint8_t *base)
 }
 
 // Number of kernel launches msm_launch issues for plan p.
-inline uint64_t msm_launch_count(const MsmPlan &p) { return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 1 + p.n_levels + 1; }
+inline uint64_t msm_launch_count(const MsmPlan &p) { return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 8 + p.n_levels + 1; }
 
 // Launch the whole MSM on `st`. d_bases: affine image (G copies of copy_stride points);
 // d_scalars: Fr Montgomery. Result (libff special form, 288 B) is left in buffers.result.
 inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affine *d_bases, const uint8_t *d_is_inf,
-                              const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, cudaStream_t st)
+                              const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, cudaStream_t st,
+                              cudaEvent_t acc_ev0 = nullptr, cudaEvent_t acc_ev1 = nullptr)
 {
     const uint32_t n = p.n;
     cudaMemsetAsync(b.counts, 0, (p.n_buckets + 1) * 4, st);
@@ -625,13 +790,16 @@ inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affin
     unsigned gb = (unsigned)((p.n_buckets + 255) / 256);
     k_task_count<<<gb, 256, 0, st>>>(p, b.counts, b.ntasks);
     exclusive_scan_u32(b.ntasks, p.n_buckets, b.task_off, b.scan_tmp, st);
-    k_task_fill<<<gb, 256, 0, st>>>(p, b.counts, b.offsets, b.task_off, b.task_start, b.task_len, b.len_hist);
+    k_task_fill<<<gb, 256, 0, st>>>(p, b.counts, b.offsets, b.task_off, b.task_start, b.task_len, b.task_bucket, b.len_hist);
     exclusive_scan_u32(b.len_hist, MSM_LEN_BINS + 1, b.len_cursor, b.scan_tmp, st);
     const uint32_t *n_tasks = b.task_off + p.n_buckets;
     k_task_order<<<(unsigned)((p.max_tasks + 255) / 256), 256, 0, st>>>(n_tasks, b.task_len, b.len_cursor, b.order);
+    if (acc_ev0) cudaEventRecord(acc_ev0, st);
     k_accumulate<<<(unsigned)((p.max_tasks + 127) / 128), 128, 0, st>>>(p, d_bases, n_tasks, b.order, b.task_start,
                                                                          b.task_len, b.entries, b.partial);
-    k_fold<<<(unsigned)((p.n_buckets + 127) / 128), 128, 0, st>>>(p, b.task_off, b.partial);
+    if (acc_ev1) cudaEventRecord(acc_ev1, st);
+    for (uint32_t j = 0; (1u << j) < MSM_MAX_TASKS_PER_BUCKET; j++)
+        k_fold_level<<<(unsigned)((p.max_tasks + 127) / 128), 128, 0, st>>>(j, n_tasks, b.task_off, b.task_bucket, b.partial);
     // reduction levels
     ReduceLevel r{};
     r.n_in = (uint32_t)p.n_buckets;

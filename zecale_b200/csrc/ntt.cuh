@@ -93,6 +93,36 @@ __global__ void k_fr_scale_table(Fr *a, const Fr *table, size_t n)
     fr_store(a + i, x);
 }
 
+// h[i] = (a[i]*b[i] - c[i]) * zinv   — the pointwise core of r1cs_to_qap_witness_map
+// (libsnark r1cs_to_qap.tcc:283-315: H_tmp = aA∘aB, -= aC, divide_by_Z_on_coset). In place in a.
+__global__ void k_qap_pointwise(Fr *a, const Fr *b, const Fr *c, const Fr *zinv, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t x[12], y[12], z[12];
+    fr_load(x, a + i);
+    fr_load(y, b + i);
+    fr_mul_regs(x, x, y);
+    fr_load(y, c + i);
+    fr_sub_regs(x, x, y);
+    fr_load(z, zinv);
+    fr_mul_regs(x, x, z);
+    fr_store(a + i, x);
+}
+
+// out = (g^(2^log_m) - 1)^-1 : the vanishing polynomial on the coset g*H is the constant
+// g^m - 1 (libfqfft basic_radix2_domain.tcc:103-126 compute_vanishing_polynomial / divide_by_Z_on_coset).
+__global__ void k_fr_zinv(Fr *out, Fr g, uint32_t log_m)
+{
+    uint32_t x[12], one[12];
+    fr_load(x, &g);
+    for (uint32_t i = 0; i < log_m; i++) fr_sqr_regs(x, x);
+    fr_set_const(one, FR_ONE);
+    fr_sub_regs(x, x, one);
+    fr_inv(x, x);
+    fr_store(out, x);
+}
+
 // ------------------------------------------------------------------ pass kernel
 struct NttPass {
     uint32_t logR;      // sub-transform length R = 2^logR

@@ -4,6 +4,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -35,9 +36,17 @@ struct zecale_gpu_ctx {
     std::mutex mu;
     std::string err;
     uint64_t launches = 0;
-    DevBuf ws_msm, ws_in, ws_sc, ws_idx, ws_ntt, ws_tmp;
+    DevBuf ws_msm, ws_in, ws_sc, ws_idx, ws_ntt, ws_tmp, ws_qap;
     int *d_status = nullptr;
     NttTables ntt;
+    // per-kernel-class timers (class 0: MSM bucket accumulation, class 1: NTT transforms)
+    std::vector<cudaEvent_t> ev_pool;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending[2];
+    uint32_t last_stats[2] = {0, 0}; // entries, tasks of the last MSM
+    MsmPlan last_plan{};
+    double kernel_ms[2] = {0, 0};
+    uint64_t kernel_n[2] = {0, 0};
+    std::map<std::pair<uint32_t, std::vector<uint32_t>>, Fr *> zinv; // (log_m, g) -> (g^m - 1)^-1
 };
 
 namespace {
@@ -71,6 +80,36 @@ int reserve(zecale_gpu_ctx *ctx, DevBuf &b, size_t bytes)
     CK(cudaMalloc(&b.p, want));
     b.cap = want;
     return 0;
+}
+
+cudaEvent_t take_event(zecale_gpu_ctx *ctx)
+{
+    if (!ctx->ev_pool.empty()) {
+        cudaEvent_t e = ctx->ev_pool.back();
+        ctx->ev_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+// Fold finished event pairs into the per-class totals (synchronises the stream).
+void drain_timers(zecale_gpu_ctx *ctx)
+{
+    cudaStreamSynchronize(ctx->stream);
+    for (int k = 0; k < 2; k++) {
+        for (auto &pr : ctx->ev_pending[k]) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) {
+                ctx->kernel_ms[k] += ms;
+                ctx->kernel_n[k]++;
+            }
+            ctx->ev_pool.push_back(pr.first);
+            ctx->ev_pool.push_back(pr.second);
+        }
+        ctx->ev_pending[k].clear();
+    }
 }
 
 int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n, Affine *d_out, uint8_t *d_inf)
@@ -113,10 +152,16 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
     if (rc) return rc;
     MsmBuffers b = msm_layout(plan, (uint8_t *)ctx->ws_msm.p);
     if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    CK(msm_launch(plan, b, d_bases, d_inf, d_scalars, sstride, d_index, ctx->stream));
+    cudaEvent_t a0 = take_event(ctx), a1 = take_event(ctx);
+    CK(msm_launch(plan, b, d_bases, d_inf, d_scalars, sstride, d_index, ctx->stream, a0, a1));
+    ctx->ev_pending[0].emplace_back(a0, a1);
+    if (ctx->ev_pending[0].size() > 256) drain_timers(ctx);
     ctx->launches += msm_launch_count(plan);
     if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
     CK(cudaMemcpyAsync(out_point, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&ctx->last_stats[0], b.offsets + plan.n_buckets, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&ctx->last_stats[1], b.task_off + plan.n_buckets, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->last_plan = plan;
     CK(cudaStreamSynchronize(ctx->stream));
     if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
     return 0;
@@ -171,6 +216,65 @@ int msm_host(zecale_gpu_ctx *ctx, const void *bases, size_t bstride, const void 
     return msm_device(ctx, d_aff, d_inf, 0, 0, (uint32_t)n, d_sc, sstride, d_idx, n, out, nullptr);
 }
 
+// NTT on a device vector, no locking, no sync; timed as kernel class 1.
+int ntt_device(zecale_gpu_ctx *ctx, Fr *d_a, unsigned log_m, unsigned flags, const Fr *coset_g)
+{
+    size_t m = (size_t)1 << log_m;
+    int rc = reserve(ctx, ctx->ws_ntt, m * sizeof(Fr));
+    if (rc) return rc;
+    unsigned nl = 0;
+    // tables are built (and synchronised) before the timed region
+    const Fr *tw = nullptr;
+    CK(ntt_get_twiddles(ctx->ntt, log_m, ctx->stream, &tw, &nl));
+    cudaEvent_t e0 = take_event(ctx), e1 = take_event(ctx);
+    CK(cudaEventRecord(e0, ctx->stream));
+    CK(ntt_launch(ctx->ntt, d_a, (Fr *)ctx->ws_ntt.p, log_m, flags, coset_g, ctx->stream, &nl));
+    CK(cudaEventRecord(e1, ctx->stream));
+    ctx->ev_pending[1].emplace_back(e0, e1);
+    if (ctx->ev_pending[1].size() > 256) drain_timers(ctx);
+    ctx->launches += nl;
+    return 0;
+}
+
+// (g^m - 1)^-1 on the device, cached per (log_m, g).
+int get_zinv(zecale_gpu_ctx *ctx, unsigned log_m, const Fr *g, const Fr **out)
+{
+    auto key = std::make_pair((uint32_t)log_m, std::vector<uint32_t>(g->l, g->l + 12));
+    auto it = ctx->zinv.find(key);
+    if (it != ctx->zinv.end()) {
+        *out = it->second;
+        return 0;
+    }
+    Fr *d = nullptr;
+    CK(cudaMalloc((void **)&d, sizeof(Fr)));
+    k_fr_zinv<<<1, 1, 0, ctx->stream>>>(d, *g, log_m);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    ctx->zinv[key] = d;
+    *out = d;
+    return 0;
+}
+
+// The device part of r1cs_to_qap_witness_map (libsnark r1cs_to_qap.tcc:252-330) for d1 = d2 = d3 = 0:
+// aA, aB, aC hold the evaluations <A_i,w>, <B_i,w>, <C_i,w> on the domain; on return aA holds
+// coefficients_for_H[0..m) (entry m is zero). aB and aC are clobbered.
+int qap_h_device(zecale_gpu_ctx *ctx, Fr *aA, Fr *aB, Fr *aC, unsigned log_m, const Fr *g)
+{
+    const size_t m = (size_t)1 << log_m;
+    const Fr *zinv = nullptr;
+    int rc = get_zinv(ctx, log_m, g, &zinv);
+    if (rc) return rc;
+    Fr *v[3] = {aA, aB, aC};
+    for (int k = 0; k < 3; k++) {
+        if ((rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_INVERSE, nullptr))) return rc;
+        if ((rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_COSET, g))) return rc;
+    }
+    k_qap_pointwise<<<(unsigned)((m + 255) / 256), 256, 0, ctx->stream>>>(aA, aB, aC, zinv, m);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    return ntt_device(ctx, aA, log_m, ZECALE_GPU_NTT_INVERSE | ZECALE_GPU_NTT_COSET, g);
+}
+
 // ------------------------------------------------------------------ test kernels
 __global__ void __launch_bounds__(64, 1) k_test_fq(int op, const Fq *a, const Fq *b, Fq *out, size_t n)
 {
@@ -179,9 +283,10 @@ __global__ void __launch_bounds__(64, 1) k_test_fq(int op, const Fq *a, const Fq
     FqSlots S;
     vs_set(S, VS_QX, a + i);
     vs_set(S, VS_QY, b ? b + i : a + i);
-    if (op == 4) { // inverse through the VM's Fermat loop; 0 -> 0
-        vs_set(S, VS_T2, a + i);
-        fqvm_run(S, VPC_INVPROD, [&](uint32_t, uint32_t &, FqSlots &) { return false; });
+    if (op == 4 || op == 7) { // inverse: 4 = binary Euclid (product path), 7 = Fermat ladder (cross-check); 0 -> 0
+        vs_set(S, VS_K1, a + i);
+        vs_set(S, VS_T1, a + i);
+        fqvm_run(S, op == 4 ? VPC_INVPROD : VPC_INV_FERMAT, [&](uint32_t, uint32_t &, FqSlots &) { return false; });
         vs_get(out + i, S, VS_T0);
         return;
     }
@@ -320,14 +425,14 @@ __global__ void __launch_bounds__(128, 2) k_bench_fq_mul(Fq *sink, unsigned iter
     x[23] &= 0xffffff;
     y[23] &= 0xffffff;
     vs_store(S, VS_ZZZ, x);
-    vs_store(S, VS_T2, y);
+    vs_store(S, VS_K1, y);
     unsigned k = 0;
     fqvm_run(S, VPC_PRODSTEP, [&](uint32_t, uint32_t &pc, FqSlots &) {
         pc = VPC_PRODSTEP;
         return ++k < iters;
     });
-    vs_load(x, S, VS_T2);
-    if (x[0] == 0x12345678u && x[5] == 77u) vs_get(sink, S, VS_T2); // keep the chain alive
+    vs_load(x, S, VS_K1);
+    if (x[0] == 0x12345678u && x[5] == 77u) vs_get(sink, S, VS_K1); // keep the chain alive
 }
 
 template <typename T>
@@ -407,9 +512,12 @@ void zecale_gpu_shutdown(zecale_gpu_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (DevBuf *b : {&ctx->ws_msm, &ctx->ws_in, &ctx->ws_sc, &ctx->ws_idx, &ctx->ws_ntt, &ctx->ws_tmp})
+    for (DevBuf *b : {&ctx->ws_msm, &ctx->ws_in, &ctx->ws_sc, &ctx->ws_idx, &ctx->ws_ntt, &ctx->ws_tmp, &ctx->ws_qap})
         if (b->p) cudaFree(b->p);
     ntt_tables_free(ctx->ntt);
+    drain_timers(ctx);
+    for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
+    for (auto &kv : ctx->zinv) cudaFree(kv.second);
     cudaFree(ctx->d_status);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
@@ -432,8 +540,20 @@ int zecale_gpu_msm_g2(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride
     return msm_host(ctx, bases, base_stride, scalars, scalar_stride, scalar_index, n, out_point);
 }
 
-int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
-                         zecale_gpu_bases **handle)
+// Window size for a fully expanded image (one bucket set): fewer windows as n grows, bucket
+// count 2^(c-1) kept near n/2 so the running-sum reduction stays a few percent of the work.
+static uint32_t pinned_c(size_t n)
+{
+    uint32_t lg = 0;
+    while ((2ull << lg) <= n) lg++;
+    uint32_t c = lg;
+    if (c < 8) c = 8;
+    if (c > 20) c = 20;
+    return c;
+}
+
+int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group, int expand,
+                            zecale_gpu_bases **handle)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -444,7 +564,26 @@ int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_str
     zecale_gpu_bases *h = new zecale_gpu_bases();
     h->n = n;
     h->group = group;
-    cudaError_t e = cudaMalloc((void **)&h->d, n * sizeof(Affine));
+    // choose the expansion: G copies 2^(c*V*g) P, limited by a memory budget (<= 1/3 of free HBM)
+    uint32_t c = 0, V = 0, G = 1;
+    if (expand) {
+        size_t free_b = 0, total_b = 0;
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        c = pinned_c(n);
+        const uint32_t W = (FR_SCALAR_BITS + 1 + c - 1) / c;
+        size_t max_copies = (free_b / 3) / (n * sizeof(Affine));
+        if (max_copies < 1) max_copies = 1;
+        V = 1;
+        while ((W + V - 1) / V > max_copies || (uint64_t)((W + V - 1) / V) * n >= (1ull << 31)) V++;
+        G = (W + V - 1) / V;
+        if (G == 1) { // nothing to expand: fall back to the default per-call plan
+            c = 0;
+            V = 0;
+        }
+    }
+    h->c = c;
+    h->V = V;
+    cudaError_t e = cudaMalloc((void **)&h->d, (size_t)G * n * sizeof(Affine));
     if (e == cudaSuccess) e = cudaMalloc((void **)&h->is_inf, n);
     if (e != cudaSuccess) {
         cudaFree(h->d);
@@ -452,6 +591,21 @@ int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_str
         return fail(ctx, ZECALE_GPU_E_NOMEM, "pin_bases: %s", cudaGetErrorString(e));
     }
     int rc = import_bases(ctx, bases, base_stride, n, h->d, h->is_inf);
+    if (rc == 0 && G > 1) {
+        rc = reserve(ctx, ctx->ws_tmp, n * (sizeof(XYZZ) + sizeof(Fq)));
+        if (rc == 0) {
+            XYZZ *sp = (XYZZ *)ctx->ws_tmp.p;
+            Fq *pf = (Fq *)(sp + n);
+            unsigned threads = (unsigned)((n + EXPAND_K - 1) / EXPAND_K);
+            for (uint32_t g = 1; g < G; g++) {
+                k_expand_copy<<<(threads + 127) / 128, 128, 0, ctx->stream>>>(h->d + (size_t)(g - 1) * n, h->d + (size_t)g * n,
+                                                                               (uint32_t)n, c * V, sp, pf);
+                ctx->launches++;
+            }
+            cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
+            if (e2 != cudaSuccess) rc = fail(ctx, ZECALE_GPU_E_CUDA, "pin_bases expand: %s", cudaGetErrorString(e2));
+        }
+    }
     if (rc) {
         cudaFree(h->d);
         cudaFree(h->is_inf);
@@ -460,6 +614,12 @@ int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_str
     }
     *handle = h;
     return 0;
+}
+
+int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
+                         zecale_gpu_bases **handle)
+{
+    return zecale_gpu_pin_bases_ex(ctx, bases, base_stride, n, group, 1, handle);
 }
 
 int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *h)
@@ -513,13 +673,9 @@ int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned 
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt: bad argument");
     if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt: log_m %u out of range", log_m);
     CK(cudaSetDevice(ctx->device));
-    size_t m = (size_t)1 << log_m;
-    int rc = reserve(ctx, ctx->ws_ntt, m * sizeof(Fr));
-    if (rc) return rc;
     if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    unsigned nl = 0;
-    CK(ntt_launch(ctx->ntt, (Fr *)d_a, (Fr *)ctx->ws_ntt.p, log_m, flags, (const Fr *)coset_g, ctx->stream, &nl));
-    ctx->launches += nl;
+    int rc = ntt_device(ctx, (Fr *)d_a, log_m, flags, (const Fr *)coset_g);
+    if (rc) return rc;
     if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
@@ -529,23 +685,106 @@ int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned 
 int zecale_gpu_ntt(zecale_gpu_ctx *ctx, void *a, unsigned log_m, unsigned flags, const void *coset_g)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
-    if (!a) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt: null vector");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!a || (flags & ~3u) || ((flags & ZECALE_GPU_NTT_COSET) && !coset_g))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt: bad argument");
     if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt: log_m %u out of range", log_m);
     size_t bytes = ((size_t)1 << log_m) * sizeof(Fr);
-    void *d = nullptr;
-    {
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        CK(cudaSetDevice(ctx->device));
-        int rc = reserve(ctx, ctx->ws_in, bytes);
-        if (rc) return rc;
-        d = ctx->ws_in.p;
-        CK(cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    }
-    int rc = zecale_gpu_ntt_dev(ctx, d, log_m, flags, coset_g, nullptr);
+    CK(cudaSetDevice(ctx->device));
+    int rc = reserve(ctx, ctx->ws_in, bytes);
     if (rc) return rc;
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    void *d = ctx->ws_in.p;
+    CK(cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    rc = ntt_device(ctx, (Fr *)d, log_m, flags, (const Fr *)coset_g);
+    if (rc) return rc;
     CK(cudaMemcpyAsync(a, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int zecale_gpu_qap_h_dev(zecale_gpu_ctx *ctx, void *d_aA, void *d_aB, void *d_aC, unsigned log_m, const void *coset_g,
+                         float *elapsed_ms)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!d_aA || !d_aB || !d_aC || !coset_g) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_h: bad argument");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_qap_h: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    int rc = qap_h_device(ctx, (Fr *)d_aA, (Fr *)d_aB, (Fr *)d_aC, log_m, (const Fr *)coset_g);
+    if (rc) return rc;
+    if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    return 0;
+}
+
+int zecale_gpu_qap_h(zecale_gpu_ctx *ctx, const void *aA, const void *aB, const void *aC, unsigned log_m,
+                     const void *coset_g, void *out_h)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!aA || !aB || !aC || !coset_g || !out_h) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_h: bad argument");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_qap_h: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    const size_t m = (size_t)1 << log_m, bytes = m * sizeof(Fr);
+    int rc = reserve(ctx, ctx->ws_qap, 3 * bytes);
+    if (rc) return rc;
+    Fr *d = (Fr *)ctx->ws_qap.p;
+    CK(cudaMemcpyAsync(d, aA, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d + m, aB, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d + 2 * m, aC, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    memset((char *)out_h + bytes, 0, sizeof(Fr)); // coefficients_for_H[m] = 0 when d1 = d2 = d3 = 0
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t n, void *out_points)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!out_points || !n || n >= (1ull << 31) || (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_synth_bases: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    int rc = reserve(ctx, ctx->ws_tmp, n * sizeof(Proj));
+    if (rc) return rc;
+    k_synth_bases<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(group, seed, (uint32_t)n, (Proj *)ctx->ws_tmp.p);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_points, ctx->ws_tmp.p, n * sizeof(Proj), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int zecale_gpu_kernel_ms(zecale_gpu_ctx *ctx, int kernel_class, int reset, double *total_ms, uint64_t *count)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (kernel_class < 0 || kernel_class > 1) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_kernel_ms: bad class");
+    CK(cudaSetDevice(ctx->device));
+    drain_timers(ctx);
+    if (total_ms) *total_ms = ctx->kernel_ms[kernel_class];
+    if (count) *count = ctx->kernel_n[kernel_class];
+    if (reset) {
+        ctx->kernel_ms[kernel_class] = 0;
+        ctx->kernel_n[kernel_class] = 0;
+    }
+    return 0;
+}
+
+int zecale_gpu_msm_last_stats(zecale_gpu_ctx *ctx, uint64_t *entries, uint64_t *tasks, unsigned *c, unsigned *bucket_sets,
+                              unsigned *base_copies)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (entries) *entries = ctx->last_stats[0];
+    if (tasks) *tasks = ctx->last_stats[1];
+    if (c) *c = ctx->last_plan.c;
+    if (bucket_sets) *bucket_sets = ctx->last_plan.V;
+    if (base_copies) *base_copies = ctx->last_plan.G;
     return 0;
 }
 
