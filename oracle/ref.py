@@ -36,6 +36,7 @@ class Ref:
                   "zref_session_setup", "zref_session_prove_stock"):
             getattr(L, f).restype = _d
         L.zref_fr_signed_digit.restype = ctypes.c_long
+        L.zref_session_abc.restype = ctypes.c_long
         L.zref_optimal_c.restype = _sz
         self.L = L
         self.threads = L.zref_init()
@@ -169,6 +170,14 @@ class Ref:
             assert self.L.zref_session_csr(k, _p(rp), _p(col), _p(val)) == 0
             out["csr_" + name] = (rp, col, val)
         return out
+
+    def session_abc(self):
+        """(aA, aB, aC): the evaluation vectors of r1cs_to_qap_witness_map before its first transform."""
+        m = self.session_sizes()["m"]
+        v = [np.zeros((m, 6), dtype=np.uint64) for _ in range(3)]
+        got = self.L.zref_session_abc(_p(v[0]), _p(v[1]), _p(v[2]))
+        assert got == m, (got, m)
+        return v
 
     def session_prove(self, r, s, chunks=0):
         z = self.session_sizes()

@@ -711,6 +711,33 @@ extern "C" int zref_session_csr(int which, uint64_t *row_ptr, uint32_t *col, voi
     return 0;
 }
 
+// The evaluation vectors r1cs_to_qap_witness_map builds before its first transform
+// (r1cs_to_qap.tcc:224-248, 293-296): aA[i] = <A_i, w>, aB[i] = <B_i, w>, aC[i] = <C_i, w> for
+// i < num_constraints, aA[num_constraints + i] = (1, primary...)[i], zero padded to the
+// power-of-two domain. Each buffer holds m Fr; returns m.
+extern "C" long zref_session_abc(void *aA_, void *aB_, void *aC_)
+{
+    if (!S.have_keys)
+        return -1;
+    const auto &cs = S.kp_ptr->pk.constraint_system;
+    const std::shared_ptr<libfqfft::evaluation_domain<Fr>> domain =
+        libfqfft::get_evaluation_domain<Fr>(1ull << libff::log2(cs.num_constraints() + cs.num_inputs() + 1));
+    std::vector<Fr> full = S.primary;
+    full.insert(full.end(), S.aux.begin(), S.aux.end());
+    std::vector<Fr> aA(domain->m, Fr::zero()), aB(domain->m, Fr::zero()), aC(domain->m, Fr::zero());
+    for (size_t i = 0; i <= cs.num_inputs(); ++i)
+        aA[i + cs.num_constraints()] = (i > 0 ? full[i - 1] : Fr::one());
+    for (size_t i = 0; i < cs.num_constraints(); ++i) {
+        aA[i] += cs.constraints[i].a.evaluate(full);
+        aB[i] += cs.constraints[i].b.evaluate(full);
+        aC[i] += cs.constraints[i].c.evaluate(full);
+    }
+    copy_out(aA_, aA);
+    copy_out(aB_, aB);
+    copy_out(aC_, aC);
+    return (long)domain->m;
+}
+
 // Reference prove with fixed (r, s). Outputs: 576 proof bytes, the five MSM
 // results in special form (At, Bt.g, Bt.h, Ht, Lt: 5 x 288 B) and
 // coefficients_for_H (m+1 Fr). timings[6] = witness map, A, B, H, L, total.
