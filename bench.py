@@ -168,38 +168,55 @@ class Workload:
         self.d_abc0 = [t.cuda() for t in self.t_abc]
         self.d_abc = [torch.empty_like(t) for t in self.d_abc0]
         self.d_idx = torch.from_numpy(self.b_index.view(np.int64)).cuda()
+        self.t_hout = torch.empty(((1 << LOG_M) + 1, 6), dtype=torch.int64).pin_memory()
+        self.h_out = self.t_hout.numpy().view(np.uint64)
         torch.cuda.synchronize()
         self.last = None
 
     def step_resident(self):
-        """One proof's device work with every input already in HBM."""
+        """One proof's device work with every input already in HBM: the H polynomial and the H MSM
+        on lane 0, the four witness MSMs on lanes 1-4, one synchronisation."""
         ctx = self.ctx
-        for dst, src in zip(self.d_abc, self.d_abc0):
-            dst.copy_(src)
-        self.torch.cuda.current_stream().synchronize()
-        ctx.qap_h_dev(self.d_abc[0].data_ptr(), self.d_abc[1].data_ptr(), self.d_abc[2].data_ptr(), LOG_M, self.g)
-        w = self.d_w.data_ptr()
-        out = [ctx.msm_pinned_dev(self.pk["A"], w, N_A)[0],
-               ctx.msm_pinned_dev(self.pk["B2"], w, N_B, d_index_ptr=self.d_idx.data_ptr())[0],
-               ctx.msm_pinned_dev(self.pk["B1"], w, N_B, d_index_ptr=self.d_idx.data_ptr())[0],
-               ctx.msm_pinned_dev(self.pk["H"], self.d_abc[0].data_ptr(), N_H)[0],
-               ctx.msm_pinned_dev(self.pk["L"], w + 48 * (N_INPUTS + 1), N_L)[0]]
+        out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
+        w, idx = self.d_w.data_ptr(), self.d_idx.data_ptr()
+        ctx.qap_h_async(0, self.d_abc0[0].data_ptr(), self.d_abc0[1].data_ptr(), self.d_abc0[2].data_ptr(), self.g,
+                        log_m=LOG_M)
+        ctx.msm_pinned_async(1, self.pk["A"], w, out[0], n=N_A, device=True)
+        ctx.msm_pinned_async(2, self.pk["L"], w + 48 * (N_INPUTS + 1), out[4], n=N_L, device=True)
+        ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=idx, device=True)
+        ctx.msm_pinned_async(4, self.pk["B1"], w, out[2], n=N_B, index=idx, device=True)
+        ctx.msm_pinned_async(0, self.pk["H"], None, out[3], n=N_H, from_qap=True)
+        ctx.sync()
         self.last = out
         return out
 
     def step_e2e(self):
-        """The same proof through the host-pointer C ABI (what the hooked reference calls)."""
+        """The same proof from HOST buffers (pinned): what a hooked prover passes in. The witness
+        crosses PCIe once (shared by A, B, L), aA/aB/aC once, coefficients_for_H come back."""
+        ctx = self.ctx
+        out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
+        w = self.h_w
+        ctx.qap_h_async(0, self.h_abc[0], self.h_abc[1], self.h_abc[2], self.g, out=self.h_out)
+        ctx.msm_pinned_async(1, self.pk["A"], w, out[0], n=N_A)
+        ctx.msm_pinned_async(2, self.pk["L"], w[N_INPUTS + 1:], out[4], n=N_L)
+        ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=self.b_index)
+        ctx.msm_pinned_async(4, self.pk["B1"], w, out[2], n=N_B, index=self.b_index)
+        ctx.msm_pinned_async(0, self.pk["H"], None, out[3], n=N_H, from_qap=True)
+        ctx.sync()
+        return out
+
+    def step_blocking(self):
+        """Strict drop-in sequence: one blocking C-ABI call per reference call site, host buffers."""
         ctx = self.ctx
         h = ctx.qap_h(self.h_abc[0], self.h_abc[1], self.h_abc[2], self.g)
         w = self.h_w
-        out = [ctx.msm_pinned(self.pk["A"], w, n=N_A),
-               ctx.msm_pinned(self.pk["B2"], w, index=self.b_index, n=N_B),
-               ctx.msm_pinned(self.pk["B1"], w, index=self.b_index, n=N_B),
-               ctx.msm_pinned(self.pk["H"], h, n=N_H),
-               ctx.msm_pinned(self.pk["L"], w[N_INPUTS + 1:], n=N_L)]
-        return out
+        return [ctx.msm_pinned(self.pk["A"], w, n=N_A),
+                ctx.msm_pinned(self.pk["B2"], w, index=self.b_index, n=N_B),
+                ctx.msm_pinned(self.pk["B1"], w, index=self.b_index, n=N_B),
+                ctx.msm_pinned(self.pk["H"], h, n=N_H),
+                ctx.msm_pinned(self.pk["L"], w[N_INPUTS + 1:], n=N_L)]
 
-    E2E_H2D = 3 * (1 << LOG_M) * 48 + 4 * N_A * 48 + N_H * 48 + 2 * N_B * 8
+    E2E_H2D = 3 * (1 << LOG_M) * 48 + N_A * 48 + N_B * 8
     E2E_D2H = ((1 << LOG_M)) * 48 + 5 * 288
 
     def algorithmic_madds(self):

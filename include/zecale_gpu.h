@@ -131,6 +131,25 @@ int zecale_gpu_qap_h(zecale_gpu_ctx *ctx, const void *aA, const void *aB, const 
 int zecale_gpu_qap_h_dev(zecale_gpu_ctx *ctx, void *d_aA, void *d_aB, void *d_aC, unsigned log_m,
                          const void *coset_g, float *elapsed_ms);
 
+/* ---- asynchronous lanes ------------------------------------------------------------
+ * The MSMs of one proof are data-independent (r1cs_gg_ppzksnark.tcc:531-580) and only the H
+ * MSM waits for the H polynomial. A context owns zecale_gpu_lane_count() in-order lanes
+ * (stream + scratch); the *_async calls enqueue on a lane and return, zecale_gpu_sync waits
+ * for all lanes and then writes every out_point / out_h. Host buffers passed to an async call
+ * must stay valid and unchanged until zecale_gpu_sync returns. Blocking calls use lane 0. */
+enum {
+    ZECALE_GPU_DEVICE_POINTERS = 1u, /* scalars / scalar_index are device pointers (index: u64)      */
+    ZECALE_GPU_SCALARS_FROM_QAP = 2u /* scalars = coefficients_for_H of the last qap_h on this lane */
+};
+int zecale_gpu_lane_count(void);
+int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_bases *handle, const void *scalars,
+                                size_t scalar_stride, const void *scalar_index, size_t n, void *out_point,
+                                unsigned flags);
+/* out_h may be NULL when the coefficients are only consumed by ZECALE_GPU_SCALARS_FROM_QAP. */
+int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const void *aB, const void *aC,
+                           unsigned log_m, const void *coset_g, void *out_h);
+int zecale_gpu_sync(zecale_gpu_ctx *ctx);
+
 /* ---- synthetic inputs (bench / tests): out_points[i] = k_i * generator of the group, in
  * libff special form (288 B each), k_i a non-zero 32-bit hash of (seed, i). HOST pointer. */
 int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t n, void *out_points);

@@ -121,3 +121,37 @@ def test_msm_rejects_non_special(gpu, ref):
     with pytest.raises(z.ZecaleGpuError) as e:
         gpu.msm_g1(bad, ref.fr_rng(1, 8))
     assert e.value.code == 3
+
+
+def test_async_lanes_match_blocking_calls(gpu, ref):
+    """The prover-shaped use of the lanes: H polynomial + H MSM on one lane, witness MSMs on others
+    (shared witness uploaded once), results identical to the blocking calls and to libff."""
+    import bw6_constants as C
+    m, n = 1 << 12, 3000
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    aA, aB, aC = (ref.fr_rng(31 * k, m) for k in (1, 2, 3))
+    w = ref.fr_rng(99, n)
+    bases = {k: ref.bases_mul(ref.fr_rng(1000 + k, n if k < 2 else m - 1), 1) for k in range(3)}
+    pins = {k: gpu.pin_bases(v) for k, v in bases.items()}
+    idx = np.sort(np.random.default_rng(1).choice(n, 700, replace=False)).astype(np.uint64)
+    try:
+        h_exp, _ = ref.qap_h(aA, aB, aC)
+        exp = [ref.msm(bases[0], w, 1)[0], ref.msm(bases[1][10:], w[10:], 1)[0],
+               ref.msm(bases[2], h_exp[: m - 1], 1)[0], ref.msm(bases[0][:700], np.ascontiguousarray(w[idx]), 1)[0]]
+        out = [np.zeros(36, dtype=np.uint64) for _ in range(4)]
+        h_out = np.zeros((m + 1, 6), dtype=np.uint64)
+        for _ in range(2):  # second round reuses the staging buffers
+            gpu.qap_h_async(0, aA, aB, aC, g, out=h_out)
+            gpu.msm_pinned_async(1, pins[0], w, out[0])
+            p1 = gpu.pin_bases(bases[1][10:])
+            gpu.msm_pinned_async(2, p1, w[10:], out[1])
+            gpu.msm_pinned_async(3, pins[0], w, out[3], n=700, index=idx)
+            gpu.msm_pinned_async(0, pins[2], None, out[2], from_qap=True)
+            gpu.sync()
+            p1.release()
+            assert np.array_equal(h_out, h_exp)
+            for k in range(4):
+                assert np.array_equal(out[k], exp[k]), k
+    finally:
+        for p in pins.values():
+            p.release()

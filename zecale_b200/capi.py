@@ -51,6 +51,10 @@ EXPORTS = {
     "zecale_gpu_ntt_dev": (_i, [_vp, _vp, _u, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
     "zecale_gpu_qap_h": (_i, [_vp, _vp, _vp, _vp, _u, _vp, _vp]),
     "zecale_gpu_qap_h_dev": (_i, [_vp, _vp, _vp, _vp, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_lane_count": (_i, []),
+    "zecale_gpu_msm_pinned_async": (_i, [_vp, _i, _vp, _vp, _sz, _vp, _sz, _vp, _u]),
+    "zecale_gpu_qap_h_async": (_i, [_vp, _i, _vp, _vp, _vp, _u, _vp, _vp]),
+    "zecale_gpu_sync": (_i, [_vp]),
     "zecale_gpu_synth_bases": (_i, [_vp, _i, ctypes.c_uint64, _sz, _vp]),
     "zecale_gpu_kernel_ms": (_i, [_vp, _i, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]),
     "zecale_gpu_launch_count": (ctypes.c_uint64, [_vp]),
@@ -202,6 +206,29 @@ class Context:
         self._ck(_lib.zecale_gpu_qap_h_dev(self._h, ctypes.c_void_p(d_aA), ctypes.c_void_p(d_aB), ctypes.c_void_p(d_aC),
                                            log_m, _ptr(coset_g), ctypes.byref(ms)))
         return ms.value
+
+    # -- asynchronous lanes -----------------------------------------------------------
+    def msm_pinned_async(self, lane, pinned, scalars, out, n=None, index=None, device=False, from_qap=False):
+        """Enqueue an MSM on `lane`; `out` (uint64[36]) is filled by sync(). scalars/index: numpy arrays
+        (kept alive by the caller until sync) or raw device pointers when device=True."""
+        n = pinned.n if n is None else int(n)
+        flags = (1 if device else 0) | (2 if from_qap else 0)
+        if from_qap:
+            sp, ip, stride = None, None, 48
+        elif device:
+            sp, ip, stride = ctypes.c_void_p(scalars), (ctypes.c_void_p(index) if index else None), 48
+        else:
+            sp, ip, stride = _ptr(scalars), _ptr(index), scalars.strides[0]
+        self._ck(_lib.zecale_gpu_msm_pinned_async(self._h, lane, pinned.handle, sp, stride, ip, n, _ptr(out), flags))
+
+    def qap_h_async(self, lane, aA, aB, aC, coset_g, out=None, log_m=None):
+        """aA/aB/aC: numpy arrays, or raw pointers (host or device) with log_m given."""
+        if log_m is None:
+            log_m = aA.shape[0].bit_length() - 1
+        self._ck(_lib.zecale_gpu_qap_h_async(self._h, lane, _ptr(aA), _ptr(aB), _ptr(aC), log_m, _ptr(coset_g), _ptr(out)))
+
+    def sync(self):
+        self._ck(_lib.zecale_gpu_sync(self._h))
 
     def synth_bases(self, n, group=G1, seed=0):
         out = np.zeros((n, 36), dtype=np.uint64)

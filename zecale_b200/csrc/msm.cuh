@@ -37,6 +37,7 @@ namespace zecale {
 static constexpr int FR_SCALAR_BITS = 377;
 static constexpr int MSM_MAX_LEVELS = 24;
 static constexpr uint32_t MSM_MAX_TASKS_PER_BUCKET = 256;
+static constexpr uint64_t MSM_TARGET_TASKS = 4ull * 148 * 3 * 128;
 
 struct MsmPlan {
     uint32_t n;            // (base, scalar) pairs
@@ -74,8 +75,13 @@ inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_s
     p.G = (p.W + p.V - 1) / p.V;
     p.NB = 1u << (c - 1);
     p.copy_stride = copy_stride;
+    // Task length: ~4 waves of the 148 SM x 3 CTA x 128 thread accumulate grid, so that the
+    // length-sorted tasks balance across SMs; never more than twice the mean bucket size.
     uint64_t avg = ((uint64_t)n * p.W + (uint64_t)p.V * p.NB - 1) / ((uint64_t)p.V * p.NB);
-    p.S = (uint32_t)(avg * 2 < 16 ? 16 : avg * 2);
+    uint64_t S = ((uint64_t)n * p.W + MSM_TARGET_TASKS - 1) / MSM_TARGET_TASKS;
+    if (S > 2 * avg) S = 2 * avg;
+    if (S < 8) S = 8;
+    p.S = (uint32_t)S;
     p.n_buckets = (uint64_t)p.V * p.NB;
     p.max_tasks = ((uint64_t)n * p.W) / p.S + p.n_buckets + 1;
     uint32_t rem = c - 1;

@@ -28,25 +28,53 @@ struct zecale_gpu_bases {
     uint32_t c = 0, V = 0;    // window bits / bucket sets the image was expanded for (V = 0: not expanded)
 };
 
+// One in-order work queue of the context: a stream, its scratch buffers and the pinned
+// staging area results are read back into. Lane 0 serves the blocking entry points; the
+// *_async entry points let the caller put independent MSMs / the H polynomial on different
+// lanes so that one MSM's latency-bound tail overlaps another's bucket accumulation.
+static constexpr int ZECALE_GPU_LANES = 6;
+struct Lane {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    DevBuf ws_msm, ws_sc, ws_idx, ws_ntt, ws_qap;
+    struct Staging {
+        Proj result;
+        uint32_t stats[2];
+    } *h = nullptr;              // pinned
+    void *user_out = nullptr;    // where h->result goes at the next sync (async MSM)
+    void *user_h = nullptr;      // async qap_h: host destination ...
+    size_t user_h_bytes = 0;     // ... and its size (a zero Fr is appended)
+    uint32_t last_stats[2] = {0, 0};
+    MsmPlan last_plan{};
+};
+
 struct zecale_gpu_ctx {
     int device = 0;
     std::vector<int> devices;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    Lane lanes[ZECALE_GPU_LANES];
+    Lane *cur = nullptr;
     std::mutex mu;
     std::string err;
     uint64_t launches = 0;
-    DevBuf ws_msm, ws_in, ws_sc, ws_idx, ws_ntt, ws_tmp, ws_qap;
+    DevBuf ws_in, ws_tmp;        // import / test scratch (lane 0 only)
     int *d_status = nullptr;
     NttTables ntt;
     // per-kernel-class timers (class 0: MSM bucket accumulation, class 1: NTT transforms)
     std::vector<cudaEvent_t> ev_pool;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending[2];
-    uint32_t last_stats[2] = {0, 0}; // entries, tasks of the last MSM
-    MsmPlan last_plan{};
     double kernel_ms[2] = {0, 0};
     uint64_t kernel_n[2] = {0, 0};
     std::map<std::pair<uint32_t, std::vector<uint32_t>>, Fr *> zinv; // (log_m, g) -> (g^m - 1)^-1
+    // host scalar vectors uploaded since the last zecale_gpu_sync: the prover passes the same
+    // assignment to A, B and L (r1cs_gg_ppzksnark.tcc:531-580), so it crosses PCIe once
+    struct EpochUpload {
+        const char *host;
+        size_t bytes;
+        int buf;
+        cudaEvent_t ev;
+    };
+    std::vector<EpochUpload> uploads;
+    DevBuf up_pool[8];
 };
 
 namespace {
@@ -95,9 +123,41 @@ cudaEvent_t take_event(zecale_gpu_ctx *ctx)
 }
 
 // Fold finished event pairs into the per-class totals (synchronises the stream).
+// Wait for every lane and deliver the results of asynchronous calls to the caller's buffers.
+int sync_lanes(zecale_gpu_ctx *ctx)
+{
+    int rc = 0;
+    for (Lane &L : ctx->lanes) {
+        if (!L.stream) continue;
+        cudaError_t e = cudaStreamSynchronize(L.stream);
+        if (e != cudaSuccess && rc == 0)
+            rc = fail(ctx, ZECALE_GPU_E_CUDA, "stream synchronize: %s", cudaGetErrorString(e));
+        if (L.user_out) {
+            if (e == cudaSuccess) {
+                memcpy(L.user_out, &L.h->result, sizeof(Proj));
+                L.last_stats[0] = L.h->stats[0];
+                L.last_stats[1] = L.h->stats[1];
+            }
+            L.user_out = nullptr;
+        }
+        if (&L == &ctx->lanes[ZECALE_GPU_LANES - 1]) {
+            for (auto &u : ctx->uploads) ctx->ev_pool.push_back(u.ev);
+            ctx->uploads.clear();
+        }
+        if (L.user_h) {
+            if (e == cudaSuccess) {
+                cudaMemcpy(L.user_h, L.ws_qap.p, L.user_h_bytes, cudaMemcpyDeviceToHost);
+                memset((char *)L.user_h + L.user_h_bytes, 0, sizeof(Fr));
+            }
+            L.user_h = nullptr;
+        }
+    }
+    return rc;
+}
+
 void drain_timers(zecale_gpu_ctx *ctx)
 {
-    cudaStreamSynchronize(ctx->stream);
+    sync_lanes(ctx);
     for (int k = 0; k < 2; k++) {
         for (auto &pr : ctx->ev_pending[k]) {
             float ms = 0.f;
@@ -118,14 +178,14 @@ int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n
     size_t raw = (n - 1) * stride + sizeof(Proj);
     int rc = reserve(ctx, ctx->ws_in, raw);
     if (rc) return rc;
-    CK(cudaMemcpyAsync(ctx->ws_in.p, bases, raw, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->stream));
-    k_import_special<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>((const uint8_t *)ctx->ws_in.p, stride,
+    CK(cudaMemcpyAsync(ctx->ws_in.p, bases, raw, cudaMemcpyHostToDevice, ctx->cur->stream));
+    CK(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->cur->stream));
+    k_import_special<<<(unsigned)((n + 127) / 128), 128, 0, ctx->cur->stream>>>((const uint8_t *)ctx->ws_in.p, stride,
                                                                             (uint32_t)n, d_out, d_inf, ctx->d_status);
     ctx->launches++;
     int st = 0;
-    CK(cudaMemcpyAsync(&st, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpyAsync(&st, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->cur->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
     if (st & 1) return fail(ctx, ZECALE_GPU_E_FORM, "MSM base not in special form (Z must be one or zero)");
     return 0;
 }
@@ -133,7 +193,7 @@ int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n
 // d_bases: affine image on device; scalars: device pointer. Result -> host out (288 B).
 int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf, uint32_t c, uint32_t V,
                uint32_t copy_stride, const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, size_t n,
-               void *out_point, float *elapsed_ms)
+               void *out_point, float *elapsed_ms, bool nosync = false)
 {
     if (n == 0) {
         // empty sum = zero point (0, one, 0), as libff::multi_exp returns GroupT::zero()
@@ -146,24 +206,35 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
         if (elapsed_ms) *elapsed_ms = 0.f;
         return 0;
     }
+    if (ctx->cur->user_out || ctx->cur->user_h) { // an asynchronous result of this lane is still undelivered
+        int rc0 = sync_lanes(ctx);
+        if (rc0) return rc0;
+    }
     MsmPlan plan = msm_make_plan((uint32_t)n, c ? c : msm_default_c((uint32_t)n), V, copy_stride);
     MsmBuffers lay = msm_layout(plan, nullptr);
-    int rc = reserve(ctx, ctx->ws_msm, lay.total);
+    int rc = reserve(ctx, ctx->cur->ws_msm, lay.total);
     if (rc) return rc;
-    MsmBuffers b = msm_layout(plan, (uint8_t *)ctx->ws_msm.p);
-    if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    MsmBuffers b = msm_layout(plan, (uint8_t *)ctx->cur->ws_msm.p);
+    if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev0, ctx->cur->stream));
     cudaEvent_t a0 = take_event(ctx), a1 = take_event(ctx);
-    CK(msm_launch(plan, b, d_bases, d_inf, d_scalars, sstride, d_index, ctx->stream, a0, a1));
+    CK(msm_launch(plan, b, d_bases, d_inf, d_scalars, sstride, d_index, ctx->cur->stream, a0, a1));
     ctx->ev_pending[0].emplace_back(a0, a1);
     if (ctx->ev_pending[0].size() > 256) drain_timers(ctx);
     ctx->launches += msm_launch_count(plan);
-    if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    CK(cudaMemcpyAsync(out_point, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(&ctx->last_stats[0], b.offsets + plan.n_buckets, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(&ctx->last_stats[1], b.task_off + plan.n_buckets, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    ctx->last_plan = plan;
-    CK(cudaStreamSynchronize(ctx->stream));
-    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev1, ctx->cur->stream));
+    Lane &L = *ctx->cur;
+    CK(cudaMemcpyAsync(&L.h->result, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, L.stream));
+    CK(cudaMemcpyAsync(&L.h->stats[0], b.offsets + plan.n_buckets, 4, cudaMemcpyDeviceToHost, L.stream));
+    CK(cudaMemcpyAsync(&L.h->stats[1], b.task_off + plan.n_buckets, 4, cudaMemcpyDeviceToHost, L.stream));
+    L.last_plan = plan;
+    L.user_out = out_point;
+    if (nosync) return 0;
+    CK(cudaStreamSynchronize(L.stream));
+    memcpy(out_point, &L.h->result, sizeof(Proj));
+    L.last_stats[0] = L.h->stats[0];
+    L.last_stats[1] = L.h->stats[1];
+    L.user_out = nullptr;
+    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, L.ev0, L.ev1));
     return 0;
 }
 
@@ -179,17 +250,17 @@ int upload_scalars(zecale_gpu_ctx *ctx, const void *scalars, size_t sstride, con
         n_sc = mx + 1;
     }
     size_t bytes = (n_sc - 1) * sstride + sizeof(Fr);
-    int rc = reserve(ctx, ctx->ws_sc, bytes);
+    int rc = reserve(ctx, ctx->cur->ws_sc, bytes);
     if (rc) return rc;
-    CK(cudaMemcpyAsync(ctx->ws_sc.p, scalars, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    *d_sc = (const uint8_t *)ctx->ws_sc.p;
+    CK(cudaMemcpyAsync(ctx->cur->ws_sc.p, scalars, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+    *d_sc = (const uint8_t *)ctx->cur->ws_sc.p;
     *d_idx = nullptr;
     if (index) {
         static_assert(sizeof(size_t) == 8, "size_t");
-        rc = reserve(ctx, ctx->ws_idx, n * 8);
+        rc = reserve(ctx, ctx->cur->ws_idx, n * 8);
         if (rc) return rc;
-        CK(cudaMemcpyAsync(ctx->ws_idx.p, index, n * 8, cudaMemcpyHostToDevice, ctx->stream));
-        *d_idx = (const uint64_t *)ctx->ws_idx.p;
+        CK(cudaMemcpyAsync(ctx->cur->ws_idx.p, index, n * 8, cudaMemcpyHostToDevice, ctx->cur->stream));
+        *d_idx = (const uint64_t *)ctx->cur->ws_idx.p;
     }
     return 0;
 }
@@ -199,6 +270,7 @@ int msm_host(zecale_gpu_ctx *ctx, const void *bases, size_t bstride, const void 
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!out || (n && (!bases || !scalars)) || bstride < sizeof(Proj) || sstride < sizeof(Fr) || n >= (1ull << 26))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm: bad argument");
     CK(cudaSetDevice(ctx->device));
@@ -220,16 +292,16 @@ int msm_host(zecale_gpu_ctx *ctx, const void *bases, size_t bstride, const void 
 int ntt_device(zecale_gpu_ctx *ctx, Fr *d_a, unsigned log_m, unsigned flags, const Fr *coset_g)
 {
     size_t m = (size_t)1 << log_m;
-    int rc = reserve(ctx, ctx->ws_ntt, m * sizeof(Fr));
+    int rc = reserve(ctx, ctx->cur->ws_ntt, m * sizeof(Fr));
     if (rc) return rc;
     unsigned nl = 0;
     // tables are built (and synchronised) before the timed region
     const Fr *tw = nullptr;
-    CK(ntt_get_twiddles(ctx->ntt, log_m, ctx->stream, &tw, &nl));
+    CK(ntt_get_twiddles(ctx->ntt, log_m, ctx->cur->stream, &tw, &nl));
     cudaEvent_t e0 = take_event(ctx), e1 = take_event(ctx);
-    CK(cudaEventRecord(e0, ctx->stream));
-    CK(ntt_launch(ctx->ntt, d_a, (Fr *)ctx->ws_ntt.p, log_m, flags, coset_g, ctx->stream, &nl));
-    CK(cudaEventRecord(e1, ctx->stream));
+    CK(cudaEventRecord(e0, ctx->cur->stream));
+    CK(ntt_launch(ctx->ntt, d_a, (Fr *)ctx->cur->ws_ntt.p, log_m, flags, coset_g, ctx->cur->stream, &nl));
+    CK(cudaEventRecord(e1, ctx->cur->stream));
     ctx->ev_pending[1].emplace_back(e0, e1);
     if (ctx->ev_pending[1].size() > 256) drain_timers(ctx);
     ctx->launches += nl;
@@ -247,9 +319,10 @@ int get_zinv(zecale_gpu_ctx *ctx, unsigned log_m, const Fr *g, const Fr **out)
     }
     Fr *d = nullptr;
     CK(cudaMalloc((void **)&d, sizeof(Fr)));
-    k_fr_zinv<<<1, 1, 0, ctx->stream>>>(d, *g, log_m);
+    k_fr_zinv<<<1, 1, 0, ctx->cur->stream>>>(d, *g, log_m);
     ctx->launches++;
     CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->cur->stream)); // other lanes may read it right away
     ctx->zinv[key] = d;
     *out = d;
     return 0;
@@ -269,7 +342,7 @@ int qap_h_device(zecale_gpu_ctx *ctx, Fr *aA, Fr *aB, Fr *aC, unsigned log_m, co
         if ((rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_INVERSE, nullptr))) return rc;
         if ((rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_COSET, g))) return rc;
     }
-    k_qap_pointwise<<<(unsigned)((m + 255) / 256), 256, 0, ctx->stream>>>(aA, aB, aC, zinv, m);
+    k_qap_pointwise<<<(unsigned)((m + 255) / 256), 256, 0, ctx->cur->stream>>>(aA, aB, aC, zinv, m);
     ctx->launches++;
     CK(cudaGetLastError());
     return ntt_device(ctx, aA, log_m, ZECALE_GPU_NTT_INVERSE | ZECALE_GPU_NTT_COSET, g);
@@ -441,19 +514,20 @@ int test_elementwise(zecale_gpu_ctx *ctx, void (*launch)(int, const T *, const T
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!a || !out || !n) return fail(ctx, ZECALE_GPU_E_ARG, "test hook: bad argument");
     CK(cudaSetDevice(ctx->device));
     size_t bytes = n * sizeof(T);
     int rc = reserve(ctx, ctx->ws_tmp, bytes * 3);
     if (rc) return rc;
     T *da = (T *)ctx->ws_tmp.p, *db = da + n, *dout = db + n;
-    CK(cudaMemcpyAsync(da, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    if (b) CK(cudaMemcpyAsync(db, b, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    launch(op, da, b ? db : nullptr, dout, n, ctx->stream);
+    CK(cudaMemcpyAsync(da, a, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+    if (b) CK(cudaMemcpyAsync(db, b, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+    launch(op, da, b ? db : nullptr, dout, n, ctx->cur->stream);
     ctx->launches++;
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(out, dout, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpyAsync(out, dout, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
     return 0;
 }
 
@@ -497,10 +571,14 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
         delete ctx;
         return ZECALE_GPU_E_CUDA; // sm_100a only: no fallback path
     }
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
-        cudaMalloc((void **)&ctx->d_status, sizeof(int)) != cudaSuccess) {
-        delete ctx;
+    bool ok = cudaMalloc((void **)&ctx->d_status, sizeof(int)) == cudaSuccess;
+    for (Lane &L : ctx->lanes)
+        ok = ok && cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreate(&L.ev0) == cudaSuccess && cudaEventCreate(&L.ev1) == cudaSuccess &&
+             cudaMallocHost((void **)&L.h, sizeof(Lane::Staging)) == cudaSuccess;
+    ctx->cur = &ctx->lanes[0];
+    if (!ok) {
+        zecale_gpu_shutdown(ctx);
         return ZECALE_GPU_E_CUDA;
     }
     *out = ctx;
@@ -511,17 +589,24 @@ void zecale_gpu_shutdown(zecale_gpu_ctx *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
-    for (DevBuf *b : {&ctx->ws_msm, &ctx->ws_in, &ctx->ws_sc, &ctx->ws_idx, &ctx->ws_ntt, &ctx->ws_tmp, &ctx->ws_qap})
-        if (b->p) cudaFree(b->p);
-    ntt_tables_free(ctx->ntt);
+    ctx->cur = &ctx->lanes[0];
     drain_timers(ctx);
+    for (Lane &L : ctx->lanes) {
+        for (DevBuf *b : {&L.ws_msm, &L.ws_sc, &L.ws_idx, &L.ws_ntt, &L.ws_qap})
+            if (b->p) cudaFree(b->p);
+        if (L.h) cudaFreeHost(L.h);
+        if (L.ev0) cudaEventDestroy(L.ev0);
+        if (L.ev1) cudaEventDestroy(L.ev1);
+        if (L.stream) cudaStreamDestroy(L.stream);
+    }
+    for (DevBuf *b : {&ctx->ws_in, &ctx->ws_tmp})
+        if (b->p) cudaFree(b->p);
+    for (DevBuf &b : ctx->up_pool)
+        if (b.p) cudaFree(b.p);
+    ntt_tables_free(ctx->ntt);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     for (auto &kv : ctx->zinv) cudaFree(kv.second);
-    cudaFree(ctx->d_status);
-    cudaEventDestroy(ctx->ev0);
-    cudaEventDestroy(ctx->ev1);
-    cudaStreamDestroy(ctx->stream);
+    if (ctx->d_status) cudaFree(ctx->d_status);
     delete ctx;
 }
 
@@ -557,6 +642,7 @@ int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!bases || !handle || !n || base_stride < sizeof(Proj) || n >= (1ull << 26) ||
         (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_pin_bases: bad argument");
@@ -598,11 +684,11 @@ int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_
             Fq *pf = (Fq *)(sp + n);
             unsigned threads = (unsigned)((n + EXPAND_K - 1) / EXPAND_K);
             for (uint32_t g = 1; g < G; g++) {
-                k_expand_copy<<<(threads + 127) / 128, 128, 0, ctx->stream>>>(h->d + (size_t)(g - 1) * n, h->d + (size_t)g * n,
+                k_expand_copy<<<(threads + 127) / 128, 128, 0, ctx->cur->stream>>>(h->d + (size_t)(g - 1) * n, h->d + (size_t)g * n,
                                                                                (uint32_t)n, c * V, sp, pf);
                 ctx->launches++;
             }
-            cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
+            cudaError_t e2 = cudaStreamSynchronize(ctx->cur->stream);
             if (e2 != cudaSuccess) rc = fail(ctx, ZECALE_GPU_E_CUDA, "pin_bases expand: %s", cudaGetErrorString(e2));
         }
     }
@@ -626,8 +712,9 @@ int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *h)
 {
     if (!ctx || !h) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    cudaStreamSynchronize(ctx->cur->stream);
     cudaFree(h->d);
     cudaFree(h->is_inf);
     delete h;
@@ -639,6 +726,7 @@ int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, const 
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!h || !out_point || n > h->n || (n && !scalars) || scalar_stride < sizeof(Fr))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned: bad argument");
     CK(cudaSetDevice(ctx->device));
@@ -657,6 +745,7 @@ int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, co
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!h || !out_point || n > h->n || (n && !d_scalars) || scalar_stride < sizeof(Fr))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: bad argument");
     CK(cudaSetDevice(ctx->device));
@@ -669,16 +758,17 @@ int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned 
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!d_a || (flags & ~3u) || ((flags & ZECALE_GPU_NTT_COSET) && !coset_g))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt: bad argument");
     if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt: log_m %u out of range", log_m);
     CK(cudaSetDevice(ctx->device));
-    if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev0, ctx->cur->stream));
     int rc = ntt_device(ctx, (Fr *)d_a, log_m, flags, (const Fr *)coset_g);
     if (rc) return rc;
-    if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev1, ctx->cur->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
+    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->cur->ev0, ctx->cur->ev1));
     return 0;
 }
 
@@ -686,6 +776,7 @@ int zecale_gpu_ntt(zecale_gpu_ctx *ctx, void *a, unsigned log_m, unsigned flags,
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!a || (flags & ~3u) || ((flags & ZECALE_GPU_NTT_COSET) && !coset_g))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt: bad argument");
     if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt: log_m %u out of range", log_m);
@@ -694,11 +785,11 @@ int zecale_gpu_ntt(zecale_gpu_ctx *ctx, void *a, unsigned log_m, unsigned flags,
     int rc = reserve(ctx, ctx->ws_in, bytes);
     if (rc) return rc;
     void *d = ctx->ws_in.p;
-    CK(cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
     rc = ntt_device(ctx, (Fr *)d, log_m, flags, (const Fr *)coset_g);
     if (rc) return rc;
-    CK(cudaMemcpyAsync(a, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpyAsync(a, d, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
     return 0;
 }
 
@@ -707,15 +798,16 @@ int zecale_gpu_qap_h_dev(zecale_gpu_ctx *ctx, void *d_aA, void *d_aB, void *d_aC
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!d_aA || !d_aB || !d_aC || !coset_g) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_h: bad argument");
     if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_qap_h: log_m %u out of range", log_m);
     CK(cudaSetDevice(ctx->device));
-    if (elapsed_ms) CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev0, ctx->cur->stream));
     int rc = qap_h_device(ctx, (Fr *)d_aA, (Fr *)d_aB, (Fr *)d_aC, log_m, (const Fr *)coset_g);
     if (rc) return rc;
-    if (elapsed_ms) CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev1, ctx->cur->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
+    if (elapsed_ms) CK(cudaEventElapsedTime(elapsed_ms, ctx->cur->ev0, ctx->cur->ev1));
     return 0;
 }
 
@@ -724,38 +816,154 @@ int zecale_gpu_qap_h(zecale_gpu_ctx *ctx, const void *aA, const void *aB, const 
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!aA || !aB || !aC || !coset_g || !out_h) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_h: bad argument");
     if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_qap_h: log_m %u out of range", log_m);
     CK(cudaSetDevice(ctx->device));
     const size_t m = (size_t)1 << log_m, bytes = m * sizeof(Fr);
-    int rc = reserve(ctx, ctx->ws_qap, 3 * bytes);
+    int rc = reserve(ctx, ctx->cur->ws_qap, 3 * bytes);
     if (rc) return rc;
-    Fr *d = (Fr *)ctx->ws_qap.p;
-    CK(cudaMemcpyAsync(d, aA, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemcpyAsync(d + m, aB, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemcpyAsync(d + 2 * m, aC, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    Fr *d = (Fr *)ctx->cur->ws_qap.p;
+    CK(cudaMemcpyAsync(d, aA, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+    CK(cudaMemcpyAsync(d + m, aB, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+    CK(cudaMemcpyAsync(d + 2 * m, aC, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
     rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
     if (rc) return rc;
-    CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
     memset((char *)out_h + bytes, 0, sizeof(Fr)); // coefficients_for_H[m] = 0 when d1 = d2 = d3 = 0
-    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
     return 0;
+}
+
+int zecale_gpu_lane_count(void) { return ZECALE_GPU_LANES; }
+
+// Device copy of the host byte range [host, host+bytes) for the current lane: reuses an upload
+// made earlier in this epoch (any lane) if it covers the range, else uploads on this lane.
+static int epoch_upload(zecale_gpu_ctx *ctx, const void *host, size_t bytes, const uint8_t **d_out)
+{
+    const char *h = (const char *)host;
+    for (auto &u : ctx->uploads)
+        if (h >= u.host && h + bytes <= u.host + u.bytes) {
+            CK(cudaStreamWaitEvent(ctx->cur->stream, u.ev, 0));
+            *d_out = (const uint8_t *)ctx->up_pool[u.buf].p + (h - u.host);
+            return 0;
+        }
+    if (ctx->uploads.size() >= 8) return 1; // pool exhausted: caller falls back to a lane-private upload
+    int slot = (int)ctx->uploads.size();
+    int rc = reserve(ctx, ctx->up_pool[slot], bytes);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(ctx->up_pool[slot].p, host, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+    cudaEvent_t ev = take_event(ctx);
+    CK(cudaEventRecord(ev, ctx->cur->stream));
+    ctx->uploads.push_back({h, bytes, slot, ev});
+    *d_out = (const uint8_t *)ctx->up_pool[slot].p;
+    return 0;
+}
+
+int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_bases *h, const void *scalars,
+                                size_t scalar_stride, const void *scalar_index, size_t n, void *out_point, unsigned flags)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (lane < 0 || lane >= ZECALE_GPU_LANES || !h || !out_point || !n || n > h->n || (flags & ~3u) ||
+        (!(flags & ZECALE_GPU_SCALARS_FROM_QAP) && (!scalars || scalar_stride < sizeof(Fr))))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_async: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    ctx->cur = &ctx->lanes[lane];
+    const uint8_t *d_sc = (const uint8_t *)scalars;
+    const uint64_t *d_idx = (const uint64_t *)scalar_index;
+    if (flags & ZECALE_GPU_SCALARS_FROM_QAP) {
+        if (!ctx->cur->ws_qap.p) return fail(ctx, ZECALE_GPU_E_ARG, "msm_pinned_async: no H polynomial on this lane");
+        d_sc = (const uint8_t *)ctx->cur->ws_qap.p;
+        scalar_stride = sizeof(Fr);
+        d_idx = nullptr;
+    } else if (!(flags & ZECALE_GPU_DEVICE_POINTERS)) {
+        if (ctx->cur->user_out || ctx->cur->user_h) { // the staging buffers of this lane are still in flight
+            int rc0 = sync_lanes(ctx);
+            if (rc0) return rc0;
+        }
+        const size_t *idx = (const size_t *)scalar_index;
+        size_t n_sc = n;
+        if (idx) {
+            size_t mx = 0;
+            for (size_t i = 0; i < n; i++)
+                if (idx[i] > mx) mx = idx[i];
+            n_sc = mx + 1;
+        }
+        int rc = epoch_upload(ctx, scalars, (n_sc - 1) * scalar_stride + sizeof(Fr), &d_sc);
+        if (rc == 1) rc = upload_scalars(ctx, scalars, scalar_stride, nullptr, n_sc, &d_sc, &d_idx);
+        if (rc) return rc;
+        d_idx = nullptr;
+        if (idx) {
+            const uint8_t *d_i = nullptr;
+            rc = epoch_upload(ctx, idx, n * 8, &d_i);
+            if (rc == 1) {
+                rc = reserve(ctx, ctx->cur->ws_idx, n * 8);
+                if (rc == 0) {
+                    CK(cudaMemcpyAsync(ctx->cur->ws_idx.p, idx, n * 8, cudaMemcpyHostToDevice, ctx->cur->stream));
+                    d_i = (const uint8_t *)ctx->cur->ws_idx.p;
+                }
+            }
+            if (rc) return rc;
+            d_idx = (const uint64_t *)d_i;
+        }
+    }
+    return msm_device(ctx, h->d, h->is_inf, h->c, h->V, (uint32_t)h->n, d_sc, scalar_stride, d_idx, n, out_point, nullptr,
+                      true);
+}
+
+int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const void *aB, const void *aC, unsigned log_m,
+                           const void *coset_g, void *out_h)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (lane < 0 || lane >= ZECALE_GPU_LANES || !aA || !aB || !aC || !coset_g)
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_h_async: bad argument");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_qap_h: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    ctx->cur = &ctx->lanes[lane];
+    if (ctx->cur->user_out || ctx->cur->user_h) {
+        int rc0 = sync_lanes(ctx);
+        if (rc0) return rc0;
+    }
+    const size_t m = (size_t)1 << log_m, bytes = m * sizeof(Fr);
+    int rc = reserve(ctx, ctx->cur->ws_qap, 3 * bytes);
+    if (rc) return rc;
+    Fr *d = (Fr *)ctx->cur->ws_qap.p;
+    // cudaMemcpyDefault: the three vectors may be host or device memory
+    CK(cudaMemcpyAsync(d, aA, bytes, cudaMemcpyDefault, ctx->cur->stream));
+    CK(cudaMemcpyAsync(d + m, aB, bytes, cudaMemcpyDefault, ctx->cur->stream));
+    CK(cudaMemcpyAsync(d + 2 * m, aC, bytes, cudaMemcpyDefault, ctx->cur->stream));
+    rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
+    if (rc) return rc;
+    ctx->cur->user_h = out_h; // may be NULL: the coefficients then only feed ZECALE_GPU_SCALARS_FROM_QAP
+    ctx->cur->user_h_bytes = bytes;
+    return 0;
+}
+
+int zecale_gpu_sync(zecale_gpu_ctx *ctx)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    return sync_lanes(ctx);
 }
 
 int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t n, void *out_points)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!out_points || !n || n >= (1ull << 31) || (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_synth_bases: bad argument");
     CK(cudaSetDevice(ctx->device));
     int rc = reserve(ctx, ctx->ws_tmp, n * sizeof(Proj));
     if (rc) return rc;
-    k_synth_bases<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(group, seed, (uint32_t)n, (Proj *)ctx->ws_tmp.p);
+    k_synth_bases<<<(unsigned)((n + 127) / 128), 128, 0, ctx->cur->stream>>>(group, seed, (uint32_t)n, (Proj *)ctx->ws_tmp.p);
     ctx->launches++;
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(out_points, ctx->ws_tmp.p, n * sizeof(Proj), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpyAsync(out_points, ctx->ws_tmp.p, n * sizeof(Proj), cudaMemcpyDeviceToHost, ctx->cur->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
     return 0;
 }
 
@@ -763,6 +971,7 @@ int zecale_gpu_kernel_ms(zecale_gpu_ctx *ctx, int kernel_class, int reset, doubl
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (kernel_class < 0 || kernel_class > 1) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_kernel_ms: bad class");
     CK(cudaSetDevice(ctx->device));
     drain_timers(ctx);
@@ -780,11 +989,12 @@ int zecale_gpu_msm_last_stats(zecale_gpu_ctx *ctx, uint64_t *entries, uint64_t *
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
-    if (entries) *entries = ctx->last_stats[0];
-    if (tasks) *tasks = ctx->last_stats[1];
-    if (c) *c = ctx->last_plan.c;
-    if (bucket_sets) *bucket_sets = ctx->last_plan.V;
-    if (base_copies) *base_copies = ctx->last_plan.G;
+    ctx->cur = &ctx->lanes[0];
+    if (entries) *entries = ctx->cur->last_stats[0];
+    if (tasks) *tasks = ctx->cur->last_stats[1];
+    if (c) *c = ctx->cur->last_plan.c;
+    if (bucket_sets) *bucket_sets = ctx->cur->last_plan.V;
+    if (base_copies) *base_copies = ctx->cur->last_plan.G;
     return 0;
 }
 
@@ -809,17 +1019,18 @@ int zecale_gpu_bench_fq_mul(zecale_gpu_ctx *ctx, unsigned blocks, unsigned tpb, 
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
     if (!blocks || !tpb || tpb > 128 || !elapsed_ms || !iters) return fail(ctx, ZECALE_GPU_E_ARG, "bench_fq_mul: bad argument");
     CK(cudaSetDevice(ctx->device));
     int rc = reserve(ctx, ctx->ws_tmp, sizeof(Fq));
     if (rc) return rc;
-    k_bench_fq_mul<<<blocks, tpb, 0, ctx->stream>>>((Fq *)ctx->ws_tmp.p, 8); // warm-up
-    CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    k_bench_fq_mul<<<blocks, tpb, 0, ctx->stream>>>((Fq *)ctx->ws_tmp.p, iters);
-    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    k_bench_fq_mul<<<blocks, tpb, 0, ctx->cur->stream>>>((Fq *)ctx->ws_tmp.p, 8); // warm-up
+    CK(cudaEventRecord(ctx->cur->ev0, ctx->cur->stream));
+    k_bench_fq_mul<<<blocks, tpb, 0, ctx->cur->stream>>>((Fq *)ctx->ws_tmp.p, iters);
+    CK(cudaEventRecord(ctx->cur->ev1, ctx->cur->stream));
     ctx->launches += 2;
-    CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
+    CK(cudaEventElapsedTime(elapsed_ms, ctx->cur->ev0, ctx->cur->ev1));
     return 0;
 }
 
