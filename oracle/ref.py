@@ -12,12 +12,14 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REF_SO = os.path.join(_HERE, "_ref", "libzecale_ref.so")
 REF_AGG_SO = os.path.join(_HERE, "_ref", "libzecale_ref_agg.so")
+# ref-agg compiled with -include zecale_gpu_hooks.hpp: the reference prover running on the GPU (drop-in demo)
+REF_HOOKED_SO = os.path.join(_HERE, "_ref", "libzecale_ref_hooked.so")
 
 _vp, _sz, _u64, _d, _i = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint64, ctypes.c_double, ctypes.c_int
 
 
-def available(aggregator=False):
-    return os.path.exists(REF_AGG_SO if aggregator else REF_SO)
+def available(aggregator=False, hooked=False):
+    return os.path.exists(REF_HOOKED_SO if hooked else REF_AGG_SO if aggregator else REF_SO)
 
 
 def _p(a):
@@ -27,8 +29,8 @@ def _p(a):
 class Ref:
     """One loaded copy of the reference. Use aggregator=True for the zecale circuit."""
 
-    def __init__(self, aggregator=False):
-        path = REF_AGG_SO if aggregator else REF_SO
+    def __init__(self, aggregator=False, hooked=False):
+        path = REF_HOOKED_SO if hooked else REF_AGG_SO if aggregator else REF_SO
         if not os.path.exists(path):
             raise FileNotFoundError(path + " (run `make -C oracle ref ref-agg` where /root/reference exists)")
         L = ctypes.CDLL(path)
@@ -196,6 +198,16 @@ class Ref:
 
     def session_prove_stock(self):
         return self.L.zref_session_prove_stock()
+
+    # ---- hooked build only ------------------------------------------------------------
+    def is_hooked(self):
+        return bool(self.L.zref_is_hooked())
+
+    def hooks_pin_pk(self):
+        return self.L.zref_hooks_pin_pk()
+
+    def hooks_unpin(self):
+        return self.L.zref_hooks_unpin()
 
 
 def ints_to_limbs(vals, n64):

@@ -811,3 +811,44 @@ extern "C" double zref_session_prove_stock(void)
     return snark::verify(S.primary, proof, S.kp_ptr->vk) ? (t1 - t0) : -2.0;
 }
 
+
+// ---------------------------------------------------------------- hooked build
+// When this file is compiled with `-include zecale_gpu_hooks.hpp` (make ref-hooked) every
+// multi_exp / kc_multi_exp / evaluation-domain call above — including the ones inside the
+// unmodified r1cs_gg_ppzksnark_prover behind zref_session_prove_stock — runs on the GPU through
+// libzecale_gpu.so. That build is the drop-in demonstration, not an oracle.
+extern "C" int zref_is_hooked(void)
+{
+#ifdef ZECALE_GPU_HOOKS_HPP
+    return 1;
+#else
+    return 0;
+#endif
+}
+
+extern "C" int zref_hooks_pin_pk(void)
+{
+#ifdef ZECALE_GPU_HOOKS_HPP
+    if (!S.have_keys)
+        return -1;
+    try {
+        zecale_gpu_hooks::pin_proving_key(S.kp_ptr->pk);
+    } catch (const std::exception &e) {
+        std::cerr << "zref_hooks_pin_pk: " << e.what() << std::endl;
+        return 1;
+    }
+    return 0;
+#else
+    return -3;
+#endif
+}
+
+extern "C" int zref_hooks_unpin(void)
+{
+#ifdef ZECALE_GPU_HOOKS_HPP
+    zecale_gpu_hooks::unpin_all();
+    return 0;
+#else
+    return -3;
+#endif
+}
