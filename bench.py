@@ -30,6 +30,9 @@ import time
 
 import numpy as np
 
+# one hardware work queue per CUDA stream: the library runs up to 12 streams per proof in flight
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -134,13 +137,16 @@ class ClockSampler:
 class Workload:
     """Synthetic batch-8 proving key image + witness, on one GPU."""
 
-    def __init__(self, device, seed=1):
+    def __init__(self, device, seed=1, depth=2):
         import torch
         import zecale_b200 as z
         self.torch, self.z = torch, z
         self.dev = device
         torch.cuda.set_device(device)
-        self.ctx = z.Context(device)
+        # `depth` proofs are kept in flight, each on its own context (= its own lanes, streams and
+        # scratch); the pinned proving key is shared by all of them
+        self.ctxs = [z.Context(device) for _ in range(max(1, depth))]
+        self.ctx = self.ctxs[0]
         rng = np.random.default_rng(seed)
         ctx = self.ctx
         # proving-key queries: distinct curve points, pinned (device-resident) once, like a loaded pk
@@ -168,15 +174,43 @@ class Workload:
         self.d_abc0 = [t.cuda() for t in self.t_abc]
         self.d_abc = [torch.empty_like(t) for t in self.d_abc0]
         self.d_idx = torch.from_numpy(self.b_index.view(np.int64)).cuda()
-        self.t_hout = torch.empty(((1 << LOG_M) + 1, 6), dtype=torch.int64).pin_memory()
-        self.h_out = self.t_hout.numpy().view(np.uint64)
+        self.t_hout = [torch.empty(((1 << LOG_M) + 1, 6), dtype=torch.int64).pin_memory() for _ in self.ctxs]
+        self.h_out = [t.numpy().view(np.uint64) for t in self.t_hout]
         torch.cuda.synchronize()
         self.last = None
+        self.results = [None] * len(self.ctxs)
+
+    def run(self, steps, mode):
+        """`steps` proofs, `len(self.ctxs)` of them in flight: proof i is enqueued on context i mod
+        depth as soon as proof i - depth (same context) has delivered its results. Returns the
+        results of the last proof."""
+        enqueue = self.enqueue_resident if mode == "resident" else self.enqueue_e2e
+        d = len(self.ctxs)
+        for i in range(steps):
+            k = i % d
+            if self.results[k] is not None:
+                self.ctxs[k].sync()
+            self.results[k] = enqueue(k)
+        last = None
+        for j in range(steps, steps + d):     # drain in issue order
+            k = j % d
+            if self.results[k] is not None:
+                self.ctxs[k].sync()
+                last = self.results[k]
+                self.results[k] = None
+        self.last = last
+        return last
 
     def step_resident(self):
+        return self.run(1, "resident")
+
+    def step_e2e(self):
+        return self.run(1, "e2e")
+
+    def enqueue_resident(self, slot=0):
         """One proof's device work with every input already in HBM: the H polynomial and the H MSM
-        on lane 0, the four witness MSMs on lanes 1-4, one synchronisation."""
-        ctx = self.ctx
+        on lane 0, the four witness MSMs on lanes 1-4; results are delivered by the context's sync."""
+        ctx = self.ctxs[slot]
         out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
         w, idx = self.d_w.data_ptr(), self.d_idx.data_ptr()
         ctx.qap_h_async(0, self.d_abc0[0].data_ptr(), self.d_abc0[1].data_ptr(), self.d_abc0[2].data_ptr(), self.g,
@@ -186,23 +220,20 @@ class Workload:
         ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=idx, device=True)
         ctx.msm_pinned_async(4, self.pk["B1"], w, out[2], n=N_B, index=idx, device=True)
         ctx.msm_pinned_async(0, self.pk["H"], None, out[3], n=N_H, from_qap=True)
-        ctx.sync()
-        self.last = out
         return out
 
-    def step_e2e(self):
+    def enqueue_e2e(self, slot=0):
         """The same proof from HOST buffers (pinned): what a hooked prover passes in. The witness
         crosses PCIe once (shared by A, B, L), aA/aB/aC once, coefficients_for_H come back."""
-        ctx = self.ctx
+        ctx = self.ctxs[slot]
         out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
         w = self.h_w
-        ctx.qap_h_async(0, self.h_abc[0], self.h_abc[1], self.h_abc[2], self.g, out=self.h_out)
+        ctx.qap_h_async(0, self.h_abc[0], self.h_abc[1], self.h_abc[2], self.g, out=self.h_out[slot])
         ctx.msm_pinned_async(1, self.pk["A"], w, out[0], n=N_A)
         ctx.msm_pinned_async(2, self.pk["L"], w[N_INPUTS + 1:], out[4], n=N_L)
         ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=self.b_index)
         ctx.msm_pinned_async(4, self.pk["B1"], w, out[2], n=N_B, index=self.b_index)
         ctx.msm_pinned_async(0, self.pk["H"], None, out[3], n=N_H, from_qap=True)
-        ctx.sync()
         return out
 
     def step_blocking(self):
@@ -242,7 +273,19 @@ class Workload:
     def close(self):
         for p in self.pk.values():
             p.release()
-        self.ctx.close()
+        for c in self.ctxs:
+            c.close()
+
+    def kernel_ms(self, kernel_class):
+        ms, n = 0.0, 0
+        for c in self.ctxs:
+            a, b = c.kernel_ms(kernel_class)
+            ms += a
+            n += b
+        return ms, n
+
+    def launch_count(self):
+        return sum(c.launch_count() for c in self.ctxs)
 
 
 def measured_peaks():
@@ -269,7 +312,7 @@ def run_b200(args, rank, world, local_rank):
     import torch.distributed as dist
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    wl = Workload(local_rank, seed=1 + rank)
+    wl = Workload(local_rank, seed=1 + rank, depth=args.depth)
     ctx = wl.ctx
 
     def barrier():
@@ -279,19 +322,17 @@ def run_b200(args, rank, world, local_rank):
         torch.cuda.synchronize()
 
     # ---- device-resident arm (value)
-    for _ in range(args.warmup):
-        wl.step_resident()
-    ctx.kernel_ms(0)
-    ctx.kernel_ms(1)
-    launches0 = ctx.launch_count()
+    wl.run(args.warmup, "resident")
+    wl.kernel_ms(0)
+    wl.kernel_ms(1)
+    launches0 = wl.launch_count()
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        wl.step_resident()   # every library call synchronises its own stream before returning
+    wl.run(args.steps, "resident")   # returns after every context has synchronised its lanes
     torch.cuda.synchronize()
     ev1.record()
     barrier()
@@ -301,17 +342,15 @@ def run_b200(args, rank, world, local_rank):
     # torch events above enclose it; keep the larger of the two clocks to be safe
     t_res = max(t_res, wall_res) if t_res < 0.5 * wall_res else t_res
     clocks = sampler.stop()
-    launches = ctx.launch_count() - launches0
-    acc_ms, acc_n = ctx.kernel_ms(0)
-    ntt_ms, ntt_n = ctx.kernel_ms(1)
+    launches = wl.launch_count() - launches0
+    acc_ms, acc_n = wl.kernel_ms(0)
+    ntt_ms, ntt_n = wl.kernel_ms(1)
 
     # ---- end-to-end arm (host pointers)
-    for _ in range(max(1, min(args.warmup, 2))):
-        wl.step_e2e()
+    wl.run(max(1, min(args.warmup, 2)), "e2e")
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        wl.step_e2e()
+    wl.run(args.steps, "e2e")
     torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
     barrier()
@@ -350,6 +389,7 @@ def run_b200(args, rank, world, local_rank):
             "config": {"workload": "batch-8 aggregator Groth16 prove hot path: H-poly (7 NTT, m=2^18) + MSM A/B(G2,G1)/H/L",
                        "msm_sizes": {"A": N_A, "B_g2": N_B, "B_g1": N_B, "H": N_H, "L": N_L}, "ntt_log_m": LOG_M,
                        "parallelism": "replicas (one proof stream per GPU)" if world > 1 else "single GPU",
+                       "proofs_in_flight": args.depth,
                        "l2": "inputs larger than L2 (158 MB of bases per step)"},
             "e2e": {"value": world * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": Workload.E2E_H2D,
                     "d2h_bytes_per_step": Workload.E2E_D2H},
@@ -455,6 +495,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--depth", type=int, default=2, help="proofs kept in flight per GPU (1 = strictly one at a time)")
     ap.add_argument("--skip-msm20", action="store_true")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -196,6 +196,16 @@ class Ref:
         rc = self.L.zref_session_assemble(_p(r), _p(s), _p(np.ascontiguousarray(msm5)), _p(proof))
         return proof, rc == 0
 
+    def session_assignment(self):
+        n = self.session_sizes()["num_variables"] + 1
+        a = np.zeros((n, 6), dtype=np.uint64)
+        assert self.L.zref_session_get(7, _p(a)) == 0
+        return a
+
+    def session_set_assignment(self, full):
+        full = np.ascontiguousarray(full)
+        return self.L.zref_session_set_assignment(_p(full), _sz(full.shape[0]))
+
     def session_prove_stock(self):
         return self.L.zref_session_prove_stock()
 

@@ -852,3 +852,16 @@ extern "C" int zref_hooks_unpin(void)
     return -3;
 #endif
 }
+
+// Replace the session's witness with `full` = [1, primary..., aux...] (num_variables + 1 Fr), as
+// exported by zref_session_get(7): lets two builds of this harness prove the same statement even
+// though nested-proof generation draws from std::random_device. Returns 0 if it satisfies the cs.
+extern "C" int zref_session_set_assignment(const void *full, size_t count)
+{
+    if (!S.have_cs || count != S.cs.num_variables() + 1)
+        return -1;
+    const Fr *f = (const Fr *)full;
+    S.primary.assign(f + 1, f + 1 + S.cs.num_inputs());
+    S.aux.assign(f + 1 + S.cs.num_inputs(), f + count);
+    return S.cs.is_satisfied(S.primary, S.aux) ? 0 : 1;
+}

@@ -24,6 +24,8 @@ def _same_session(cpu, hooked, make):
     for lib in (cpu, hooked):
         assert make(lib) == 0
         lib.session_setup(9)
+    # same statement in both builds (nested-proof generation is randomised inside the reference)
+    assert hooked.session_set_assignment(cpu.session_assignment()) == 0
     r = cpu.fr_rng(0xC0FFEE, 1)[0]
     s = cpu.fr_rng(0xBEEF, 1)[0]
     exp = cpu.session_prove(r, s)

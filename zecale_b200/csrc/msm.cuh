@@ -37,7 +37,8 @@ namespace zecale {
 static constexpr int FR_SCALAR_BITS = 377;
 static constexpr int MSM_MAX_LEVELS = 24;
 static constexpr uint32_t MSM_MAX_TASKS_PER_BUCKET = 256;
-static constexpr uint64_t MSM_TARGET_TASKS = 4ull * 148 * 3 * 128;
+static constexpr uint64_t MSM_TARGET_TASKS = 3ull * 148 * 3 * 128;
+static constexpr uint32_t MSM_INLINE_FOLD = 4; // buckets cut into <= 4 tasks are folded inside k_reduce_level
 
 struct MsmPlan {
     uint32_t n;            // (base, scalar) pairs
@@ -75,12 +76,18 @@ inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_s
     p.G = (p.W + p.V - 1) / p.V;
     p.NB = 1u << (c - 1);
     p.copy_stride = copy_stride;
-    // Task length: ~4 waves of the 148 SM x 3 CTA x 128 thread accumulate grid, so that the
-    // length-sorted tasks balance across SMs; never more than twice the mean bucket size.
+    // Task length S (max entries per accumulate task): long enough that an ordinary bucket
+    // (mean + 4 sigma of a Poisson load) is ONE task — a mixed addition inside a task costs 10
+    // products, folding two partial sums 14 — and at least what keeps the task count near 3 waves
+    // of the 148 SM x 3 CTA x 128 thread accumulate grid for very large n. SM load balance comes
+    // from the length-sorted task order and from the sibling MSMs of a proof running concurrently.
+    // Buckets cut into <= MSM_INLINE_FOLD tasks are folded on the fly by the first running-sum
+    // level; genuinely heavy ones (many equal small scalars) go through k_fold_heavy.
     uint64_t avg = ((uint64_t)n * p.W + (uint64_t)p.V * p.NB - 1) / ((uint64_t)p.V * p.NB);
     uint64_t S = ((uint64_t)n * p.W + MSM_TARGET_TASKS - 1) / MSM_TARGET_TASKS;
-    if (S > 2 * avg) S = 2 * avg;
-    if (S < 8) S = 8;
+    uint64_t sq = 0;
+    while ((sq + 1) * (sq + 1) <= avg) sq++;
+    if (S < avg + 4 * sq + 8) S = avg + 4 * sq + 8;
     p.S = (uint32_t)S;
     p.n_buckets = (uint64_t)p.V * p.NB;
     p.max_tasks = ((uint64_t)n * p.W) / p.S + p.n_buckets + 1;
@@ -441,11 +448,13 @@ static constexpr uint32_t MSM_LEN_BINS = 1024;
 __device__ __forceinline__ uint32_t msm_len_bin(uint32_t len) { return len >= MSM_LEN_BINS ? 0u : MSM_LEN_BINS - len; }
 
 __global__ void k_task_fill(MsmPlan p, const uint32_t *counts, const uint32_t *offsets, const uint32_t *task_off,
-                            uint32_t *task_start, uint32_t *task_len, uint32_t *task_bucket, uint32_t *len_hist)
+                            uint32_t *task_start, uint32_t *task_len, uint32_t *task_bucket, uint32_t *len_hist,
+                            uint32_t *heavy_list, uint32_t *heavy_count)
 {
     size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= p.n_buckets) return;
     uint32_t t0 = task_off[b], nt = task_off[b + 1] - t0;
+    if (nt > MSM_INLINE_FOLD) heavy_list[atomicAdd(heavy_count, 1u)] = (uint32_t)b; // folded by k_fold_heavy
     uint64_t cnt = counts[b];
     uint32_t off = offsets[b];
     for (uint32_t k = 0; k < nt; k++) {
@@ -468,7 +477,7 @@ __global__ void k_task_order(const uint32_t *task_off_total, const uint32_t *tas
 
 // ------------------------------------------------------------------ accumulate
 // One thread per task: partial[t] = sum of its entries (mixed additions).
-__global__ void __launch_bounds__(128, 2)
+__global__ void __launch_bounds__(128, 3)
 k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint32_t *order, const uint32_t *task_start,
              const uint32_t *task_len, const uint32_t *entries, XYZZ *partial)
 {
@@ -507,25 +516,35 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
     fqvm_run(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); });
 }
 
-// Buckets that were cut into several tasks: pairwise tree fold of their partials into the
-// first one. Level j: partial[t] += partial[t + 2^j] for tasks whose index inside the bucket
-// is a multiple of 2^(j+1). log2(MSM_MAX_TASKS_PER_BUCKET) launches, one addition deep each.
-__global__ void __launch_bounds__(128, 2)
-k_fold_level(uint32_t j, const uint32_t *n_tasks, const uint32_t *task_off, const uint32_t *task_bucket, XYZZ *partial)
+// Buckets that were cut into several tasks ("heavy" buckets, listed by k_task_fill; rare by the
+// choice of S): one warp per heavy bucket folds the bucket's partials into the first one by a
+// pairwise tree, level j: partial[i] += partial[i + 2^j] for i a multiple of 2^(j+1); the pairs
+// of a level are spread over the 32 lanes. One launch, log2(MSM_MAX_TASKS_PER_BUCKET) levels deep.
+static constexpr uint32_t MSM_FOLD_BLOCKS = 148 * 8;
+__global__ void __launch_bounds__(32, 1)
+k_fold_heavy(const uint32_t *heavy_list, const uint32_t *heavy_count, const uint32_t *task_off, XYZZ *partial)
 {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= *n_tasks) return;
-    const uint32_t b = task_bucket[t];
-    const uint32_t t0 = task_off[b], nt = task_off[b + 1] - t0;
-    const uint32_t i = t - t0, step = 1u << j;
-    if ((i & (2 * step - 1)) != 0 || i + step >= nt) return;
-    FqSlots S;
-    vs_load_acc(S, partial + t);
-    vs_load_q(S, partial + t + step);
-    fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &, FqSlots &S_) {
-        vs_store_acc(partial + t, S_);
-        return false;
-    });
+    const uint32_t n_heavy = *heavy_count;
+    for (uint32_t h = blockIdx.x; h < n_heavy; h += gridDim.x) {
+        const uint32_t b = heavy_list[h];
+        const uint32_t t0 = task_off[b], nt = task_off[b + 1] - t0;
+        for (uint32_t step = 1; step < nt; step <<= 1) {
+            // pairs (i, i + step), i = 2*step*k, k < ceil((nt - step) / (2 step))
+            const uint32_t n_pairs = (nt - step + 2 * step - 1) / (2 * step);
+            for (uint32_t k = threadIdx.x; k < n_pairs; k += 32) {
+                XYZZ *dst = partial + t0 + 2 * step * k;
+                FqSlots S;
+                vs_load_acc(S, dst);
+                vs_load_q(S, dst + step);
+                fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &, FqSlots &S_) {
+                    vs_store_acc(dst, S_);
+                    return false;
+                });
+            }
+            __threadfence_block();
+            __syncwarp();
+        }
+    }
 }
 
 // ------------------------------------------------------------------ reduce
@@ -562,13 +581,20 @@ k_reduce_level(ReduceLevel r, const uint32_t *task_off, const XYZZ *inA, const X
         vs_one(S, VS_RY);
         vs_zero(S, VS_RZZ);
         vs_zero(S, VS_RZZZ);
+        // level 0: item = bucket; a bucket cut into nsub <= MSM_INLINE_FOLD tasks is summed here
+        // (partials t0 .. t0+nsub-1), a heavier one was already folded into partial[t0]
+        uint32_t sub = 0, nsub = 1, sub_t0 = 0;
         auto load_item = [&](FqSlots &S_, uint32_t idx) {
+            sub = 0;
+            nsub = 1;
             if (r.level0) {
                 uint32_t t0 = task_off[idx], t1 = task_off[idx + 1];
                 if (t0 == t1) {
                     vs_zero(S_, VS_QZZ); // infinity: the add program only tests QZZ
                     return;
                 }
+                sub_t0 = t0;
+                if (t1 - t0 <= MSM_INLINE_FOLD) nsub = t1 - t0;
                 vs_load_q(S_, inA + t0);
             } else {
                 vs_load_q(S_, inA + idx);
@@ -577,6 +603,11 @@ k_reduce_level(ReduceLevel r, const uint32_t *task_off, const XYZZ *inA, const X
         load_item(S, s * L + j);
         fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
             if (phase == 0) {
+                if (++sub < nsub) { // next partial of the same bucket
+                    vs_load_q(S_, inA + sub_t0 + sub);
+                    pc = VPC_ADD;
+                    return true;
+                }
                 // acc now holds run_j
                 if (j > 0 || r.level0) {
                     phase = 1;
@@ -776,14 +807,15 @@ inline MsmBuffers msm_layout(const MsmPlan &p, uint8_t *base)
     return b;
 }
 
-// Number of kernel launches msm_launch issues for plan p.
-inline uint64_t msm_launch_count(const MsmPlan &p) { return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 8 + p.n_levels + 1; }
+// Number of kernel launches msm_launch_front + msm_launch_tail issue for plan p.
+inline uint64_t msm_launch_count(const MsmPlan &p) { return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 1 + p.n_levels + 1; }
 
-// Launch the whole MSM on `st`. d_bases: affine image (G copies of copy_stride points);
-// d_scalars: Fr Montgomery. Result (libff special form, 288 B) is left in buffers.result.
-inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affine *d_bases, const uint8_t *d_is_inf,
-                              const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, cudaStream_t st,
-                              cudaEvent_t acc_ev0 = nullptr, cudaEvent_t acc_ev1 = nullptr)
+// First half of an MSM on `st`: digit decomposition, counting sort by bucket, task cutting and
+// the bucket accumulation kernel (the throughput-bound part). d_bases: affine image (G copies of
+// copy_stride points); d_scalars: Fr Montgomery.
+inline cudaError_t msm_launch_front(const MsmPlan &p, const MsmBuffers &b, const Affine *d_bases, const uint8_t *d_is_inf,
+                                    const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, cudaStream_t st,
+                                    cudaEvent_t acc_ev0 = nullptr, cudaEvent_t acc_ev1 = nullptr)
 {
     const uint32_t n = p.n;
     cudaMemsetAsync(b.counts, 0, (p.n_buckets + 1) * 4, st);
@@ -796,7 +828,9 @@ inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affin
     unsigned gb = (unsigned)((p.n_buckets + 255) / 256);
     k_task_count<<<gb, 256, 0, st>>>(p, b.counts, b.ntasks);
     exclusive_scan_u32(b.ntasks, p.n_buckets, b.task_off, b.scan_tmp, st);
-    k_task_fill<<<gb, 256, 0, st>>>(p, b.counts, b.offsets, b.task_off, b.task_start, b.task_len, b.task_bucket, b.len_hist);
+    // heavy-bucket list: reuses ntasks (dead after its scan); counter = spare word of len_hist
+    k_task_fill<<<gb, 256, 0, st>>>(p, b.counts, b.offsets, b.task_off, b.task_start, b.task_len, b.task_bucket, b.len_hist,
+                                    b.ntasks, b.len_hist + MSM_LEN_BINS + 1);
     exclusive_scan_u32(b.len_hist, MSM_LEN_BINS + 1, b.len_cursor, b.scan_tmp, st);
     const uint32_t *n_tasks = b.task_off + p.n_buckets;
     k_task_order<<<(unsigned)((p.max_tasks + 255) / 256), 256, 0, st>>>(n_tasks, b.task_len, b.len_cursor, b.order);
@@ -804,9 +838,15 @@ inline cudaError_t msm_launch(const MsmPlan &p, const MsmBuffers &b, const Affin
     k_accumulate<<<(unsigned)((p.max_tasks + 127) / 128), 128, 0, st>>>(p, d_bases, n_tasks, b.order, b.task_start,
                                                                          b.task_len, b.entries, b.partial);
     if (acc_ev1) cudaEventRecord(acc_ev1, st);
-    for (uint32_t j = 0; (1u << j) < MSM_MAX_TASKS_PER_BUCKET; j++)
-        k_fold_level<<<(unsigned)((p.max_tasks + 127) / 128), 128, 0, st>>>(j, n_tasks, b.task_off, b.task_bucket, b.partial);
-    // reduction levels
+    return cudaGetLastError();
+}
+
+// Second half: fold of split buckets, blocked running sums, Horner + normalisation — a chain of
+// small dependent kernels (latency-bound). Result (libff special form, 288 B) is left in
+// buffers.result.
+inline cudaError_t msm_launch_tail(const MsmPlan &p, const MsmBuffers &b, cudaStream_t st)
+{
+    k_fold_heavy<<<MSM_FOLD_BLOCKS, 32, 0, st>>>(b.ntasks, b.len_hist + MSM_LEN_BINS + 1, b.task_off, b.partial);
     ReduceLevel r{};
     r.n_in = (uint32_t)p.n_buckets;
     const XYZZ *inA = b.partial, *inC = nullptr;

@@ -3,6 +3,7 @@
 // copy of fq_mul & co.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -35,6 +36,11 @@ struct zecale_gpu_bases {
 static constexpr int ZECALE_GPU_LANES = 6;
 struct Lane {
     cudaStream_t stream = nullptr;
+    // High-priority twin of `stream`: the latency-bound parts (NTT passes, the fold / running-sum /
+    // Horner tail of an MSM: long chains of small dependent kernels) run here so that their blocks
+    // are placed ahead of the queued blocks of other lanes' throughput-bound bucket accumulation.
+    cudaStream_t hi = nullptr;
+    cudaEvent_t ev_hand = nullptr, ev_back = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     DevBuf ws_msm, ws_sc, ws_idx, ws_ntt, ws_qap;
     struct Staging {
@@ -46,6 +52,14 @@ struct Lane {
     size_t user_h_bytes = 0;     // ... and its size (a zero Fr is appended)
     uint32_t last_stats[2] = {0, 0};
     MsmPlan last_plan{};
+    // Asynchronous MSM whose second half (fold / running sums / Horner) has not been enqueued yet:
+    // the tails of all MSMs of a proof are issued together, after every bucket accumulation of the
+    // proof, so that the latency-bound tails neither starve behind nor displace the accumulation
+    // kernels of sibling lanes (see flush_tails).
+    bool tail_pending = false;
+    MsmPlan tail_plan{};
+    MsmBuffers tail_buf{};
+    cudaEvent_t ev_acc = nullptr; // bucket accumulation of the pending MSM finished
 };
 
 struct zecale_gpu_ctx {
@@ -75,6 +89,20 @@ struct zecale_gpu_ctx {
     };
     std::vector<EpochUpload> uploads;
     DevBuf up_pool[8];
+    // Set by qap_h_async until the next sync: asynchronous MSMs enqueued after it on other lanes
+    // start once the seven transforms are done. The transforms are short (~1 ms) but sit on the
+    // proof's critical path (the H MSM consumes them); left to compete with four bucket
+    // accumulations for SM space they finish ten times later.
+    cudaEvent_t ev_qap = nullptr;
+    bool qap_in_epoch = false;
+    // ZECALE_GPU_TRACE=1: phase timestamps of every lane, printed to stderr at each sync
+    bool trace = false;
+    struct TraceMark {
+        const char *label;
+        int lane;
+        cudaEvent_t ev;
+    };
+    std::vector<TraceMark> marks;
 };
 
 namespace {
@@ -122,11 +150,62 @@ cudaEvent_t take_event(zecale_gpu_ctx *ctx)
     return e;
 }
 
+void trace_mark(zecale_gpu_ctx *ctx, const char *label, cudaStream_t st, int lane = -1)
+{
+    if (!ctx->trace) return;
+    cudaEvent_t e = take_event(ctx);
+    cudaEventRecord(e, st);
+    ctx->marks.push_back({label, lane >= 0 ? lane : (int)(ctx->cur - ctx->lanes), e});
+}
+
+// Enqueue the second half of every pending asynchronous MSM: each on its lane's high-priority
+// stream, gated on the accumulation kernels of ALL pending MSMs, then joined back into the lane.
+int flush_tails(zecale_gpu_ctx *ctx)
+{
+    for (Lane &L : ctx->lanes) {
+        if (!L.tail_pending) continue;
+        for (Lane &O : ctx->lanes)
+            if (O.tail_pending) CK(cudaStreamWaitEvent(L.hi, O.ev_acc, 0));
+    }
+    for (Lane &L : ctx->lanes) {
+        if (!L.tail_pending) continue;
+        const int lane = (int)(&L - ctx->lanes);
+        trace_mark(ctx, "tail0", L.hi, lane);
+        CK(msm_launch_tail(L.tail_plan, L.tail_buf, L.hi));
+        CK(cudaMemcpyAsync(&L.h->result, L.tail_buf.result, sizeof(Proj), cudaMemcpyDeviceToHost, L.hi));
+        CK(cudaEventRecord(L.ev_back, L.hi));
+        CK(cudaStreamWaitEvent(L.stream, L.ev_back, 0));
+        trace_mark(ctx, "tail1", L.stream, lane);
+    }
+    for (Lane &L : ctx->lanes) L.tail_pending = false;
+    return 0;
+}
+
+void trace_dump(zecale_gpu_ctx *ctx)
+{
+    if (ctx->marks.empty()) return;
+    fprintf(stderr, "[zecale_gpu trace ctx=%p] ms since first mark (lane: label=t ...)\n", (void *)ctx);
+    for (int lane = 0; lane < ZECALE_GPU_LANES; lane++) {
+        bool any = false;
+        for (auto &m : ctx->marks) {
+            if (m.lane != lane) continue;
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, ctx->marks[0].ev, m.ev);
+            if (!any) fprintf(stderr, "  lane %d:", lane);
+            any = true;
+            fprintf(stderr, " %s=%.2f", m.label, ms);
+        }
+        if (any) fprintf(stderr, "\n");
+    }
+    for (auto &m : ctx->marks) ctx->ev_pool.push_back(m.ev);
+    ctx->marks.clear();
+}
+
 // Fold finished event pairs into the per-class totals (synchronises the stream).
 // Wait for every lane and deliver the results of asynchronous calls to the caller's buffers.
 int sync_lanes(zecale_gpu_ctx *ctx)
 {
-    int rc = 0;
+    int rc = flush_tails(ctx);
     for (Lane &L : ctx->lanes) {
         if (!L.stream) continue;
         cudaError_t e = cudaStreamSynchronize(L.stream);
@@ -152,6 +231,8 @@ int sync_lanes(zecale_gpu_ctx *ctx)
             L.user_h = nullptr;
         }
     }
+    ctx->qap_in_epoch = false;
+    if (ctx->trace) trace_dump(ctx);
     return rc;
 }
 
@@ -217,15 +298,29 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
     MsmBuffers b = msm_layout(plan, (uint8_t *)ctx->cur->ws_msm.p);
     if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev0, ctx->cur->stream));
     cudaEvent_t a0 = take_event(ctx), a1 = take_event(ctx);
-    CK(msm_launch(plan, b, d_bases, d_inf, d_scalars, sstride, d_index, ctx->cur->stream, a0, a1));
-    ctx->ev_pending[0].emplace_back(a0, a1);
+    trace_mark(ctx, "msm", ctx->cur->stream);
+    Lane &L = *ctx->cur;
+    CK(msm_launch_front(plan, b, d_bases, d_inf, d_scalars, sstride, d_index, L.stream, a0, a1));
+    if (ctx->trace) { // the accumulate events become trace marks (the per-class timer is off while tracing)
+        ctx->marks.push_back({"acc0", (int)(ctx->cur - ctx->lanes), a0});
+        ctx->marks.push_back({"acc1", (int)(ctx->cur - ctx->lanes), a1});
+    } else {
+        ctx->ev_pending[0].emplace_back(a0, a1);
+    }
     if (ctx->ev_pending[0].size() > 256) drain_timers(ctx);
     ctx->launches += msm_launch_count(plan);
-    if (elapsed_ms) CK(cudaEventRecord(ctx->cur->ev1, ctx->cur->stream));
-    Lane &L = *ctx->cur;
-    CK(cudaMemcpyAsync(&L.h->result, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, L.stream));
     CK(cudaMemcpyAsync(&L.h->stats[0], b.offsets + plan.n_buckets, 4, cudaMemcpyDeviceToHost, L.stream));
     CK(cudaMemcpyAsync(&L.h->stats[1], b.task_off + plan.n_buckets, 4, cudaMemcpyDeviceToHost, L.stream));
+    if (nosync) { // the tail is issued by flush_tails (at the next sync), with its siblings
+        CK(cudaEventRecord(L.ev_acc, L.stream));
+        L.tail_pending = true;
+        L.tail_plan = plan;
+        L.tail_buf = b;
+    } else {
+        CK(msm_launch_tail(plan, b, L.stream));
+        if (elapsed_ms) CK(cudaEventRecord(L.ev1, L.stream));
+        CK(cudaMemcpyAsync(&L.h->result, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, L.stream));
+    }
     L.last_plan = plan;
     L.user_out = out_point;
     if (nosync) return 0;
@@ -337,15 +432,30 @@ int qap_h_device(zecale_gpu_ctx *ctx, Fr *aA, Fr *aB, Fr *aC, unsigned log_m, co
     const Fr *zinv = nullptr;
     int rc = get_zinv(ctx, log_m, g, &zinv);
     if (rc) return rc;
+    // the seven transforms are on the proof's critical path (the H MSM waits for them): run them on
+    // the lane's high-priority stream, in order with the rest of the lane
+    Lane &L = *ctx->cur;
+    trace_mark(ctx, "qap0", L.stream);
+    CK(cudaEventRecord(L.ev_hand, L.stream));
+    CK(cudaStreamWaitEvent(L.hi, L.ev_hand, 0));
+    std::swap(L.stream, L.hi);
     Fr *v[3] = {aA, aB, aC};
-    for (int k = 0; k < 3; k++) {
-        if ((rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_INVERSE, nullptr))) return rc;
-        if ((rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_COSET, g))) return rc;
+    for (int k = 0; k < 3 && rc == 0; k++) {
+        rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_INVERSE, nullptr);
+        if (rc == 0) rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_COSET, g);
     }
-    k_qap_pointwise<<<(unsigned)((m + 255) / 256), 256, 0, ctx->cur->stream>>>(aA, aB, aC, zinv, m);
-    ctx->launches++;
+    if (rc == 0) {
+        k_qap_pointwise<<<(unsigned)((m + 255) / 256), 256, 0, L.stream>>>(aA, aB, aC, zinv, m);
+        ctx->launches++;
+        rc = ntt_device(ctx, aA, log_m, ZECALE_GPU_NTT_INVERSE | ZECALE_GPU_NTT_COSET, g);
+    }
+    std::swap(L.stream, L.hi);
+    if (rc) return rc;
     CK(cudaGetLastError());
-    return ntt_device(ctx, aA, log_m, ZECALE_GPU_NTT_INVERSE | ZECALE_GPU_NTT_COSET, g);
+    CK(cudaEventRecord(L.ev_back, L.hi));
+    CK(cudaStreamWaitEvent(L.stream, L.ev_back, 0));
+    trace_mark(ctx, "qap1", L.stream);
+    return 0;
 }
 
 // ------------------------------------------------------------------ test kernels
@@ -553,6 +663,9 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
 {
     if (!out) return ZECALE_GPU_E_ARG;
     *out = nullptr;
+    // one hardware work queue per stream (the default of 8 makes lanes share queues, which
+    // serialises independent streams); only effective if CUDA is not initialised yet
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0) return ZECALE_GPU_E_CUDA;
@@ -571,12 +684,21 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
         delete ctx;
         return ZECALE_GPU_E_CUDA; // sm_100a only: no fallback path
     }
-    bool ok = cudaMalloc((void **)&ctx->d_status, sizeof(int)) == cudaSuccess;
+    bool ok = cudaMalloc((void **)&ctx->d_status, sizeof(int)) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_qap, cudaEventDisableTiming) == cudaSuccess;
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi); // numerically lower = higher priority
     for (Lane &L : ctx->lanes)
-        ok = ok && cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking) == cudaSuccess &&
+        ok = ok && cudaStreamCreateWithPriority(&L.stream, cudaStreamNonBlocking, prio_lo) == cudaSuccess &&
+             cudaStreamCreateWithPriority(&L.hi, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
+             cudaEventCreateWithFlags(&L.ev_hand, cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&L.ev_back, cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&L.ev_acc, cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreate(&L.ev0) == cudaSuccess && cudaEventCreate(&L.ev1) == cudaSuccess &&
              cudaMallocHost((void **)&L.h, sizeof(Lane::Staging)) == cudaSuccess;
     ctx->cur = &ctx->lanes[0];
+    const char *tr = getenv("ZECALE_GPU_TRACE");
+    ctx->trace = tr && tr[0] == '1';
     if (!ok) {
         zecale_gpu_shutdown(ctx);
         return ZECALE_GPU_E_CUDA;
@@ -597,6 +719,10 @@ void zecale_gpu_shutdown(zecale_gpu_ctx *ctx)
         if (L.h) cudaFreeHost(L.h);
         if (L.ev0) cudaEventDestroy(L.ev0);
         if (L.ev1) cudaEventDestroy(L.ev1);
+        if (L.ev_hand) cudaEventDestroy(L.ev_hand);
+        if (L.ev_back) cudaEventDestroy(L.ev_back);
+        if (L.ev_acc) cudaEventDestroy(L.ev_acc);
+        if (L.hi) cudaStreamDestroy(L.hi);
         if (L.stream) cudaStreamDestroy(L.stream);
     }
     for (DevBuf *b : {&ctx->ws_in, &ctx->ws_tmp})
@@ -607,6 +733,7 @@ void zecale_gpu_shutdown(zecale_gpu_ctx *ctx)
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     for (auto &kv : ctx->zinv) cudaFree(kv.second);
     if (ctx->d_status) cudaFree(ctx->d_status);
+    if (ctx->ev_qap) cudaEventDestroy(ctx->ev_qap);
     delete ctx;
 }
 
@@ -908,6 +1035,8 @@ int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_
             d_idx = (const uint64_t *)d_i;
         }
     }
+    if (ctx->qap_in_epoch && !(flags & ZECALE_GPU_SCALARS_FROM_QAP))
+        CK(cudaStreamWaitEvent(ctx->cur->stream, ctx->ev_qap, 0));
     return msm_device(ctx, h->d, h->is_inf, h->c, h->V, (uint32_t)h->n, d_sc, scalar_stride, d_idx, n, out_point, nullptr,
                       true);
 }
@@ -936,6 +1065,8 @@ int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const 
     CK(cudaMemcpyAsync(d + 2 * m, aC, bytes, cudaMemcpyDefault, ctx->cur->stream));
     rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
     if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev_qap, ctx->cur->stream));
+    ctx->qap_in_epoch = true;
     ctx->cur->user_h = out_h; // may be NULL: the coefficients then only feed ZECALE_GPU_SCALARS_FROM_QAP
     ctx->cur->user_h_bytes = bytes;
     return 0;
