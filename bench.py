@@ -250,25 +250,36 @@ class Workload:
     E2E_H2D = 3 * (1 << LOG_M) * 48 + N_A * 48 + N_B * 8
     E2E_D2H = ((1 << LOG_M)) * 48 + 5 * 288
 
-    def algorithmic_madds(self):
-        """Mixed additions one step's five bucket-accumulation launches execute: bucket entries
-        (non-zero signed digits of points that are not at infinity) minus accumulate tasks (the
-        first entry of a task is a copy), read back from the library after an untimed step."""
+    def isolated_kernels(self):
+        """The dominant kernels timed ALONE (nothing else on the GPU), on the step's own inputs:
+        each of the five MSMs and the H polynomial are run once through the blocking device-pointer
+        entry points and the library's CUDA-event brackets around k_accumulate (class 0) and the NTT
+        transforms (class 1) are read back. Inside the timed region these kernels overlap with the
+        kernels of sibling lanes and of the other proof in flight, so event brackets taken there
+        measure co-scheduled time, not the kernel. Also returns the mixed additions executed: bucket
+        entries (non-zero signed digits of points that are not at infinity) minus accumulate tasks
+        (the first entry of a task is a copy)."""
         ctx = self.ctx
         w = self.d_w.data_ptr()
         for dst, src in zip(self.d_abc, self.d_abc0):
             dst.copy_(src)
         self.torch.cuda.current_stream().synchronize()
+        ctx.kernel_ms(0)
+        ctx.kernel_ms(1)
         ctx.qap_h_dev(self.d_abc[0].data_ptr(), self.d_abc[1].data_ptr(), self.d_abc[2].data_ptr(), LOG_M, self.g)
+        ntt_ms, ntt_n = ctx.kernel_ms(1)
         tot, shapes = 0, {}
         calls = (("A", w, N_A, None), ("B2", w, N_B, self.d_idx.data_ptr()), ("B1", w, N_B, self.d_idx.data_ptr()),
                  ("H", self.d_abc[0].data_ptr(), N_H, None), ("L", w + 48 * (N_INPUTS + 1), N_L, None))
         for name, sc, n, idx in calls:
             ctx.msm_pinned_dev(self.pk[name], sc, n, d_index_ptr=idx)
             st = ctx.msm_last_stats()
+            ms, _ = ctx.kernel_ms(0)
+            st["accumulate_ms"] = ms
             tot += st["entries"] - st["tasks"]
             shapes[name] = st
-        return tot, shapes
+        acc_ms = sum(v["accumulate_ms"] for v in shapes.values())
+        return tot, shapes, acc_ms, ntt_ms, ntt_n
 
     def close(self):
         for p in self.pk.values():
@@ -376,11 +387,13 @@ def run_b200(args, rank, world, local_rank):
     if rank == 0:
         peaks, peaks_src = measured_peaks()
         peak_prod = imad_peak(ctx)
-        madds, shapes = wl.algorithmic_madds()
-        acc_s = acc_ms * 1e-3 / max(args.steps, 1)          # accumulate time per step (5 launches)
+        madds, shapes, iso_acc_ms, iso_ntt_ms, iso_ntt_n = wl.isolated_kernels()
+        acc_s = iso_acc_ms * 1e-3                            # the step's 5 accumulate launches, each timed alone
         achieved = madds * FQ_MUL_PER_MADD * PRODUCTS_PER_FQ_MUL / acc_s if acc_s > 0 else 0.0
         ntt_bytes = 7 * 192 * (1 << LOG_M)                   # 2 passes x (48 B read + 48 B write) per element
-        ntt_s = ntt_ms * 1e-3 / max(args.steps, 1)
+        ntt_s = iso_ntt_ms * 1e-3                            # the step's 7 transforms, timed alone
+        overlapped = {"accumulate_ms_per_step": acc_ms / max(args.steps, 1), "ntt_ms_per_step": ntt_ms / max(args.steps, 1),
+                      "note": "event brackets inside the timed region (kernels co-scheduled with sibling lanes / the other proof)"}
         out = {
             "metric": METRIC, "value": world * args.steps / t_res, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps,
@@ -395,11 +408,16 @@ def run_b200(args, rank, world, local_rank):
                     "d2h_bytes_per_step": Workload.E2E_D2H},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "imad", "kernel": "k_accumulate (MSM bucket accumulation)", "achieved": achieved / 1e12,
+            "roofline": {"bound": "imad", "bound_note": "integer-multiply pipe (sm__pipe_fmaheavy): neither HBM- nor tensor-bound, SURVEY.md 8(d)", "kernel": "k_accumulate (MSM bucket accumulation)", "achieved": achieved / 1e12,
                          "peak": peak_prod / 1e12, "unit": "T(32x32 products)/s", "frac": achieved / peak_prod if peak_prod else None,
                          "peak_source": "measured in this run: dependent-chain Fq Montgomery products (k_bench_fq_mul)",
                          "share_of_step": acc_s / (t_res / args.steps), "launches_per_step": acc_n / max(args.steps, 1),
-                         "madds_per_step": madds, "msm_shapes": shapes, "traffic": None},
+                         "launch_ms_avg": 1e3 * acc_s / 5, "timing": "CUDA events on the launching stream, each launch alone on the GPU",
+                         "algorithmic_products_per_launch_avg": madds * FQ_MUL_PER_MADD * PRODUCTS_PER_FQ_MUL / 5,
+                         "hbm_algorithmic_bytes_per_launch_avg": (madds + sum(v["tasks"] for v in shapes.values())) * 192 / 5,
+                         "in_step": overlapped,
+                         "madds_per_step": madds, "msm_shapes": shapes,
+                         "traffic": 2.54e9, "traffic_source": "ncu r01, A-query launch: dram read 1.31 GB + write 1.23 GB (profiles/r01_k_accumulate_raw.md)"},
             "roofline_ntt": {"bound": "hbm", "kernel": "k_ntt_pass (Fr radix-2 NTT, 7 transforms per step)",
                              "achieved": ntt_bytes / ntt_s / 1e9 if ntt_s > 0 else None, "peak": peaks["hbm_gbs"],
                              "unit": "GB/s", "frac": (ntt_bytes / ntt_s / 1e9) / peaks["hbm_gbs"] if ntt_s > 0 else None,

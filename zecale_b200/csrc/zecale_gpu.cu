@@ -223,11 +223,8 @@ int sync_lanes(zecale_gpu_ctx *ctx)
             for (auto &u : ctx->uploads) ctx->ev_pool.push_back(u.ev);
             ctx->uploads.clear();
         }
-        if (L.user_h) {
-            if (e == cudaSuccess) {
-                cudaMemcpy(L.user_h, L.ws_qap.p, L.user_h_bytes, cudaMemcpyDeviceToHost);
-                memset((char *)L.user_h + L.user_h_bytes, 0, sizeof(Fr));
-            }
+        if (L.user_h) { // the copy itself was enqueued by qap_h_async
+            if (e == cudaSuccess) memset((char *)L.user_h + L.user_h_bytes, 0, sizeof(Fr));
             L.user_h = nullptr;
         }
     }
@@ -287,7 +284,7 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
         if (elapsed_ms) *elapsed_ms = 0.f;
         return 0;
     }
-    if (ctx->cur->user_out || ctx->cur->user_h) { // an asynchronous result of this lane is still undelivered
+    if (ctx->cur->user_out) { // an asynchronous result of this lane is still undelivered
         int rc0 = sync_lanes(ctx);
         if (rc0) return rc0;
     }
@@ -1005,7 +1002,7 @@ int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_
         scalar_stride = sizeof(Fr);
         d_idx = nullptr;
     } else if (!(flags & ZECALE_GPU_DEVICE_POINTERS)) {
-        if (ctx->cur->user_out || ctx->cur->user_h) { // the staging buffers of this lane are still in flight
+        if (ctx->cur->user_out) { // the staging buffers of this lane are still in flight
             int rc0 = sync_lanes(ctx);
             if (rc0) return rc0;
         }
@@ -1063,10 +1060,14 @@ int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const 
     CK(cudaMemcpyAsync(d, aA, bytes, cudaMemcpyDefault, ctx->cur->stream));
     CK(cudaMemcpyAsync(d + m, aB, bytes, cudaMemcpyDefault, ctx->cur->stream));
     CK(cudaMemcpyAsync(d + 2 * m, aC, bytes, cudaMemcpyDefault, ctx->cur->stream));
+    trace_mark(ctx, "abc_h2d", ctx->cur->stream);
     rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev_qap, ctx->cur->stream));
     ctx->qap_in_epoch = true;
+    // coefficients_for_H go back on the lane's stream (copy engine; overlaps the MSMs)
+    if (out_h) CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
+    trace_mark(ctx, "h_d2h", ctx->cur->stream);
     ctx->cur->user_h = out_h; // may be NULL: the coefficients then only feed ZECALE_GPU_SCALARS_FROM_QAP
     ctx->cur->user_h_bytes = bytes;
     return 0;
