@@ -150,6 +150,33 @@ int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const 
                            unsigned log_m, const void *coset_g, void *out_h);
 int zecale_gpu_sync(zecale_gpu_ctx *ctx);
 
+/* ---- multi-GPU building blocks (one process per GPU; the exchange itself is the caller's:
+ * NCCL through torch.distributed in zecale_b200/dist.py) --------------------------------
+ *
+ * Point-sharded MSM: rank g runs zecale_gpu_msm_* / _pinned on bases [g*n/G, (g+1)*n/G) — the
+ * chunking of libff::multi_exp (multiexp.tcc:663-685) — the G partial points are all-gathered
+ * and summed in chunk order with zecale_gpu_point_sum (multiexp.tcc:680-685). `points`: n
+ * projective points of 288 B (any Z), HOST pointer; out_point: special form. */
+int zecale_gpu_point_sum(zecale_gpu_ctx *ctx, const void *points, size_t n, void *out_point);
+/* 4-step NTT of m = 2^log_m elements over `world` ranks (a power of two) with ONE all-to-all.
+ * With m1 = 2^ceil(log_m/2), m2 = m/m1, c1 = m1/world, c2 = m2/world:
+ *   layout A: rank g holds index j = j1*m2 + j2 for j2 in [g*c2, (g+1)*c2), stored [j1][j2 - g*c2]
+ *   layout B: rank h holds index k = k1 + m1*k2 for k1 in [h*c1, (h+1)*c1), stored [k1 - h*c1][k2]
+ * FFT / cosetFFT take layout A to layout B; iFFT / icosetFFT take layout B to layout A (so the
+ * iFFT -> cosetFFT -> pointwise -> icosetFFT chain of r1cs_to_qap_witness_map needs no other
+ * exchange). phase 0: local sub-transforms + twiddles, d_out = `world` contiguous chunks, chunk d
+ * for rank d; the caller then runs an all-to-all (chunk s of the result comes from rank s);
+ * phase 1: local sub-transforms on the exchanged buffer. d_in / d_out: distinct DEVICE buffers of
+ * m/world Fr. flags / coset_g as zecale_gpu_ntt. sync != 0 waits for the kernels (needed before
+ * handing the buffer to a collective on another stream). */
+int zecale_gpu_ntt_dist_phase(zecale_gpu_ctx *ctx, const void *d_in, void *d_out, unsigned log_m, unsigned flags,
+                              const void *coset_g, int world, int rank, int phase, int sync);
+
+/* The pointwise step of r1cs_to_qap_witness_map on `count` locally held elements of a domain of
+ * size 2^log_m (r1cs_to_qap.tcc:283-315): aA[i] = (aA[i]*aB[i] - aC[i]) / (g^m - 1). DEVICE pointers. */
+int zecale_gpu_qap_pointwise_dev(zecale_gpu_ctx *ctx, void *d_aA, const void *d_aB, const void *d_aC, unsigned log_m,
+                                 const void *coset_g, size_t count);
+
 /* ---- synthetic inputs (bench / tests): out_points[i] = k_i * generator of the group, in
  * libff special form (288 B each), k_i a non-zero 32-bit hash of (seed, i). HOST pointer. */
 int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t n, void *out_points);

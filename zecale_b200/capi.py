@@ -51,6 +51,9 @@ EXPORTS = {
     "zecale_gpu_ntt_dev": (_i, [_vp, _vp, _u, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
     "zecale_gpu_qap_h": (_i, [_vp, _vp, _vp, _vp, _u, _vp, _vp]),
     "zecale_gpu_qap_h_dev": (_i, [_vp, _vp, _vp, _vp, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_point_sum": (_i, [_vp, _vp, _sz, _vp]),
+    "zecale_gpu_ntt_dist_phase": (_i, [_vp, _vp, _vp, _u, _u, _vp, _i, _i, _i, _i]),
+    "zecale_gpu_qap_pointwise_dev": (_i, [_vp, _vp, _vp, _vp, _u, _vp, _sz]),
     "zecale_gpu_lane_count": (_i, []),
     "zecale_gpu_msm_pinned_async": (_i, [_vp, _i, _vp, _vp, _sz, _vp, _sz, _vp, _u]),
     "zecale_gpu_qap_h_async": (_i, [_vp, _i, _vp, _vp, _vp, _u, _vp, _vp]),
@@ -206,6 +209,22 @@ class Context:
         self._ck(_lib.zecale_gpu_qap_h_dev(self._h, ctypes.c_void_p(d_aA), ctypes.c_void_p(d_aB), ctypes.c_void_p(d_aC),
                                            log_m, _ptr(coset_g), ctypes.byref(ms)))
         return ms.value
+
+    # -- multi-GPU building blocks ---------------------------------------------------------
+    def point_sum(self, points):
+        """Sum of (n, 36) projective points, special form out."""
+        out = np.zeros(36, dtype=np.uint64)
+        pts = np.ascontiguousarray(points)
+        self._ck(_lib.zecale_gpu_point_sum(self._h, _ptr(pts) if pts.shape[0] else None, pts.shape[0], _ptr(out)))
+        return out
+
+    def ntt_dist_phase(self, d_in, d_out, log_m, flags, coset_g, world, rank, phase, sync=True):
+        self._ck(_lib.zecale_gpu_ntt_dist_phase(self._h, ctypes.c_void_p(d_in), ctypes.c_void_p(d_out), log_m, flags,
+                                                _ptr(coset_g), world, rank, phase, 1 if sync else 0))
+
+    def qap_pointwise_dev(self, d_aA, d_aB, d_aC, log_m, coset_g, count):
+        self._ck(_lib.zecale_gpu_qap_pointwise_dev(self._h, ctypes.c_void_p(d_aA), ctypes.c_void_p(d_aB), ctypes.c_void_p(d_aC),
+                                                   log_m, _ptr(coset_g), count))
 
     # -- asynchronous lanes -----------------------------------------------------------
     def msm_pinned_async(self, lane, pinned, scalars, out, n=None, index=None, device=False, from_qap=False):

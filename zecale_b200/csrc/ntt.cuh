@@ -138,6 +138,19 @@ struct NttPass {
     uint32_t log_m;           // full domain size (twiddle table has m/2 entries)
     uint32_t inverse;         // use w^-1
     uint64_t sub_tw_stride;   // w_R^e = w_m^(e*sub_tw_stride)
+    // distributed (4-step across ranks) extensions; all zero for a single-GPU transform
+    uint32_t r_lo_bits;       // != 0: input element r is split, address += (r >> r_lo_bits)*isr_hi + (r & lo)*isr
+    uint64_t isr_hi;
+    uint32_t k_lo_bits;       // != 0: output element k is split the same way with osr_hi
+    uint64_t osr_hi;
+    uint32_t tw_use_beta;     // inter-step twiddle exponent uses beta (row vectors) instead of u
+    uint64_t tw_vec_off;      // global offset of this rank's vectors in the twiddle exponent
+    const Fr *scale_tab;      // != null: output (natural index n) is also multiplied by scale_tab[n], where
+    uint64_t sc_bs, sc_sv, sc_sr; // n = beta*sc_bs + u*sc_sv + k*sc_sr + sc_off (global index of the output)
+    uint64_t sc_off;
+    const Fr *in_scale_tab;   // != null: input element is first multiplied by in_scale_tab[u*isc_sv + r*isc_sr + isc_off]
+    uint64_t isc_sv, isc_sr, isc_off;
+    uint32_t stw_global;      // 1: sub-transform twiddles are read from the global table (R too large to stage)
 };
 
 __device__ __forceinline__ uint32_t bitrev(uint32_t x, uint32_t bits) { return __brev(x) >> (32 - bits); }
@@ -182,7 +195,7 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
     }
 
     // sub-transform twiddles w_R^e, e < R/2
-    for (uint32_t e = tid; e < R / 2; e += nthr) {
+    for (uint32_t e = tid; e < R / 2 && !p.stw_global; e += nthr) {
         uint32_t w[12];
         ntt_twiddle(w, tw, (uint64_t)e * p.sub_tw_stride, p.log_m, p.inverse);
         fr_store(stw + e, w);
@@ -199,9 +212,18 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
         }
         uint32_t beta = beta0 + (p.tile_over_batch ? v : 0);
         uint32_t u = u0 + (p.tile_over_batch ? 0 : v);
-        uint64_t idx = (uint64_t)beta * p.ibs + (uint64_t)u * p.isv + (uint64_t)r * p.isr;
+        uint64_t idx = (uint64_t)beta * p.ibs + (uint64_t)u * p.isv;
+        if (p.r_lo_bits)
+            idx += (uint64_t)(r >> p.r_lo_bits) * p.isr_hi + (uint64_t)(r & ((1u << p.r_lo_bits) - 1)) * p.isr;
+        else
+            idx += (uint64_t)r * p.isr;
         uint32_t x[12];
         fr_load(x, in + idx);
+        if (p.in_scale_tab) {
+            uint32_t w[12];
+            fr_load(w, p.in_scale_tab + ((uint64_t)u * p.isc_sv + (uint64_t)r * p.isc_sr + p.isc_off));
+            fr_mul_regs(x, x, w);
+        }
         fr_store(data + (size_t)v * vstride + bitrev(r, p.logR), x);
     }
     __syncthreads();
@@ -220,7 +242,10 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
             uint32_t x[12], y[12], w[12];
             fr_load(y, pb);
             if (j != 0) {
-                fr_load(w, stw + (size_t)j * tw_step);
+                if (p.stw_global)
+                    ntt_twiddle(w, tw, (uint64_t)j * tw_step * p.sub_tw_stride, p.log_m, p.inverse);
+                else
+                    fr_load(w, stw + (size_t)j * tw_step);
                 fr_mul_regs(y, y, w);
             }
             fr_load(x, pa);
@@ -239,13 +264,23 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
         uint32_t u = u0 + (p.tile_over_batch ? 0 : v);
         uint32_t x[12];
         fr_load(x, data + (size_t)v * vstride + k);
-        if (p.tw_post && u != 0 && k != 0) {
+        const uint64_t tv = (p.tw_use_beta ? beta : u) + p.tw_vec_off;
+        if (p.tw_post && tv != 0 && k != 0) {
             uint32_t w[12];
-            uint64_t e = ((uint64_t)u * k * p.tw_mul) & ((1ull << p.log_m) - 1);
+            uint64_t e = (tv * k * p.tw_mul) & ((1ull << p.log_m) - 1);
             ntt_twiddle(w, tw, e, p.log_m, p.inverse);
             fr_mul_regs(x, x, w);
         }
-        uint64_t idx = (uint64_t)beta * p.obs + (uint64_t)u * p.osv + (uint64_t)k * p.osr;
+        if (p.scale_tab) {
+            uint32_t w[12];
+            fr_load(w, p.scale_tab + ((uint64_t)beta * p.sc_bs + (uint64_t)u * p.sc_sv + (uint64_t)k * p.sc_sr + p.sc_off));
+            fr_mul_regs(x, x, w);
+        }
+        uint64_t idx = (uint64_t)beta * p.obs + (uint64_t)u * p.osv;
+        if (p.k_lo_bits)
+            idx += (uint64_t)(k >> p.k_lo_bits) * p.osr_hi + (uint64_t)(k & ((1u << p.k_lo_bits) - 1)) * p.osr;
+        else
+            idx += (uint64_t)k * p.osr;
         fr_store(out + idx, x);
     }
 }
@@ -360,6 +395,7 @@ inline cudaError_t ntt_get_coset(NttTables &t, uint32_t log_m, const Fr &g, uint
 inline size_t ntt_pass_smem(uint32_t logR, uint32_t T)
 {
     size_t R = (size_t)1 << logR;
+    if (logR >= 12) return (size_t)T * (R + 1) * sizeof(Fr); // twiddles stay in global memory (stw_global)
     return ((size_t)T * (R + 1) + R / 2) * sizeof(Fr);
 }
 
@@ -375,6 +411,7 @@ inline uint32_t ntt_pick_T(uint32_t logR, uint32_t n_avail)
 inline cudaError_t ntt_run_pass(const Fr *in, Fr *out, const Fr *tw, NttPass p, cudaStream_t st)
 {
     size_t smem = ntt_pass_smem(p.logR, p.T);
+    p.stw_global = p.logR >= 12;
     cudaError_t e = cudaFuncSetAttribute(k_ntt_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
     uint64_t tiles = (uint64_t)p.n_batch * p.n_inner / p.T;
@@ -401,11 +438,11 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         e = ntt_get_coset(tabs, log_m, coset ? *coset_g : one_g, inverse, st, &ctab, launches);
         if (e != cudaSuccess) return e;
     }
-    const unsigned sb = (unsigned)((m + 255) / 256);
-    if (coset && !inverse) { // cosetFFT: a[i] *= g^i, then FFT  (basic_radix2_domain.tcc:77-81)
-        k_fr_scale_table<<<sb, 256, 0, st>>>(a, ctab, m);
-        (*launches)++;
-    }
+    // cosetFFT: a[i] *= g^i before the transform (basic_radix2_domain.tcc:77-81) — fused into the
+    // load of the first pass; iFFT: * 1/m, icosetFFT: additionally * g^-i (:63-88) — fused into
+    // the store of the last pass. `first` / `last` set the table on the pass that needs it.
+    const Fr *in_tab = (coset && !inverse) ? ctab : nullptr;
+    const Fr *out_tab = inverse ? ctab : nullptr;
     NttPass p{};
     p.log_m = log_m;
     p.inverse = inverse;
@@ -420,6 +457,8 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.in_fast_v = 0;
         p.tw_post = 0;
         p.sub_tw_stride = 1;
+        p.in_scale_tab = in_tab; p.isc_sr = 1;
+        p.scale_tab = out_tab; p.sc_sr = 1;
         e = ntt_run_pass(a, tmp, tw, p, st);
         if (e != cudaSuccess) return e;
         (*launches)++;
@@ -440,8 +479,10 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.tw_post = 1;
         p.tw_mul = 1;
         p.sub_tw_stride = m2; // w_m1 = w_m^m2
+        p.in_scale_tab = in_tab; p.isc_sv = 1; p.isc_sr = m2;
         e = ntt_run_pass(a, tmp, tw, p, st);
         if (e != cudaSuccess) return e;
+        p.in_scale_tab = nullptr;
         // pass 2: rows. vector beta = k1 < m1, element r = j2: in = beta*m2 + r ; out = beta + k*m1
         p.logR = l2;
         p.n_batch = (uint32_t)m1;
@@ -453,6 +494,7 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.in_fast_v = 0;
         p.tw_post = 0;
         p.sub_tw_stride = m1; // w_m2 = w_m^m1
+        p.scale_tab = out_tab; p.sc_bs = 1; p.sc_sr = m1;
         e = ntt_run_pass(tmp, a, tw, p, st);
         if (e != cudaSuccess) return e;
         *launches += 2;
@@ -472,8 +514,10 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.tw_post = 1;
         p.tw_mul = 1;
         p.sub_tw_stride = m2 * m3;
+        p.in_scale_tab = in_tab; p.isc_sv = 1; p.isc_sr = m2 * m3;
         e = ntt_run_pass(a, tmp, tw, p, st);
         if (e != cudaSuccess) return e;
+        p.in_scale_tab = nullptr;
         // pass 2: inside each row beta = k1, length-m2 transforms down columns of m2 x m3
         p.logR = l2;
         p.n_batch = (uint32_t)m1;
@@ -499,15 +543,85 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.in_fast_v = 0;
         p.tw_post = 0;
         p.sub_tw_stride = m1 * m2;
+        p.scale_tab = out_tab; p.sc_bs = 1; p.sc_sv = m1; p.sc_sr = m1 * m2;
         e = ntt_run_pass(tmp, a, tw, p, st);
         if (e != cudaSuccess) return e;
         *launches += 3;
     }
-    if (inverse) { // iFFT: * 1/m ; icosetFFT: additionally * g^-i  (basic_radix2_domain.tcc:63-88)
-        k_fr_scale_table<<<sb, 256, 0, st>>>(a, ctab, m);
-        (*launches)++;
-    }
     return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ distributed 4-step
+// One transform of m = m1*m2 elements over `world` ranks (a power of two dividing m1 and m2) with
+// ONE exchange. Layouts of the distributed vector (c1 = m1/world, c2 = m2/world):
+//   layout A: rank g holds the elements whose index j = j1*m2 + j2 has j2 in [g*c2, (g+1)*c2),
+//             stored [j1][j2 - g*c2]                      (m1 x c2, "column block")
+//   layout B: rank h holds the elements whose index k = k1 + m1*k2 has k1 in [h*c1, (h+1)*c1),
+//             stored [k1 - h*c1][k2]                      (c1 x m2)
+// forward (FFT, cosetFFT):   layout A -> layout B;   inverse (iFFT, icosetFFT): layout B -> layout A.
+// phase 0 = local sub-transforms + inter-step twiddle, output written as `world` contiguous chunks
+// (chunk d goes to rank d); then the caller exchanges chunks (all-to-all: chunk s of the receive
+// buffer comes from rank s); phase 1 = local sub-transforms on the received chunks.
+// Coset multiplication (forward) and the 1/m, g^-i scaling (inverse) are fused into the first /
+// last pass. `in` and `out` are different buffers of m/world elements.
+inline cudaError_t ntt_dist_phase(NttTables &tabs, const Fr *in, Fr *out, uint32_t log_m, uint32_t flags, const Fr *coset_g,
+                                  uint32_t world, uint32_t rank, uint32_t phase, cudaStream_t st, unsigned *launches)
+{
+    const uint32_t inverse = flags & 1u, coset = (flags >> 1) & 1u;
+    uint32_t lg = 0;
+    while ((1u << lg) < world) lg++;
+    const uint32_t l1 = (log_m + 1) / 2, l2 = log_m - l1;
+    if ((1u << lg) != world || lg >= l2 || l1 > 12 || rank >= world || phase > 1) return cudaErrorInvalidValue;
+    const uint64_t m1 = 1ull << l1, m2 = 1ull << l2, c1 = m1 >> lg, c2 = m2 >> lg;
+    const Fr *tw = nullptr;
+    cudaError_t e = ntt_get_twiddles(tabs, log_m, st, &tw, launches);
+    if (e != cudaSuccess) return e;
+    const Fr *ctab = nullptr;
+    Fr one_g;
+    if (!coset) cudaMemcpyFromSymbol(&one_g, FR_ONE, sizeof(Fr));
+    if (coset || inverse) {
+        e = ntt_get_coset(tabs, log_m, coset ? *coset_g : one_g, inverse, st, &ctab, launches);
+        if (e != cudaSuccess) return e;
+    }
+    NttPass p{};
+    p.log_m = log_m;
+    p.inverse = inverse;
+    if (!inverse && phase == 0) {
+        // columns of layout A: vector u = local column, element r = j1
+        p.logR = l1; p.n_batch = 1; p.n_inner = (uint32_t)c2; p.T = ntt_pick_T(l1, p.n_inner);
+        p.tile_over_batch = 0; p.in_fast_v = 1;
+        p.isv = 1; p.isr = c2;
+        p.osv = 1; p.osr = c2;                       // [k1][j2 local]: chunk d = rows k1 in [d*c1, (d+1)*c1)
+        p.tw_post = 1; p.tw_mul = 1; p.tw_vec_off = (uint64_t)rank * c2;
+        p.sub_tw_stride = m2;
+        if (coset) { p.in_scale_tab = ctab; p.isc_sv = 1; p.isc_sr = m2; p.isc_off = (uint64_t)rank * c2; }
+    } else if (!inverse) {
+        // rows of layout B from the received chunks [s][k1 local][j2 local]: vector beta = k1 local, element r = j2
+        p.logR = l2; p.n_batch = (uint32_t)c1; p.n_inner = 1; p.T = ntt_pick_T(l2, p.n_batch);
+        p.tile_over_batch = 1; p.in_fast_v = 0;
+        p.ibs = c2; p.isr = 1; p.r_lo_bits = l2 - lg; p.isr_hi = c1 * c2;
+        p.obs = m2; p.osr = 1;
+        p.sub_tw_stride = m1;
+    } else if (phase == 0) {
+        // rows of layout B: vector beta = k1 local, element r = k2; twiddle w^-(k1 * j2)
+        p.logR = l2; p.n_batch = (uint32_t)c1; p.n_inner = 1; p.T = ntt_pick_T(l2, p.n_batch);
+        p.tile_over_batch = 1; p.in_fast_v = 0;
+        p.ibs = m2; p.isr = 1;
+        p.obs = c2; p.osr = 1; p.k_lo_bits = l2 - lg; p.osr_hi = c1 * c2; // chunk d = columns j2 in [d*c2, (d+1)*c2)
+        p.tw_post = 1; p.tw_mul = 1; p.tw_use_beta = 1; p.tw_vec_off = (uint64_t)rank * c1;
+        p.sub_tw_stride = m1;
+    } else {
+        // columns of layout A from the received chunks [s][k1 local][j2 local]: vector u = j2 local, element r = k1
+        p.logR = l1; p.n_batch = 1; p.n_inner = (uint32_t)c2; p.T = ntt_pick_T(l1, p.n_inner);
+        p.tile_over_batch = 0; p.in_fast_v = 1;
+        p.isv = 1; p.isr = c2; p.r_lo_bits = l1 - lg; p.isr_hi = c1 * c2;
+        p.osv = 1; p.osr = c2;
+        p.sub_tw_stride = m2;
+        p.scale_tab = ctab; p.sc_sv = 1; p.sc_sr = m2; p.sc_off = (uint64_t)rank * c2; // 1/m (and g^-j)
+    }
+    e = ntt_run_pass(in, out, tw, p, st);
+    (*launches)++;
+    return e;
 }
 
 } // namespace zecale

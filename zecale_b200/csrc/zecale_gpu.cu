@@ -615,6 +615,53 @@ __global__ void __launch_bounds__(128, 2) k_bench_fq_mul(Fq *sink, unsigned iter
     if (x[0] == 0x12345678u && x[5] == 77u) vs_get(sink, S, VS_K1); // keep the chain alive
 }
 
+// out = sum of n projective points (any Z), normalised to libff special form. One thread: n is
+// the number of ranks / chunks (multi_exp's serial "final = final + partial[i]", multiexp.tcc:680-685).
+__global__ void __launch_bounds__(32, 1) k_point_sum(const Proj *pts, uint32_t n, Proj *out)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    FqSlots S;
+    vs_acc_inf(S);
+    auto load = [&](FqSlots &S_, uint32_t i) {
+        vs_set(S_, VS_QX, &pts[i].X);
+        vs_set(S_, VS_QY, &pts[i].Y);
+        vs_set(S_, VS_QZZ, &pts[i].Z);
+    };
+    uint32_t i = 0, stage = 0; // 0: conversion of point i finished, 1: its addition finished, 2: normalised
+    load(S, 0);
+    fqvm_run(S, VPC_FROMPROJ, [&](uint32_t id, uint32_t &pc, FqSlots &S_) {
+        if (stage == 2) {
+            if (id == 2) { // infinity
+                vs_zero(S_, VS_T0);
+                vs_get(&out->X, S_, VS_T0);
+                vs_get(&out->Z, S_, VS_T0);
+                vs_one(S_, VS_T0);
+                vs_get(&out->Y, S_, VS_T0);
+            } else {
+                vs_get(&out->X, S_, VS_QX);
+                vs_get(&out->Y, S_, VS_QY);
+                vs_one(S_, VS_T0);
+                vs_get(&out->Z, S_, VS_T0);
+            }
+            return false;
+        }
+        if (stage == 0) {
+            stage = 1;
+            pc = VPC_ADD;
+            return true;
+        }
+        if (++i < n) {
+            load(S_, i);
+            stage = 0;
+            pc = VPC_FROMPROJ;
+            return true;
+        }
+        stage = 2;
+        pc = VPC_TOAFF;
+        return true;
+    });
+}
+
 template <typename T>
 int test_elementwise(zecale_gpu_ctx *ctx, void (*launch)(int, const T *, const T *, T *, size_t, cudaStream_t), int op,
                      const void *a, const void *b, void *out, size_t n)
@@ -955,6 +1002,75 @@ int zecale_gpu_qap_h(zecale_gpu_ctx *ctx, const void *aA, const void *aB, const 
     if (rc) return rc;
     CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
     memset((char *)out_h + bytes, 0, sizeof(Fr)); // coefficients_for_H[m] = 0 when d1 = d2 = d3 = 0
+    CK(cudaStreamSynchronize(ctx->cur->stream));
+    return 0;
+}
+
+int zecale_gpu_point_sum(zecale_gpu_ctx *ctx, const void *points, size_t n, void *out_point)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!out_point || (n && !points) || n >= (1u << 20)) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_point_sum: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, 0, 0, nullptr, 0, nullptr, 0, out_point, nullptr);
+    int rc = reserve(ctx, ctx->ws_tmp, (n + 1) * sizeof(Proj));
+    if (rc) return rc;
+    Proj *d = (Proj *)ctx->ws_tmp.p;
+    CK(cudaMemcpyAsync(d, points, n * sizeof(Proj), cudaMemcpyHostToDevice, ctx->cur->stream));
+    k_point_sum<<<1, 32, 0, ctx->cur->stream>>>(d, (uint32_t)n, d + n);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_point, d + n, sizeof(Proj), cudaMemcpyDeviceToHost, ctx->cur->stream));
+    CK(cudaStreamSynchronize(ctx->cur->stream));
+    return 0;
+}
+
+int zecale_gpu_ntt_dist_phase(zecale_gpu_ctx *ctx, const void *d_in, void *d_out, unsigned log_m, unsigned flags,
+                              const void *coset_g, int world, int rank, int phase, int sync)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!d_in || !d_out || d_in == d_out || (flags & ~3u) || ((flags & ZECALE_GPU_NTT_COSET) && !coset_g) || world < 1 ||
+        rank < 0 || rank >= world || (phase != 0 && phase != 1))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_ntt_dist_phase: bad argument");
+    if (log_m < 4 || log_m > 24) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt_dist_phase: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    unsigned nl = 0;
+    const Fr *tw = nullptr;
+    CK(ntt_get_twiddles(ctx->ntt, log_m, ctx->cur->stream, &tw, &nl)); // tables outside the timed region
+    cudaEvent_t e0 = take_event(ctx), e1 = take_event(ctx);
+    CK(cudaEventRecord(e0, ctx->cur->stream));
+    cudaError_t e = ntt_dist_phase(ctx->ntt, (const Fr *)d_in, (Fr *)d_out, log_m, flags, (const Fr *)coset_g, (uint32_t)world,
+                                   (uint32_t)rank, (uint32_t)phase, ctx->cur->stream, &nl);
+    if (e == cudaErrorInvalidValue)
+        return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt_dist_phase: world %d does not divide the 4-step factors of 2^%u", world, log_m);
+    CK(e);
+    CK(cudaEventRecord(e1, ctx->cur->stream));
+    ctx->ev_pending[1].emplace_back(e0, e1);
+    if (ctx->ev_pending[1].size() > 256) drain_timers(ctx);
+    ctx->launches += nl;
+    if (sync) CK(cudaStreamSynchronize(ctx->cur->stream));
+    return 0;
+}
+
+int zecale_gpu_qap_pointwise_dev(zecale_gpu_ctx *ctx, void *d_aA, const void *d_aB, const void *d_aC, unsigned log_m,
+                                 const void *coset_g, size_t count)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!d_aA || !d_aB || !d_aC || !coset_g || !count) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_pointwise_dev: bad argument");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_qap_pointwise_dev: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    const Fr *zinv = nullptr;
+    int rc = get_zinv(ctx, log_m, (const Fr *)coset_g, &zinv);
+    if (rc) return rc;
+    k_qap_pointwise<<<(unsigned)((count + 255) / 256), 256, 0, ctx->cur->stream>>>((Fr *)d_aA, (const Fr *)d_aB, (const Fr *)d_aC,
+                                                                                zinv, count);
+    ctx->launches++;
+    CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->cur->stream));
     return 0;
 }
