@@ -508,6 +508,15 @@ def run_reference(args, rank, world):
 
 
 def main():
+    # the contract is ONE JSON line on stdout: native libraries (NCCL prints its version banner) write to
+    # fd 1 too, so everything but the final line is sent to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -523,7 +532,7 @@ def main():
     if args.impl == "reference":
         out = run_reference(args, rank, world)
         if out is not None:
-            print(json.dumps(out), flush=True)
+            emit(out)
         return
     if args.warmup < 3:
         args.warmup = 3
@@ -531,7 +540,7 @@ def main():
     if rank == 0:
         if world == 1 and not args.skip_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline_sample()
-        print(json.dumps(out), flush=True)
+        emit(out)
 
 
 if __name__ == "__main__":

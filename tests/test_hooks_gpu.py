@@ -66,3 +66,27 @@ def test_hooked_reference_prover_aggregator_batch1(pair):
         print("aggregator batch-1 prove: reference CPU %.2f s, hooked (GPU) %.2f s" % (t_cpu, t_gpu))
     finally:
         hooked.hooks_unpin()
+
+
+def test_hooked_reference_prover_aggregator_batch8(pair, capsys):
+    """BASELINE config 4: batch-8 aggregation (m = 2^18) proved by the reference's code with the
+    hooks, bit-identical to the CPU build; prints both prove times (same box, same process)."""
+    cpu, hooked = pair
+    r, s, exp = _same_session(cpu, hooked, lambda lib: lib.session_aggregator(8, 3))
+    sz = cpu.session_sizes()
+    assert sz["m"] == 1 << 18
+    assert hooked.hooks_pin_pk() == 0
+    try:
+        _check(hooked, r, s, exp)
+        got = hooked.session_prove(r, s)      # second run: tables and key resident
+        t_stock = hooked.session_prove_stock()
+        assert t_stock > 0
+        with capsys.disabled():
+            print("\n[batch-8 aggregator prove, %d constraints] reference CPU (%d threads): %.2f s (witness map %.2f, MSM %.2f);"
+                  " hooked on the GPU: %.2f s (witness map %.2f, MSM %.2f); unmodified prover entry, hooked: %.2f s"
+                  % (sz["num_constraints"], cpu.threads, exp["timings"]["total"], exp["timings"]["witness_map"],
+                     sum(exp["timings"][k] for k in ("msm_a", "msm_b", "msm_h", "msm_l")),
+                     got["timings"]["total"], got["timings"]["witness_map"],
+                     sum(got["timings"][k] for k in ("msm_a", "msm_b", "msm_h", "msm_l")), t_stock))
+    finally:
+        hooked.hooks_unpin()
