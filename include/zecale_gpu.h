@@ -41,6 +41,7 @@ extern "C" {
 
 typedef struct zecale_gpu_ctx zecale_gpu_ctx;
 typedef struct zecale_gpu_bases zecale_gpu_bases;
+typedef struct zecale_gpu_r1cs zecale_gpu_r1cs;
 
 enum {
     ZECALE_GPU_OK = 0,
@@ -130,6 +131,29 @@ int zecale_gpu_qap_h(zecale_gpu_ctx *ctx, const void *aA, const void *aB, const 
 /* Device-resident variant: d_aA receives coefficients_for_H[0..m); d_aB, d_aC are clobbered. */
 int zecale_gpu_qap_h_dev(zecale_gpu_ctx *ctx, void *d_aA, void *d_aB, void *d_aC, unsigned log_m,
                          const void *coset_g, float *elapsed_ms);
+
+/* ---- H polynomial straight from the witness ---------------------------------
+ * Device image of the constraint system of a proving key (libsnark r1cs_constraint_system,
+ * relations/constraint_satisfaction_problems/r1cs/r1cs.hpp; pk.constraint_system in
+ * r1cs_gg_ppzksnark.hpp:74-167): matrix k (0 = A, 1 = B, 2 = C) in CSR form, row i =
+ * constraints[i].{a,b,c}.terms: col = variable index (0 = the constant one), val = coefficient
+ * (Fr, Montgomery). row_ptr[k] has n_constraints + 1 entries. HOST pointers; nothing is retained. */
+int zecale_gpu_r1cs_load(zecale_gpu_ctx *ctx, size_t n_constraints, size_t n_inputs, size_t n_variables,
+                         const uint64_t *const row_ptr[3], const uint32_t *const col[3], const void *const val[3],
+                         zecale_gpu_r1cs **handle);
+int zecale_gpu_r1cs_free(zecale_gpu_ctx *ctx, zecale_gpu_r1cs *handle);
+/* log2 of the evaluation domain r1cs_to_qap_witness_map uses for this system (power-of-two domain
+ * of at least n_constraints + n_inputs + 1 points, r1cs_to_qap.tcc:224-227). */
+unsigned zecale_gpu_r1cs_log_domain(const zecale_gpu_r1cs *handle);
+/* The whole of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:210-344, d1 = d2 = d3 = 0) on the device,
+ * enqueued on `lane`: the evaluations <A_i,w>, <B_i,w>, <C_i,w> (+ the input-consistency rows) are
+ * computed from the assignment by a sparse mat-vec kernel, then the seven transforms. assignment =
+ * [1, primary..., auxiliary...] (n_variables + 1 Fr; HOST pointer, or device with
+ * ZECALE_GPU_DEVICE_POINTERS). MSMs enqueued afterwards with scalars inside the same host range
+ * reuse its upload. out_h: m + 1 Fr at zecale_gpu_sync, or NULL when only
+ * ZECALE_GPU_SCALARS_FROM_QAP consumes the coefficients. */
+int zecale_gpu_qap_h_from_witness_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_r1cs *r1cs, const void *assignment,
+                                        const void *coset_g, void *out_h, unsigned flags);
 
 /* ---- asynchronous lanes ------------------------------------------------------------
  * The MSMs of one proof are data-independent (r1cs_gg_ppzksnark.tcc:531-580) and only the H

@@ -216,6 +216,14 @@ class Ref:
     def hooks_pin_pk(self):
         return self.L.zref_hooks_pin_pk()
 
+    def session_prove_fused(self, r, s):
+        """Hooked build: the specialised prover body with (r, s) given (fused device path if pinned)."""
+        proof = np.zeros(576, dtype=np.uint8)
+        msm5 = np.zeros((5, 36), dtype=np.uint64)
+        tm = np.zeros(1, dtype=np.float64)
+        rc = self.L.zref_session_prove_fused(_p(r), _p(s), _p(proof), _p(msm5), _p(tm))
+        return {"verified": rc == 0, "rc": rc, "proof": proof, "msm5": msm5, "seconds": float(tm[0])}
+
     def hooks_unpin(self):
         return self.L.zref_hooks_unpin()
 

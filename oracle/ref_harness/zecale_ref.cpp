@@ -865,3 +865,39 @@ extern "C" int zref_session_set_assignment(const void *full, size_t count)
     S.aux.assign(f + 1 + S.cs.num_inputs(), f + count);
     return S.cs.is_satisfied(S.primary, S.aux) ? 0 : 1;
 }
+
+// Hooked build only: zecale_gpu_hooks::prove_with_rs — what the specialised
+// libsnark::r1cs_gg_ppzksnark_prover<bw6_761_pp> runs — with (r, s) given. Uses the fused device
+// path when the key is resident (zref_hooks_pin_pk). Outputs as zref_session_prove; timings[0] =
+// seconds for the whole call. Returns 0 if the proof verifies.
+extern "C" int zref_session_prove_fused(const void *r48, const void *s48, void *proof576, void *msm5, double *timings)
+{
+#ifdef ZECALE_GPU_HOOKS_HPP
+    if (!S.have_keys)
+        return -1;
+    Fr r, s;
+    std::memcpy((void *)&r, r48, 48);
+    std::memcpy((void *)&s, s48, 48);
+    zecale_gpu_hooks::evaluations_t e;
+    const double t0 = now_s();
+    auto proof = zecale_gpu_hooks::prove_with_rs(S.kp_ptr->pk, S.primary, S.aux, true, r, s, &e);
+    const double t1 = now_s();
+    if (timings)
+        timings[0] = t1 - t0;
+    if (proof576)
+        proof_bytes(proof, proof576);
+    if (msm5) {
+        e.At.to_special(); e.Bt_g.to_special(); e.Bt_h.to_special(); e.Ht.to_special(); e.Lt.to_special();
+        char *o = (char *)msm5;
+        std::memcpy(o, (const void *)&e.At, 288);
+        std::memcpy(o + 288, (const void *)&e.Bt_g, 288);
+        std::memcpy(o + 576, (const void *)&e.Bt_h, 288);
+        std::memcpy(o + 864, (const void *)&e.Ht, 288);
+        std::memcpy(o + 1152, (const void *)&e.Lt, 288);
+    }
+    return snark::verify(S.primary, proof, S.kp_ptr->vk) ? 0 : 1;
+#else
+    (void)r48; (void)s48; (void)proof576; (void)msm5; (void)timings;
+    return -3;
+#endif
+}

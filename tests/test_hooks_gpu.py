@@ -33,6 +33,15 @@ def _same_session(cpu, hooked, make):
     return r, s, exp
 
 
+def _check_fused(hooked, r, s, exp):
+    """The specialised libsnark::r1cs_gg_ppzksnark_prover body (fused device path when the key is resident)."""
+    got = hooked.session_prove_fused(r, s)
+    assert got["verified"], got["rc"]
+    assert np.array_equal(got["msm5"], exp["msm5"]), "MSM results differ (fused prover)"
+    assert got["proof"].tobytes() == exp["proof"].tobytes(), "proof bytes differ (fused prover)"
+    return got["seconds"]
+
+
 def _check(hooked, r, s, exp):
     got = hooked.session_prove(r, s)
     assert got["verified"]
@@ -45,9 +54,11 @@ def test_hooked_reference_prover_synthetic(pair):
     cpu, hooked = pair
     r, s, exp = _same_session(cpu, hooked, lambda lib: lib.session_synthetic(3000, 10, 400, 21))
     _check(hooked, r, s, exp)                       # un-pinned: bases uploaded per call
+    _check_fused(hooked, r, s, exp)                 # un-pinned key: the sequential body
     assert hooked.hooks_pin_pk() == 0
     try:
         _check(hooked, r, s, exp)                   # pinned proving key
+        _check_fused(hooked, r, s, exp)             # resident key: mat-vecs + transforms + MSMs fused on the device
         assert hooked.session_prove_stock() > 0     # unmodified prover, random r/s: proof verifies
     finally:
         hooked.hooks_unpin()
@@ -60,6 +71,7 @@ def test_hooked_reference_prover_aggregator_batch1(pair):
     assert hooked.hooks_pin_pk() == 0
     try:
         _check(hooked, r, s, exp)
+        _check_fused(hooked, r, s, exp)
         t_gpu = hooked.session_prove_stock()
         assert t_gpu > 0
         t_cpu = exp["timings"]["total"]
@@ -79,14 +91,17 @@ def test_hooked_reference_prover_aggregator_batch8(pair, capsys):
     try:
         _check(hooked, r, s, exp)
         got = hooked.session_prove(r, s)      # second run: tables and key resident
-        t_stock = hooked.session_prove_stock()
+        _check_fused(hooked, r, s, exp)
+        t_fused = min(_check_fused(hooked, r, s, exp) for _ in range(3))
+        t_stock = min(hooked.session_prove_stock() for _ in range(3))
         assert t_stock > 0
         with capsys.disabled():
             print("\n[batch-8 aggregator prove, %d constraints] reference CPU (%d threads): %.2f s (witness map %.2f, MSM %.2f);"
-                  " hooked on the GPU: %.2f s (witness map %.2f, MSM %.2f); unmodified prover entry, hooked: %.2f s"
+                  " call-site hooks on the GPU: %.3f s (witness map %.3f, MSM %.3f); specialised prover (fused device path): %.3f s;"
+                  " snark::generate_proof entry, hooked, random r/s: %.3f s"
                   % (sz["num_constraints"], cpu.threads, exp["timings"]["total"], exp["timings"]["witness_map"],
                      sum(exp["timings"][k] for k in ("msm_a", "msm_b", "msm_h", "msm_l")),
                      got["timings"]["total"], got["timings"]["witness_map"],
-                     sum(got["timings"][k] for k in ("msm_a", "msm_b", "msm_h", "msm_l")), t_stock))
+                     sum(got["timings"][k] for k in ("msm_a", "msm_b", "msm_h", "msm_l")), t_fused, t_stock))
     finally:
         hooked.hooks_unpin()

@@ -74,3 +74,41 @@ def test_aggregator_batch1_proof_bytes(gpu):
     sz = agg.session_sizes()
     assert sz["m"] == 1 << 16 and sz["num_inputs"] == 3
     _check(gpu, agg, pinned=True)
+
+
+def test_h_polynomial_from_witness_on_device(gpu, ref):
+    """the sparse mat-vecs <A_i,w>, <B_i,w>, <C_i,w> and the whole of
+    r1cs_to_qap_witness_map on the device (zecale_gpu_r1cs_load + zecale_gpu_qap_h_from_witness_async),
+    fused with the five MSMs of the prover on the asynchronous lanes; (r, s) fixed -> same proof bytes."""
+    assert ref.session_synthetic(5000, 12, 700, 11) == 0
+    ref.session_setup(4)
+    z = ref.session_export()
+    nv, ni, m = z["num_variables"], z["num_inputs"], z["m"]
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    r, s = ref.fr_rng(1, 1)[0], ref.fr_rng(2, 1)[0]
+    exp = ref.session_prove(r, s)
+    w = z["assignment"]
+    r1cs = gpu.r1cs_load(z["num_constraints"], ni, nv, [z["csr_a"], z["csr_b"], z["csr_c"]])
+    assert (1 << gpu.r1cs_log_domain(r1cs)) == m
+    pins = [gpu.pin_bases(z["A_query"][: nv + 1]), gpu.pin_bases(z["B_values"], 2), gpu.pin_bases(z["B_values"], 1, base_offset_bytes=288),
+            gpu.pin_bases(z["H_query"][: m - 1]), gpu.pin_bases(z["L_query"])]
+    try:
+        for rnd in range(2):
+            out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
+            h = np.zeros((m + 1, 6), dtype=np.uint64)
+            gpu.qap_h_from_witness_async(0, r1cs, w, g, out=h if rnd == 0 else None)
+            gpu.msm_pinned_async(1, pins[0], w, out[0])
+            gpu.msm_pinned_async(2, pins[1], w, out[1], index=z["B_indices"], n=z["nnz_B"])
+            gpu.msm_pinned_async(3, pins[2], w, out[2], index=z["B_indices"], n=z["nnz_B"])
+            gpu.msm_pinned_async(0, pins[3], None, out[3], from_qap=True)
+            gpu.msm_pinned_async(4, pins[4], w[ni + 1:], out[4])
+            gpu.sync()
+            if rnd == 0:
+                assert np.array_equal(h, exp["h"])
+            assert np.array_equal(np.stack(out), exp["msm5"])
+            proof, ok = ref.session_assemble(r, s, np.stack(out))
+            assert ok and proof.tobytes() == exp["proof"].tobytes()
+    finally:
+        for p in pins:
+            p.release()
+        gpu.r1cs_free(r1cs)

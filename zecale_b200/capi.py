@@ -54,6 +54,11 @@ EXPORTS = {
     "zecale_gpu_point_sum": (_i, [_vp, _vp, _sz, _vp]),
     "zecale_gpu_ntt_dist_phase": (_i, [_vp, _vp, _vp, _u, _u, _vp, _i, _i, _i, _i]),
     "zecale_gpu_qap_pointwise_dev": (_i, [_vp, _vp, _vp, _vp, _u, _vp, _sz]),
+    "zecale_gpu_r1cs_load": (_i, [_vp, _sz, _sz, _sz, ctypes.POINTER(_vp), ctypes.POINTER(_vp), ctypes.POINTER(_vp),
+                                  ctypes.POINTER(_vp)]),
+    "zecale_gpu_r1cs_free": (_i, [_vp, _vp]),
+    "zecale_gpu_r1cs_log_domain": (_u, [_vp]),
+    "zecale_gpu_qap_h_from_witness_async": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _u]),
     "zecale_gpu_lane_count": (_i, []),
     "zecale_gpu_msm_pinned_async": (_i, [_vp, _i, _vp, _vp, _sz, _vp, _sz, _vp, _u]),
     "zecale_gpu_qap_h_async": (_i, [_vp, _i, _vp, _vp, _vp, _u, _vp, _vp]),
@@ -209,6 +214,26 @@ class Context:
         self._ck(_lib.zecale_gpu_qap_h_dev(self._h, ctypes.c_void_p(d_aA), ctypes.c_void_p(d_aB), ctypes.c_void_p(d_aC),
                                            log_m, _ptr(coset_g), ctypes.byref(ms)))
         return ms.value
+
+    # -- R1CS image / H polynomial from the witness ---------------------------------------
+    def r1cs_load(self, n_constraints, n_inputs, n_variables, csr):
+        """csr: three (row_ptr uint64, col uint32, val (nnz, 6) uint64) tuples for A, B, C."""
+        keep = [(np.ascontiguousarray(rp, dtype=np.uint64), np.ascontiguousarray(c, dtype=np.uint32),
+                 np.ascontiguousarray(v, dtype=np.uint64)) for rp, c, v in csr]
+        arr = lambda k: (_vp * 3)(*[t[k].ctypes.data for t in keep])
+        h = ctypes.c_void_p()
+        self._ck(_lib.zecale_gpu_r1cs_load(self._h, n_constraints, n_inputs, n_variables, arr(0), arr(1), arr(2), ctypes.byref(h)))
+        return h
+
+    def r1cs_free(self, handle):
+        _lib.zecale_gpu_r1cs_free(self._h, handle)
+
+    def r1cs_log_domain(self, handle):
+        return int(_lib.zecale_gpu_r1cs_log_domain(handle))
+
+    def qap_h_from_witness_async(self, lane, r1cs, assignment, coset_g, out=None, device=False):
+        a = ctypes.c_void_p(assignment) if device else _ptr(assignment)
+        self._ck(_lib.zecale_gpu_qap_h_from_witness_async(self._h, lane, r1cs, a, _ptr(coset_g), _ptr(out), 1 if device else 0))
 
     # -- multi-GPU building blocks ---------------------------------------------------------
     def point_sum(self, points):

@@ -110,6 +110,33 @@ __global__ void k_qap_pointwise(Fr *a, const Fr *b, const Fr *c, const Fr *zinv,
     fr_store(a + i, x);
 }
 
+// Evaluation vectors of r1cs_to_qap_witness_map (libsnark r1cs_to_qap.tcc:236-248, 293-296) from a CSR
+// image of one constraint matrix: out[i] = <M_i, w> for i < n_rows (linear_combination::evaluate,
+// relations/variable.tcc:288: sum of coeff * assignment[index], index 0 = the constant one, which
+// is w[0] here), and for the A matrix the input-consistency rows out[n_rows + i] = w[i], i <= n_inputs
+// (:236-240); everything else up to the domain size m is zero. One thread per row (rows hold 1-3 terms).
+__global__ void k_r1cs_eval(const uint64_t *row_ptr, const uint32_t *col, const Fr *val, const Fr *w, uint32_t n_rows,
+                            uint32_t n_inputs_plus_one /* 0 for B and C */, Fr *out, size_t m)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    uint32_t acc[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) acc[k] = 0;
+    if (i < n_rows) {
+        for (uint64_t t = row_ptr[i]; t < row_ptr[i + 1]; t++) {
+            uint32_t c[12], x[12];
+            fr_load(c, val + t);
+            fr_load(x, w + col[t]);
+            fr_mul_regs(c, c, x);
+            fr_add_regs(acc, acc, c);
+        }
+    } else if (i - n_rows < n_inputs_plus_one) {
+        fr_load(acc, w + (i - n_rows));
+    }
+    fr_store(out + i, acc);
+}
+
 // out = (g^(2^log_m) - 1)^-1 : the vanishing polynomial on the coset g*H is the constant
 // g^m - 1 (libfqfft basic_radix2_domain.tcc:103-126 compute_vanishing_polynomial / divide_by_Z_on_coset).
 __global__ void k_fr_zinv(Fr *out, Fr g, uint32_t log_m)

@@ -29,6 +29,15 @@ struct zecale_gpu_bases {
     uint32_t c = 0, V = 0;    // window bits / bucket sets the image was expanded for (V = 0: not expanded)
 };
 
+// Device image of an R1CS (three CSR matrices over Fr), loaded once per circuit.
+struct zecale_gpu_r1cs {
+    size_t n_constraints = 0, n_inputs = 0, n_variables = 0;
+    unsigned log_m = 0;
+    uint64_t *row_ptr[3] = {nullptr, nullptr, nullptr};
+    uint32_t *col[3] = {nullptr, nullptr, nullptr};
+    Fr *val[3] = {nullptr, nullptr, nullptr};
+};
+
 // One in-order work queue of the context: a stream, its scratch buffers and the pinned
 // staging area results are read back into. Lane 0 serves the blocking entry points; the
 // *_async entry points let the caller put independent MSMs / the H polynomial on different
@@ -1185,6 +1194,122 @@ int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const 
     if (out_h) CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
     trace_mark(ctx, "h_d2h", ctx->cur->stream);
     ctx->cur->user_h = out_h; // may be NULL: the coefficients then only feed ZECALE_GPU_SCALARS_FROM_QAP
+    ctx->cur->user_h_bytes = bytes;
+    return 0;
+}
+
+int zecale_gpu_r1cs_load(zecale_gpu_ctx *ctx, size_t n_constraints, size_t n_inputs, size_t n_variables,
+                         const uint64_t *const row_ptr[3], const uint32_t *const col[3], const void *const val[3],
+                         zecale_gpu_r1cs **handle)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!handle || !row_ptr || !col || !val || !n_constraints || n_inputs > n_variables || n_variables >= (1ull << 31))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_r1cs_load: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    zecale_gpu_r1cs *h = new zecale_gpu_r1cs();
+    h->n_constraints = n_constraints;
+    h->n_inputs = n_inputs;
+    h->n_variables = n_variables;
+    // domain of r1cs_to_qap_witness_map with force_pow_2_domain (r1cs_to_qap.tcc:224-227)
+    while (((size_t)1 << h->log_m) < n_constraints + n_inputs + 1) h->log_m++;
+    cudaError_t e = cudaSuccess;
+    for (int k = 0; k < 3 && e == cudaSuccess; k++) {
+        if (!row_ptr[k] || row_ptr[k][0] != 0) {
+            e = cudaErrorInvalidValue;
+            break;
+        }
+        const size_t nnz = row_ptr[k][n_constraints];
+        for (size_t t = 0; t < nnz; t++)
+            if (col[k][t] > n_variables) e = cudaErrorInvalidValue; // index 0 = one, 1..n_variables
+        if (e != cudaSuccess) break;
+        e = cudaMalloc((void **)&h->row_ptr[k], (n_constraints + 1) * 8);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&h->col[k], (nnz + 1) * 4);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&h->val[k], (nnz + 1) * sizeof(Fr));
+        if (e == cudaSuccess) e = cudaMemcpy(h->row_ptr[k], row_ptr[k], (n_constraints + 1) * 8, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && nnz) e = cudaMemcpy(h->col[k], col[k], nnz * 4, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && nnz) e = cudaMemcpy(h->val[k], val[k], nnz * sizeof(Fr), cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) {
+        for (int k = 0; k < 3; k++) {
+            cudaFree(h->row_ptr[k]);
+            cudaFree(h->col[k]);
+            cudaFree(h->val[k]);
+        }
+        delete h;
+        return fail(ctx, e == cudaErrorInvalidValue ? ZECALE_GPU_E_ARG : ZECALE_GPU_E_NOMEM, "zecale_gpu_r1cs_load: %s",
+                    cudaGetErrorString(e));
+    }
+    *handle = h;
+    return 0;
+}
+
+int zecale_gpu_r1cs_free(zecale_gpu_ctx *ctx, zecale_gpu_r1cs *h)
+{
+    if (!ctx || !h) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaSetDevice(ctx->device);
+    sync_lanes(ctx);
+    for (int k = 0; k < 3; k++) {
+        cudaFree(h->row_ptr[k]);
+        cudaFree(h->col[k]);
+        cudaFree(h->val[k]);
+    }
+    delete h;
+    return 0;
+}
+
+unsigned zecale_gpu_r1cs_log_domain(const zecale_gpu_r1cs *h) { return h ? h->log_m : 0; }
+
+int zecale_gpu_qap_h_from_witness_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_r1cs *r1cs, const void *assignment,
+                                        const void *coset_g, void *out_h, unsigned flags)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (lane < 0 || lane >= ZECALE_GPU_LANES || !r1cs || !assignment || !coset_g || (flags & ~ZECALE_GPU_DEVICE_POINTERS))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_h_from_witness_async: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    ctx->cur = &ctx->lanes[lane];
+    if (ctx->cur->user_out || ctx->cur->user_h) {
+        int rc0 = sync_lanes(ctx);
+        if (rc0) return rc0;
+    }
+    const unsigned log_m = r1cs->log_m;
+    const size_t m = (size_t)1 << log_m, bytes = m * sizeof(Fr);
+    int rc = reserve(ctx, ctx->cur->ws_qap, 3 * bytes);
+    if (rc) return rc;
+    Fr *d = (Fr *)ctx->cur->ws_qap.p;
+    // the assignment [1, primary, aux] crosses PCIe once per proof: the MSM calls that pass the
+    // same host range (A, B, L) find it in the epoch's upload table
+    const uint8_t *d_w = (const uint8_t *)assignment;
+    if (!(flags & ZECALE_GPU_DEVICE_POINTERS)) {
+        const size_t wbytes = (r1cs->n_variables + 1) * sizeof(Fr);
+        rc = epoch_upload(ctx, assignment, wbytes, &d_w);
+        if (rc == 1) { // upload table full: lane-private copy
+            rc = reserve(ctx, ctx->cur->ws_sc, wbytes);
+            if (rc) return rc;
+            CK(cudaMemcpyAsync(ctx->cur->ws_sc.p, assignment, wbytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+            d_w = (const uint8_t *)ctx->cur->ws_sc.p;
+        } else if (rc) {
+            return rc;
+        }
+    }
+    trace_mark(ctx, "w_h2d", ctx->cur->stream);
+    const unsigned grid = (unsigned)((m + 127) / 128);
+    for (int k = 0; k < 3; k++) {
+        k_r1cs_eval<<<grid, 128, 0, ctx->cur->stream>>>(r1cs->row_ptr[k], r1cs->col[k], r1cs->val[k], (const Fr *)d_w,
+                                                         (uint32_t)r1cs->n_constraints, k == 0 ? (uint32_t)r1cs->n_inputs + 1 : 0u,
+                                                         d + (size_t)k * m, m);
+        ctx->launches++;
+    }
+    CK(cudaGetLastError());
+    rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev_qap, ctx->cur->stream));
+    ctx->qap_in_epoch = true;
+    if (out_h) CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
+    ctx->cur->user_h = out_h;
     ctx->cur->user_h_bytes = bytes;
     return 0;
 }

@@ -37,6 +37,7 @@
 #include <libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp>
 #include <libfqfft/evaluation_domain/get_evaluation_domain.hpp>
 #include <libsnark/knowledge_commitment/kc_multiexp.hpp>
+#include <libsnark/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.hpp>
 
 #include "zecale_gpu.h"
 
@@ -62,6 +63,12 @@ struct state_t {
         size_t n;
     };
     std::map<const void *, pin_t> pins;
+    // whole-key images for the fused prover (pin_proving_key): key = address of pk.A_query[0]
+    struct key_t {
+        zecale_gpu_bases *A, *B2, *B1, *H, *L;
+        zecale_gpu_r1cs *r1cs;
+    };
+    std::map<const void *, key_t> keys;
 };
 
 inline state_t &state()
@@ -109,17 +116,55 @@ inline void pin_bases(const void *bases, size_t stride, size_t n, int group)
     s.pins[bases] = {h, n};
 }
 
-/// Pin the four queries of a Groth16 proving key (A, B as G2 and G1 halves, H, L).
+inline zecale_gpu_bases *pinned_handle(const void *bases)
+{
+    state_t &s = state();
+    std::lock_guard<std::mutex> lk(s.mu);
+    auto it = s.pins.find(bases);
+    return it == s.pins.end() ? nullptr : it->second.handle;
+}
+
+/// Make a Groth16 proving key device-resident: the four queries (A; B as its G2 and G1 halves; H; L)
+/// and the CSR image of pk.constraint_system. Afterwards r1cs_gg_ppzksnark_prover on this key runs
+/// the fused path (see prove_fused). The key must outlive unpin_all().
 template<typename PK> inline void pin_proving_key(const PK &pk)
 {
     pin_bases(pk.A_query.data(), sizeof(G1), pk.A_query.size(), ZECALE_GPU_G1);
     pin_bases(pk.H_query.data(), sizeof(G1), pk.H_query.size(), ZECALE_GPU_G1);
     pin_bases(pk.L_query.data(), sizeof(G1), pk.L_query.size(), ZECALE_GPU_G1);
+    const char *b = reinterpret_cast<const char *>(pk.B_query.values.data());
     if (!pk.B_query.values.empty()) {
-        const char *b = reinterpret_cast<const char *>(pk.B_query.values.data());
         pin_bases(b, sizeof(KC), pk.B_query.values.size(), ZECALE_GPU_G2);
         pin_bases(b + sizeof(G2), sizeof(KC), pk.B_query.values.size(), ZECALE_GPU_G1);
     }
+    // CSR image of the constraint system (linear_combination terms: index 0 = the constant one)
+    const auto &cs = pk.constraint_system;
+    std::vector<uint64_t> rp[3];
+    std::vector<uint32_t> col[3];
+    std::vector<Fr> val[3];
+    for (int k = 0; k < 3; k++) rp[k].reserve(cs.constraints.size() + 1);
+    for (const auto &c : cs.constraints) {
+        const libsnark::linear_combination<Fr> *lc[3] = {&c.a, &c.b, &c.c};
+        for (int k = 0; k < 3; k++) {
+            rp[k].push_back(col[k].size());
+            for (const auto &t : lc[k]->terms) {
+                col[k].push_back((uint32_t)t.index);
+                val[k].push_back(t.coeff);
+            }
+        }
+    }
+    for (int k = 0; k < 3; k++) rp[k].push_back(col[k].size());
+    const uint64_t *rpp[3] = {rp[0].data(), rp[1].data(), rp[2].data()};
+    const uint32_t *cp[3] = {col[0].data(), col[1].data(), col[2].data()};
+    const void *vp[3] = {val[0].data(), val[1].data(), val[2].data()};
+    zecale_gpu_r1cs *r1cs = nullptr;
+    check(zecale_gpu_r1cs_load(context(), cs.num_constraints(), cs.num_inputs(), cs.num_variables(), rpp, cp, vp, &r1cs),
+          "zecale_gpu_r1cs_load");
+    state_t::key_t key{pinned_handle(pk.A_query.data()), pinned_handle(b), pinned_handle(b + sizeof(G2)),
+                       pinned_handle(pk.H_query.data()), pinned_handle(pk.L_query.data()), r1cs};
+    state_t &s = state();
+    std::lock_guard<std::mutex> lk(s.mu);
+    s.keys[pk.A_query.data()] = key;
 }
 
 inline void unpin_all()
@@ -128,6 +173,8 @@ inline void unpin_all()
     std::lock_guard<std::mutex> lk(s.mu);
     for (auto &kv : s.pins) zecale_gpu_unpin_bases(s.ctx, kv.second.handle);
     s.pins.clear();
+    for (auto &kv : s.keys) zecale_gpu_r1cs_free(s.ctx, kv.second.r1cs);
+    s.keys.clear();
 }
 
 inline void shutdown()
@@ -329,6 +376,162 @@ inline knowledge_commitment<libff::bw6_761_G2, libff::bw6_761_G1> kc_multi_exp_w
     out.g = msm<G2>(ZECALE_GPU_G2, base, sizeof(KC), scalars, index, n);
     out.h = msm<G1>(ZECALE_GPU_G1, base + sizeof(G2), sizeof(KC), scalars, index, n);
     return out;
+}
+
+} // namespace libsnark
+
+namespace zecale_gpu_hooks
+{
+
+// ---------------------------------------------------------------- the prover itself
+using ppT = libff::bw6_761_pp;
+using proof_t = libsnark::r1cs_gg_ppzksnark_proof<ppT>;
+using proving_key_t = libsnark::r1cs_gg_ppzksnark_proving_key<ppT>;
+
+/// The five multi-exponentiation results of r1cs_gg_ppzksnark_prover (r1cs_gg_ppzksnark.tcc:531-580).
+struct evaluations_t {
+    G1 At;
+    G2 Bt_g;
+    G1 Bt_h;
+    G1 Ht;
+    G1 Lt;
+};
+
+/// Fused path for a key made resident with pin_proving_key: the assignment is uploaded once, the
+/// sparse mat-vecs and the seven transforms of r1cs_to_qap_witness_map run on the device, the H MSM
+/// reads coefficients_for_H from device memory, the five MSMs overlap on the context's lanes, and
+/// one synchronisation returns 5 x 288 bytes. Returns false if the key is not resident or the
+/// reference would not use the power-of-two domain for it.
+inline bool evaluate_fused(
+    const proving_key_t &pk,
+    const std::vector<Fr> &primary_input,
+    const std::vector<Fr> &auxiliary_input,
+    bool force_pow_2_domain,
+    evaluations_t &out)
+{
+    state_t::key_t key;
+    {
+        state_t &s = state();
+        std::lock_guard<std::mutex> lk(s.mu);
+        auto it = s.keys.find(pk.A_query.data());
+        if (it == s.keys.end()) return false;
+        key = it->second;
+    }
+    const auto &cs = pk.constraint_system;
+    const size_t nv = cs.num_variables(), ni = cs.num_inputs();
+    const size_t min_n = cs.num_constraints() + ni + 1;
+    const size_t m = (size_t)1 << zecale_gpu_r1cs_log_domain(key.r1cs);
+    if (!force_pow_2_domain && min_n != m) return false;
+    if (primary_input.size() != ni || primary_input.size() + auxiliary_input.size() != nv ||
+        pk.A_query.size() != nv + 1 || pk.H_query.size() != m - 1 || pk.L_query.size() != nv - ni ||
+        !key.A || !key.H || !key.L) {
+        return false;
+    }
+    zecale_gpu_ctx *ctx = context();
+    // const_padded_assignment of the reference (r1cs_gg_ppzksnark.tcc:523-528)
+    std::vector<Fr> full;
+    full.reserve(nv + 1);
+    full.push_back(Fr::one());
+    full.insert(full.end(), primary_input.begin(), primary_input.end());
+    full.insert(full.end(), auxiliary_input.begin(), auxiliary_input.end());
+    const Fr g = Fr::multiplicative_generator; // the coset of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:270)
+    unsigned char pt[5][288];
+    const size_t nnz_b = pk.B_query.indices.size();
+    check(zecale_gpu_qap_h_from_witness_async(ctx, 0, key.r1cs, full.data(), &g, nullptr, 0), "zecale_gpu_qap_h_from_witness_async");
+    check(zecale_gpu_msm_pinned_async(ctx, 1, key.A, full.data(), sizeof(Fr), nullptr, nv + 1, pt[0], 0), "msm A");
+    if (nnz_b) {
+        check(zecale_gpu_msm_pinned_async(ctx, 2, key.B2, full.data(), sizeof(Fr), pk.B_query.indices.data(), nnz_b, pt[1], 0), "msm B (G2)");
+        check(zecale_gpu_msm_pinned_async(ctx, 3, key.B1, full.data(), sizeof(Fr), pk.B_query.indices.data(), nnz_b, pt[2], 0), "msm B (G1)");
+    }
+    check(zecale_gpu_msm_pinned_async(ctx, 4, key.L, full.data() + ni + 1, sizeof(Fr), nullptr, nv - ni, pt[4], 0), "msm L");
+    check(zecale_gpu_msm_pinned_async(ctx, 0, key.H, nullptr, sizeof(Fr), nullptr, m - 1, pt[3], ZECALE_GPU_SCALARS_FROM_QAP), "msm H");
+    check(zecale_gpu_sync(ctx), "zecale_gpu_sync");
+    std::memcpy(static_cast<void *>(&out.At), pt[0], 288);
+    if (nnz_b) {
+        std::memcpy(static_cast<void *>(&out.Bt_g), pt[1], 288);
+        std::memcpy(static_cast<void *>(&out.Bt_h), pt[2], 288);
+    } else {
+        out.Bt_g = G2::zero();
+        out.Bt_h = G1::zero();
+    }
+    std::memcpy(static_cast<void *>(&out.Ht), pt[3], 288);
+    std::memcpy(static_cast<void *>(&out.Lt), pt[4], 288);
+    return true;
+}
+
+/// The reference's own sequence of calls (r1cs_gg_ppzksnark.tcc:477-580), each of which resolves
+/// to a specialisation below: used when the key is not resident.
+inline void evaluate_sequential(
+    const proving_key_t &pk,
+    const std::vector<Fr> &primary_input,
+    const std::vector<Fr> &auxiliary_input,
+    bool force_pow_2_domain,
+    evaluations_t &out)
+{
+    const libsnark::qap_witness<Fr> qap_wit = libsnark::r1cs_to_qap_witness_map(
+        pk.constraint_system, primary_input, auxiliary_input, Fr::zero(), Fr::zero(), Fr::zero(), force_pow_2_domain);
+    std::vector<Fr> padded(1, Fr::one());
+    padded.insert(padded.end(), qap_wit.coefficients_for_ABCs.begin(), qap_wit.coefficients_for_ABCs.end());
+    const size_t nv = qap_wit.num_variables();
+    constexpr libff::multi_exp_method M = libff::multi_exp_method_BDLO12_signed;
+    constexpr libff::multi_exp_base_form F = libff::multi_exp_base_form_special;
+    out.At = libff::multi_exp_filter_one_zero<G1, Fr, M, F>(
+        pk.A_query.begin(), pk.A_query.begin() + nv + 1, padded.begin(), padded.begin() + nv + 1, 1);
+    const KC bt = libsnark::kc_multi_exp_with_mixed_addition<G2, G1, Fr, M, F>(
+        pk.B_query, 0, nv + 1, padded.begin(), padded.begin() + nv + 1, 1);
+    out.Bt_g = bt.g;
+    out.Bt_h = bt.h;
+    out.Ht = libff::multi_exp<G1, Fr, M, F>(
+        pk.H_query.begin(), pk.H_query.begin() + (qap_wit.degree() - 1), qap_wit.coefficients_for_H.begin(),
+        qap_wit.coefficients_for_H.begin() + (qap_wit.degree() - 1), 1);
+    out.Lt = libff::multi_exp_filter_one_zero<G1, Fr, M, F>(
+        pk.L_query.begin(), pk.L_query.end(), padded.begin() + qap_wit.num_inputs() + 1, padded.begin() + nv + 1, 1);
+}
+
+/// r1cs_gg_ppzksnark_prover with the prover randomness as parameters (the reference samples r, s
+/// from std::random_device, r1cs_gg_ppzksnark.tcc:502-503); assembly is the reference's formulae
+/// (:582-599) on its own CPU group arithmetic.
+inline proof_t prove_with_rs(
+    const proving_key_t &pk,
+    const std::vector<Fr> &primary_input,
+    const std::vector<Fr> &auxiliary_input,
+    bool force_pow_2_domain,
+    const Fr &r,
+    const Fr &s,
+    evaluations_t *evaluations_out = nullptr)
+{
+    evaluations_t e;
+    if (!evaluate_fused(pk, primary_input, auxiliary_input, force_pow_2_domain, e)) {
+        evaluate_sequential(pk, primary_input, auxiliary_input, force_pow_2_domain, e);
+    }
+    if (evaluations_out) *evaluations_out = e;
+    G1 g1_A = pk.alpha_g1 + e.At + r * pk.delta_g1;
+    G1 g1_B = pk.beta_g1 + e.Bt_h + s * pk.delta_g1;
+    G2 g2_B = pk.beta_g2 + e.Bt_g + s * pk.delta_g2;
+    G1 g1_C = e.Ht + e.Lt + s * g1_A + r * g1_B - (r * s) * pk.delta_g1;
+    return proof_t(std::move(g1_A), std::move(g2_B), std::move(g1_C));
+}
+
+} // namespace zecale_gpu_hooks
+
+namespace libsnark
+{
+
+/// r1cs_gg_ppzksnark_prover<bw6_761_pp> (r1cs_gg_ppzksnark.tcc:460-603): same signature, same
+/// distribution of (r, s); the evaluations come from the device.
+template<>
+inline r1cs_gg_ppzksnark_proof<libff::bw6_761_pp> r1cs_gg_ppzksnark_prover<
+    libff::bw6_761_pp,
+    libff::multi_exp_method_BDLO12_signed,
+    libff::multi_exp_base_form_special>(
+    const r1cs_gg_ppzksnark_proving_key<libff::bw6_761_pp> &pk,
+    const r1cs_gg_ppzksnark_primary_input<libff::bw6_761_pp> &primary_input,
+    const r1cs_gg_ppzksnark_auxiliary_input<libff::bw6_761_pp> &auxiliary_input,
+    bool force_pow_2_domain)
+{
+    const libff::bw6_761_Fr r = libff::bw6_761_Fr::random_element();
+    const libff::bw6_761_Fr s = libff::bw6_761_Fr::random_element();
+    return zecale_gpu_hooks::prove_with_rs(pk, primary_input, auxiliary_input, force_pow_2_domain, r, s);
 }
 
 } // namespace libsnark
