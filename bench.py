@@ -3,7 +3,8 @@
 
 One "step" = the device work of ONE batch-8 aggregator proof as the hooked reference
 prover would issue it (libsnark r1cs_gg_ppzksnark_prover, r1cs_gg_ppzksnark.tcc:464-603):
-    H polynomial  : 3 x (iFFT, cosetFFT) + pointwise + icosetFFT over Fr, m = 2^18
+    witness map   : sparse mat-vecs A.w, B.w, C.w (237 702 rows, 1.8 M terms), then
+                    3 x (iFFT, cosetFFT) + pointwise + icosetFFT over Fr, m = 2^18
     MSM A  (G1)   : 237 801 bases x witness
     MSM B  (G2,G1): 87 966 sparse pairs x witness[indices]
     MSM H  (G1)   : 262 143 bases x coefficients_for_H
@@ -45,6 +46,8 @@ N_A = N_VARS + 1
 N_B = 87966              # non-zero entries of pk.B_query
 N_H = (1 << LOG_M) - 1
 N_L = N_VARS - N_INPUTS
+N_CONSTRAINTS = 237702
+NNZ = (444246, 496421, 877410)   # non-zero terms of the A / B / C constraint matrices (SURVEY.md §0 [probe])
 METRIC = "bw6_761_groth16_batch8_proofs_per_s"
 UNIT = "proofs/s"
 FR_TOP = 0x01AE3A4617C510EA  # top 64-bit limb of r: a random value with a smaller top limb is < r
@@ -76,6 +79,21 @@ def witness_like(rng, n):
     w[(kind >= 0.21) & (kind < 0.2102)] = np.array(one, dtype=np.uint64)
     w[0] = np.array(one, dtype=np.uint64)
     return w
+
+
+def synthetic_csr(rng, nnz, one):
+    """CSR matrix with N_CONSTRAINTS rows and `nnz` terms spread evenly over the rows, columns uniform
+    over the assignment, coefficients 90 % one / 10 % random (the aggregator's are mostly +-1 and
+    small constants; the cost of a term does not depend on the value)."""
+    per = np.full(N_CONSTRAINTS, nnz // N_CONSTRAINTS, dtype=np.uint64)
+    per[: nnz - int(per.sum())] += 1
+    row_ptr = np.zeros(N_CONSTRAINTS + 1, dtype=np.uint64)
+    row_ptr[1:] = np.cumsum(per)
+    col = rng.integers(0, N_VARS + 1, size=nnz, dtype=np.uint32)
+    val = np.tile(one, (nnz, 1))
+    k = nnz // 10
+    val[rng.choice(nnz, k, replace=False)] = random_fr(rng, k)
+    return row_ptr, col, val
 
 
 def fr_generator():
@@ -164,6 +182,11 @@ class Workload:
             return t, t.numpy().view(np.uint64)
         m = 1 << LOG_M
         self.t_w, self.h_w = pinned(witness_like(rng, N_A))
+        # constraint system image: the evaluations <A_i,w>, <B_i,w>, <C_i,w> are computed
+        # on the device from the assignment, as the specialised prover of the hooks does
+        one = self.h_w[0].copy()
+        self.r1cs = ctx.r1cs_load(N_CONSTRAINTS, N_INPUTS, N_VARS, [synthetic_csr(rng, nz, one) for nz in NNZ])
+        assert ctx.r1cs_log_domain(self.r1cs) == LOG_M
         self.t_abc, self.h_abc = [], []
         for _ in range(3):
             t, h = pinned(random_fr(rng, m))
@@ -213,8 +236,7 @@ class Workload:
         ctx = self.ctxs[slot]
         out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
         w, idx = self.d_w.data_ptr(), self.d_idx.data_ptr()
-        ctx.qap_h_async(0, self.d_abc0[0].data_ptr(), self.d_abc0[1].data_ptr(), self.d_abc0[2].data_ptr(), self.g,
-                        log_m=LOG_M)
+        ctx.qap_h_from_witness_async(0, self.r1cs, w, self.g, device=True)
         ctx.msm_pinned_async(1, self.pk["A"], w, out[0], n=N_A, device=True)
         ctx.msm_pinned_async(2, self.pk["L"], w + 48 * (N_INPUTS + 1), out[4], n=N_L, device=True)
         ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=idx, device=True)
@@ -223,12 +245,13 @@ class Workload:
         return out
 
     def enqueue_e2e(self, slot=0):
-        """The same proof from HOST buffers (pinned): what a hooked prover passes in. The witness
-        crosses PCIe once (shared by A, B, L), aA/aB/aC once, coefficients_for_H come back."""
+        """The same proof from HOST buffers (pinned), exactly the calls the specialised prover of the
+        hooks makes (zecale_gpu_hooks::evaluate_fused): the assignment crosses PCIe once (shared by the
+        mat-vecs and by A, B, L), five points come back."""
         ctx = self.ctxs[slot]
         out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
         w = self.h_w
-        ctx.qap_h_async(0, self.h_abc[0], self.h_abc[1], self.h_abc[2], self.g, out=self.h_out[slot])
+        ctx.qap_h_from_witness_async(0, self.r1cs, w, self.g)
         ctx.msm_pinned_async(1, self.pk["A"], w, out[0], n=N_A)
         ctx.msm_pinned_async(2, self.pk["L"], w[N_INPUTS + 1:], out[4], n=N_L)
         ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=self.b_index)
@@ -247,8 +270,8 @@ class Workload:
                 ctx.msm_pinned(self.pk["H"], h, n=N_H),
                 ctx.msm_pinned(self.pk["L"], w[N_INPUTS + 1:], n=N_L)]
 
-    E2E_H2D = 3 * (1 << LOG_M) * 48 + N_A * 48 + N_B * 8
-    E2E_D2H = ((1 << LOG_M)) * 48 + 5 * 288
+    E2E_H2D = N_A * 48 + N_B * 8      # the assignment [1, primary, aux] and the B-query index list
+    E2E_D2H = 5 * 288                 # the five MSM results (coefficients_for_H never leave the device)
 
     def isolated_kernels(self):
         """The dominant kernels timed ALONE (nothing else on the GPU), on the step's own inputs:
@@ -284,6 +307,7 @@ class Workload:
     def close(self):
         for p in self.pk.values():
             p.release()
+        self.ctx.r1cs_free(self.r1cs)
         for c in self.ctxs:
             c.close()
 
@@ -399,8 +423,9 @@ def run_b200(args, rank, world, local_rank):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32x24 (761-bit Fq) / u32x12 (377-bit Fr)",
             "data": "synthetic (seeded curve points k_i*G, aggregator-like witness)",
-            "config": {"workload": "batch-8 aggregator Groth16 prove hot path: H-poly (7 NTT, m=2^18) + MSM A/B(G2,G1)/H/L",
+            "config": {"workload": "batch-8 aggregator Groth16 prove hot path: witness map (A.w,B.w,C.w mat-vecs + 7 NTT, m=2^18) + MSM A/B(G2,G1)/H/L",
                        "msm_sizes": {"A": N_A, "B_g2": N_B, "B_g1": N_B, "H": N_H, "L": N_L}, "ntt_log_m": LOG_M,
+                       "r1cs": {"constraints": N_CONSTRAINTS, "nnz_abc": list(NNZ)},
                        "parallelism": "replicas (one proof stream per GPU)" if world > 1 else "single GPU",
                        "proofs_in_flight": args.depth,
                        "l2": "inputs larger than L2 (158 MB of bases per step)"},
@@ -494,7 +519,7 @@ def run_reference(args, rank, world):
         t, split = rw.step()
         ts.append(t)
     t = sum(ts) / len(ts)
-    sample = ("each step: 7 libfqfft transforms (m=2^18) + five libff::multi_exp<BDLO12_signed, special> calls on the first "
+    sample = ("each step: 7 libfqfft transforms (m=2^18; the serial A.w/B.w/C.w mat-vecs of the reference, ~0.3 s, are NOT included) + five libff::multi_exp<BDLO12_signed, special> calls on the first "
               "%d%% of each base vector, MSM seconds scaled by %.0fx; warm-up = one 2%% step" % (int(frac * 100), 1 / frac))
     return {"impl": "reference", "metric": METRIC, "value": 1.0 / t, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
