@@ -11,6 +11,14 @@ from oracle.ref import ints_to_limbs
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=["xyzz", "tree"], autouse=True)
+def acc_mode(request, monkeypatch):
+    """Every MSM case runs under both bucket-accumulation kernels (XYZZ chains = default; batched affine
+    pair tree = ZECALE_GPU_ACC=tree, read by the library at each call)."""
+    monkeypatch.setenv("ZECALE_GPU_ACC", request.param)
+    return request.param
+
+
 def _inf(one_limbs):
     z = np.zeros(36, dtype=np.uint64)
     z[12:24] = one_limbs

@@ -148,6 +148,60 @@ unstep:
     MUL  T4, T4, T4         ; 1/ZZ
     MUL  QX, X, T4
     HOOK 0
+; ---------------------------------------------------------------- batched affine pair additions (k_tree_round)
+; A thread adds K independent pairs P_j + Q_j in affine coordinates with ONE inversion (Montgomery's trick
+; over the denominators d_j = qx_j - px_j). P in (X, Y), Q in (QX, QY), relative slot @0 = product of the
+; denominators before pair j, K1 = running product, T4 = running inverse.
+; forward step:  d = qx - px ; @0 = K1 ; K1 *= d          HOOK 0 = pair joins the inversion
+;   same x: equal points -> tangent (d = 2 py, HOOK 2 marks it); opposite points / 2-torsion -> HOOK 1 (sum = infinity)
+tfwd:
+    SUB  T0, QX, X
+    JZ   T0, tfwd_samex
+tfwd_go:
+    MOV  @0, K1
+    MUL  K1, K1, T0
+    HOOK 0
+tfwd_samex:
+    HOOK 3                  ; the forward pass only loads x: fetch py, qy now
+    SUB  T1, QY, Y
+    JZ   T1, tfwd_dbl
+    HOOK 1
+tfwd_dbl:
+    ADD  T0, Y, Y
+    JZ   T0, tfwd_inf
+    HOOK 2
+tfwd_inf:
+    HOOK 1
+; T4 = 1 / K1
+tinv:
+    MOV  T1, K1
+    CALL inv
+    MOV  T4, T0
+    HOOK 0
+; backward step (pairs in reverse order): 1/d = T4 * @0 ; T4 *= d ; lambda = (qy - py)/d ;
+;   x3 = lambda^2 - px - qx -> T2 ; y3 = lambda (px - x3) - py -> T3
+tbwd:
+    SUB  T0, QX, X
+    MUL  T1, T4, @0
+    MUL  T4, T4, T0
+    SUB  T2, QY, Y
+tbwd_fin:
+    MUL  T1, T1, T2
+    MUL  T2, T1, T1
+    SUB  T2, T2, X
+    SUB  T2, T2, QX
+    SUB  T3, X, T2
+    MUL  T3, T1, T3
+    SUB  T3, T3, Y
+    HOOK 0
+tbwd_dbl:                   ; Q == P: lambda = 3 px^2 / (2 py)
+    ADD  T0, Y, Y
+    MUL  T1, T4, @0
+    MUL  T4, T4, T0
+    MUL  T2, X, X
+    ADD  T3, T2, T2
+    ADD  T2, T3, T2
+    JMP  tbwd_fin
 """
 
 ADD_TEMPLATE = r"""
@@ -221,7 +275,14 @@ PROGRAM += ADD_TEMPLATE.format(S="", BX="QX", BY="QY", BZZ="QZZ", BZZZ="QZZZ", *
 # second accumulator R += acc (running-sum bucket reduction)
 PROGRAM += ADD_TEMPLATE.format(S="_r", AX="RX", AY="RY", AZZ="RZZ", AZZZ="RZZZ", BX="X", BY="Y", BZZ="ZZ", BZZZ="ZZZ")
 
-ENTRY_POINTS = ["madd", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep", "inv_fermat"]
+ENTRY_POINTS = ["tfwd", "tfwd_go", "tinv", "tbwd", "tbwd_dbl", "madd", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep", "inv_fermat"]
+
+
+def slot(x):
+    """Absolute slot name, or @k = relative slot k (bit 7 set; see fqvm_run)."""
+    if x.startswith("@"):
+        return 0x80 | int(x[1:])
+    return SLOTS[x]
 
 
 def assemble(text):
@@ -244,16 +305,16 @@ def assemble(text):
         o = OPS[op]
         d = a = b = 0
         if op in ("MUL", "ADD", "SUB"):
-            d, a, b = (SLOTS[x] for x in args)
+            d, a, b = (slot(x) for x in args)
             imm = a | (b << 8)
         elif op in ("MOV", "INVP"):
-            d, a = SLOTS[args[0]], SLOTS[args[1]]
+            d, a = slot(args[0]), slot(args[1])
             imm = a
         elif op in ("ONE", "ZERO", "LDR3"):
-            d = SLOTS[args[0]]
+            d = slot(args[0])
             imm = 0
         elif op == "JZ":
-            d = SLOTS[args[0]]
+            d = slot(args[0])
             imm = labels[args[1]]
         elif op in ("JMP", "JBIT", "DECJNZ", "CALL"):
             imm = labels[args[0]]

@@ -29,6 +29,7 @@
 #include "field_asm.cuh"
 #include "field_consts.cuh"
 #include "fqvm_prog.cuh"
+#include "fq_inv.cuh"
 
 namespace zecale {
 
@@ -53,11 +54,14 @@ struct alignas(16) Proj {
 static_assert(sizeof(Affine) == 192 && sizeof(XYZZ) == 384 && sizeof(Proj) == 288, "point layout");
 
 // Slot file: VS_COUNT Fq values as uint4[6] each.
-struct FqSlots {
-    uint4 w[VS_COUNT * 6];
+template <int N>
+struct FqSlotFile {
+    uint4 w[N * 6];
 };
+using FqSlots = FqSlotFile<VS_COUNT>;
 
-__device__ __forceinline__ void vs_load(uint32_t (&x)[24], const FqSlots &S, uint32_t slot)
+template <class SF>
+__device__ __forceinline__ void vs_load(uint32_t (&x)[24], const SF &S, uint32_t slot)
 {
     const uint4 *p = S.w + slot * 6;
 #pragma unroll
@@ -70,7 +74,8 @@ __device__ __forceinline__ void vs_load(uint32_t (&x)[24], const FqSlots &S, uin
     }
 }
 
-__device__ __forceinline__ void vs_store(FqSlots &S, uint32_t slot, const uint32_t (&x)[24])
+template <class SF>
+__device__ __forceinline__ void vs_store(SF &S, uint32_t slot, const uint32_t (&x)[24])
 {
     uint4 *p = S.w + slot * 6;
 #pragma unroll
@@ -78,7 +83,8 @@ __device__ __forceinline__ void vs_store(FqSlots &S, uint32_t slot, const uint32
 }
 
 // slot <- global/shared/any 16-byte aligned Fq
-__device__ __forceinline__ void vs_set(FqSlots &S, uint32_t slot, const Fq *src)
+template <class SF>
+__device__ __forceinline__ void vs_set(SF &S, uint32_t slot, const Fq *src)
 {
     const uint4 *s = reinterpret_cast<const uint4 *>(src);
     uint4 *p = S.w + slot * 6;
@@ -86,7 +92,8 @@ __device__ __forceinline__ void vs_set(FqSlots &S, uint32_t slot, const Fq *src)
     for (int k = 0; k < 6; k++) p[k] = s[k];
 }
 
-__device__ __forceinline__ void vs_get(Fq *dst, const FqSlots &S, uint32_t slot)
+template <class SF>
+__device__ __forceinline__ void vs_get(Fq *dst, const SF &S, uint32_t slot)
 {
     uint4 *d = reinterpret_cast<uint4 *>(dst);
     const uint4 *p = S.w + slot * 6;
@@ -94,21 +101,24 @@ __device__ __forceinline__ void vs_get(Fq *dst, const FqSlots &S, uint32_t slot)
     for (int k = 0; k < 6; k++) d[k] = p[k];
 }
 
-__device__ __forceinline__ void vs_zero(FqSlots &S, uint32_t slot)
+template <class SF>
+__device__ __forceinline__ void vs_zero(SF &S, uint32_t slot)
 {
     uint4 *p = S.w + slot * 6;
 #pragma unroll
     for (int k = 0; k < 6; k++) p[k] = make_uint4(0, 0, 0, 0);
 }
 
-__device__ __forceinline__ void vs_one(FqSlots &S, uint32_t slot)
+template <class SF>
+__device__ __forceinline__ void vs_one(SF &S, uint32_t slot)
 {
     uint4 *p = S.w + slot * 6;
 #pragma unroll
     for (int k = 0; k < 6; k++) p[k] = make_uint4(FQ_ONE[4 * k], FQ_ONE[4 * k + 1], FQ_ONE[4 * k + 2], FQ_ONE[4 * k + 3]);
 }
 
-__device__ __forceinline__ bool vs_is_zero(const FqSlots &S, uint32_t slot)
+template <class SF>
+__device__ __forceinline__ bool vs_is_zero(const SF &S, uint32_t slot)
 {
     const uint4 *p = S.w + slot * 6;
     uint32_t acc = 0;
@@ -121,7 +131,8 @@ __device__ __forceinline__ bool vs_is_zero(const FqSlots &S, uint32_t slot)
 }
 
 // slot <- -(*src) mod q (0 stays 0); cf. fp.tcc:617-630
-__device__ __forceinline__ void vs_set_neg(FqSlots &S, uint32_t slot, const Fq *src)
+template <class SF>
+__device__ __forceinline__ void vs_set_neg(SF &S, uint32_t slot, const Fq *src)
 {
     uint32_t a[24], z[24], r[24];
     const uint4 *s = reinterpret_cast<const uint4 *>(src);
@@ -139,28 +150,32 @@ __device__ __forceinline__ void vs_set_neg(FqSlots &S, uint32_t slot, const Fq *
 }
 
 // Accumulator (slots X..ZZZ) <-> memory
-__device__ __forceinline__ void vs_store_acc(XYZZ *dst, const FqSlots &S)
+template <class SF>
+__device__ __forceinline__ void vs_store_acc(XYZZ *dst, const SF &S)
 {
     vs_get(&dst->x, S, VS_X);
     vs_get(&dst->y, S, VS_Y);
     vs_get(&dst->zz, S, VS_ZZ);
     vs_get(&dst->zzz, S, VS_ZZZ);
 }
-__device__ __forceinline__ void vs_load_q(FqSlots &S, const XYZZ *src)
+template <class SF>
+__device__ __forceinline__ void vs_load_q(SF &S, const XYZZ *src)
 {
     vs_set(S, VS_QX, &src->x);
     vs_set(S, VS_QY, &src->y);
     vs_set(S, VS_QZZ, &src->zz);
     vs_set(S, VS_QZZZ, &src->zzz);
 }
-__device__ __forceinline__ void vs_load_acc(FqSlots &S, const XYZZ *src)
+template <class SF>
+__device__ __forceinline__ void vs_load_acc(SF &S, const XYZZ *src)
 {
     vs_set(S, VS_X, &src->x);
     vs_set(S, VS_Y, &src->y);
     vs_set(S, VS_ZZ, &src->zz);
     vs_set(S, VS_ZZZ, &src->zzz);
 }
-__device__ __forceinline__ void vs_acc_inf(FqSlots &S)
+template <class SF>
+__device__ __forceinline__ void vs_acc_inf(SF &S)
 {
     vs_zero(S, VS_X);
     vs_one(S, VS_Y);
@@ -268,17 +283,21 @@ __device__ __forceinline__ void fq_inv_plain(uint32_t (&r)[24], const uint32_t (
 }
 
 // Run from `pc` until the hook returns false. hook(id, pc, S) may change pc.
-template <class Hook>
-__device__ __forceinline__ void fqvm_run(FqSlots &S, uint32_t pc, Hook &&hook)
+// Slot operands with bit 7 set are relative: slot = (operand & 0x7f) + rel (the hook moves `rel`
+// to walk an array of per-chain slot groups with one program).
+template <bool REL, bool INV, class SF, class Hook>
+__device__ __forceinline__ void fqvm_run_impl(SF &S, uint32_t pc, Hook &&hook, const uint32_t &rel)
 {
     uint32_t ret = 0, cnt = 0;
+    auto rs = [&](uint32_t s) -> uint32_t { return (REL && (s & 0x80u)) ? (s & 0x7fu) + rel : s; };
     for (;;) {
         const uint32_t u = FQVM_CODE[pc++];
-        const uint32_t op = u & 0xffu, d = (u >> 8) & 0xffu, imm = u >> 16;
+        const uint32_t op = u & 0xffu, imm = u >> 16;
+        const uint32_t d = op <= VOP_JZ ? rs((u >> 8) & 0xffu) : (u >> 8) & 0xffu;
         if (op <= VOP_SUB) {
             uint32_t x[24], y[24], z[24];
-            vs_load(x, S, imm & 0xffu);
-            vs_load(y, S, imm >> 8);
+            vs_load(x, S, rs(imm & 0xffu));
+            vs_load(y, S, rs(imm >> 8));
             if (op == VOP_MUL)
                 fq_mul_regs(z, x, y);
             else if (op == VOP_ADD)
@@ -290,7 +309,7 @@ __device__ __forceinline__ void fqvm_run(FqSlots &S, uint32_t pc, Hook &&hook)
         }
         switch (op) {
         case VOP_MOV: {
-            const uint4 *s = S.w + imm * 6;
+            const uint4 *s = S.w + rs(imm) * 6;
             uint4 *p = S.w + d * 6;
 #pragma unroll
             for (int k = 0; k < 6; k++) p[k] = s[k];
@@ -318,9 +337,10 @@ __device__ __forceinline__ void fqvm_run(FqSlots &S, uint32_t pc, Hook &&hook)
             break;
         case VOP_RET: pc = ret; break;
         case VOP_INVP: {
+            if (!INV) return; // kernels whose programs never invert leave the inversion code out
             uint32_t x[24], z[24];
             vs_load(x, S, imm);
-            fq_inv_plain(z, x);
+            fq_inv_bingcd(z, x, FQ_P, FQ_INV32);
             vs_store(S, d, z);
             break;
         }
@@ -336,6 +356,25 @@ __device__ __forceinline__ void fqvm_run(FqSlots &S, uint32_t pc, Hook &&hook)
         default: return; // HALT
         }
     }
+}
+
+template <class SF, class Hook>
+__device__ __forceinline__ void fqvm_run(SF &S, uint32_t pc, Hook &&hook, const uint32_t &rel)
+{
+    fqvm_run_impl<true, true>(S, pc, hook, rel);
+}
+template <class SF, class Hook>
+__device__ __forceinline__ void fqvm_run(SF &S, uint32_t pc, Hook &&hook)
+{
+    const uint32_t rel0 = 0;
+    fqvm_run_impl<false, true>(S, pc, hook, rel0);
+}
+// for kernels that only run point additions / doublings (no INVP in their programs)
+template <class SF, class Hook>
+__device__ __forceinline__ void fqvm_run_noinv(SF &S, uint32_t pc, Hook &&hook)
+{
+    const uint32_t rel0 = 0;
+    fqvm_run_impl<false, false>(S, pc, hook, rel0);
 }
 
 // ---------------------------------------------------------------- Fr (register form)

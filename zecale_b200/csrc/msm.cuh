@@ -29,6 +29,7 @@
 #pragma once
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 
 #include "fqvm.cuh"
 
@@ -53,6 +54,24 @@ struct MsmPlan {
     uint32_t lbits[MSM_MAX_LEVELS]; // log2 segment length per level
     uint64_t n_buckets;    // V * NB
     uint64_t max_tasks;
+    uint32_t acc_mode;     // MSM_ACC_XYZZ | MSM_ACC_TREE
+    uint32_t tree_rounds;  // pair-tree rounds launched = ceil(log2(n * G)) (a bucket holds <= n*G entries)
+};
+
+// Bucket accumulation mode: ZECALE_GPU_ACC = "tree" (batched affine pair tree, k_tree_round) or
+// "xyzz" (one XYZZ chain per task, k_accumulate). Read at every plan so tests can switch it.
+static constexpr uint32_t MSM_ACC_XYZZ = 0, MSM_ACC_TREE = 1;
+static constexpr uint32_t MSM_ACC_DEFAULT = MSM_ACC_XYZZ;
+inline uint32_t msm_acc_mode()
+{
+    const char *v = getenv("ZECALE_GPU_ACC");
+    if (v && v[0] == 'x') return MSM_ACC_XYZZ;
+    if (v && v[0] == 't') return MSM_ACC_TREE;
+    return MSM_ACC_DEFAULT;
+}
+
+struct TreeMeta {
+    uint32_t max_count; // largest bucket (set by k_tree_count)
 };
 
 inline uint32_t msm_default_c(uint32_t n)
@@ -89,6 +108,9 @@ inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_s
     while ((sq + 1) * (sq + 1) <= avg) sq++;
     if (S < avg + 4 * sq + 8) S = avg + 4 * sq + 8;
     p.S = (uint32_t)S;
+    p.acc_mode = msm_acc_mode();
+    p.tree_rounds = 0;
+    while ((1ull << p.tree_rounds) < (uint64_t)n * p.G) p.tree_rounds++;
     p.n_buckets = (uint64_t)p.V * p.NB;
     p.max_tasks = ((uint64_t)n * p.W) / p.S + p.n_buckets + 1;
     uint32_t rem = c - 1;
@@ -442,6 +464,20 @@ __global__ void k_task_count(MsmPlan p, const uint32_t *counts, uint32_t *ntasks
     ntasks[b] = msm_bucket_tasks(counts[b], p.S);
 }
 
+// Pair-tree mode: one "task" (= one partial sum) per non-empty bucket, and the largest bucket size.
+__global__ void k_tree_count(MsmPlan p, const uint32_t *counts, uint32_t *ntasks, TreeMeta *meta)
+{
+    size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t c = b < p.n_buckets ? counts[b] : 0;
+    if (b < p.n_buckets) ntasks[b] = c ? 1u : 0u;
+    // one atomic per warp
+    for (int d = 16; d; d >>= 1) {
+        uint32_t o = __shfl_xor_sync(0xffffffffu, c, d);
+        c = o > c ? o : c;
+    }
+    if ((threadIdx.x & 31) == 0 && c) atomicMax(&meta->max_count, c);
+}
+
 // Task t of bucket b covers entries [start, start+len). size_hist bins tasks by length
 // (capped) for the length sort.
 static constexpr uint32_t MSM_LEN_BINS = 1024;
@@ -513,7 +549,259 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
     };
     uint32_t pc = 0;
     if (!fetch(pc, S)) return;
-    fqvm_run(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); });
+    fqvm_run_noinv(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); });
+}
+
+// ------------------------------------------------------------------ accumulate: batched affine pair tree
+// Bucket b holds n_b entries at entries[off[b] .. off[b] + n_b). Round r halves every bucket:
+// level r has cnt_r(b) = ceil(n_b / 2^r) affine points per bucket, level r+1 gets
+//     out[i] = in[2i] + in[2i+1]   (or a copy of in[2i] when the count is odd),
+// until one point per bucket is left. Level 0 is the base image addressed through `entries`
+// (index | sign bit); level r >= 1 is a dense array of affine points where bucket b starts at
+//     base_r(b) = (off[b] >> r) + b
+// (closed form, buckets cannot overlap because floor((o+n)/2^r) - floor(o/2^r) + 1 >= ceil(n/2^r)),
+// so level r has at most (M >> r) + n_buckets slots and levels alternate between two buffers.
+// All additions of a round are independent: a thread owns K consecutive output slots and adds its
+// K pairs in affine coordinates with ONE field inversion (Montgomery's trick over the
+// denominators qx - px; programs tfwd/tinv/tbwd of the Fq VM): 6 products per addition +
+// inversion / K, against 10 for the XYZZ mixed addition, and the work of a round divides evenly
+// over threads whatever the bucket sizes (no tasks, no length sort, no heavy-bucket fold).
+// The special cases of libff's add / mixed_add (bw6_761_g1.cpp:160-358: an operand at infinity,
+// equal points -> doubling, opposite points -> infinity) are per-pair flags; infinity is (0,0).
+// The point pair is read again from L2/HBM in the backward pass instead of being kept.
+__device__ __forceinline__ uint32_t tree_rounds_needed(uint32_t max_count)
+{
+    uint32_t r = 0;
+    while ((1u << r) < max_count) r++;
+    return r;
+}
+
+// level-r slot index of bucket b's first point (r >= 1)
+__device__ __forceinline__ uint32_t tree_base(const uint32_t *off, uint32_t b, uint32_t r) { return (off[b] >> r) + b; }
+
+template <class SF>
+__device__ __forceinline__ void tree_load_entry(SF &S, uint32_t sx, uint32_t sy, const Affine *bases, uint32_t ent)
+{
+    const Affine *pt = bases + (ent & 0x7fffffffu);
+    vs_set(S, sx, &pt->x);
+    if (ent >> 31)
+        vs_set_neg(S, sy, &pt->y);
+    else
+        vs_set(S, sy, &pt->y);
+}
+
+template <class SF>
+__device__ __forceinline__ void tree_store_slots(Affine *dst, const SF &S, uint32_t sx, uint32_t sy)
+{
+    vs_get(&dst->x, S, sx);
+    vs_get(&dst->y, S, sy);
+}
+
+__device__ __forceinline__ void affine_store_inf(Affine *dst)
+{
+    uint4 *d = reinterpret_cast<uint4 *>(dst);
+#pragma unroll
+    for (int k = 0; k < 12; k++) d[k] = make_uint4(0, 0, 0, 0);
+}
+
+template <int K>
+__global__ void __launch_bounds__(128, 3)
+k_tree_round(uint32_t r, uint32_t n_buckets, const uint32_t *off, const TreeMeta *meta, const Affine *bases,
+             const uint32_t *entries, const Affine *in, Affine *out)
+{
+    using SF = FqSlotFile<VS_COUNT + K>;
+    if (r >= tree_rounds_needed(meta->max_count)) return; // every bucket is already down to one point
+    const uint32_t slots = (off[n_buckets] >> (r + 1)) + n_buckets; // level r+1
+    const uint32_t s0 = (blockIdx.x * blockDim.x + threadIdx.x) * K;
+    // bucket of slot s0: the largest b with base_{r+1}(b) <= s0
+    uint32_t b = 0, cur_base = 0, next_base = 0;
+    if (s0 < slots) {
+        uint32_t lo = 0, hi = n_buckets - 1;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if (tree_base(off, mid, r + 1) <= s0)
+                lo = mid;
+            else
+                hi = mid - 1;
+        }
+        b = lo;
+        cur_base = tree_base(off, b, r + 1);
+        next_base = tree_base(off, b + 1, r + 1);
+    }
+    // Pass 1 (no arithmetic): classify the K slots. Padding slots are skipped, an odd point out and a
+    // pair with an operand at infinity are copied; real additions are listed in pidx/oidx so that
+    // the 32 lanes of the warp then run the same VM steps in lock-step whatever their slot mix.
+    uint32_t pidx[K]; // level-r index of P (Q = next)
+    uint8_t oidx[K];  // output slot - s0
+    uint32_t na = 0;
+    auto point_ptr = [&](uint32_t pos) -> const Affine * { return r == 0 ? bases + (entries[pos] & 0x7fffffffu) : in + pos; };
+    auto quick_inf = [&](const Affine *pt) -> bool { // (0,0); the first 16 bytes decide in all but 2^-128 of cases
+        const uint4 *w = reinterpret_cast<const uint4 *>(pt);
+        uint4 v = w[0];
+        if (v.x | v.y | v.z | v.w) return false;
+        uint32_t acc = 0;
+        for (int k = 1; k < 12; k++) {
+            v = w[k];
+            acc |= v.x | v.y | v.z | v.w;
+        }
+        return acc == 0;
+    };
+    auto copy_point = [&](Affine *dst, uint32_t pos) {
+        const uint4 *w = reinterpret_cast<const uint4 *>(point_ptr(pos));
+        uint4 *d = reinterpret_cast<uint4 *>(dst);
+        const bool neg = r == 0 && (entries[pos] >> 31);
+        if (!neg) {
+#pragma unroll
+            for (int k = 0; k < 12; k++) d[k] = w[k];
+            return;
+        }
+#pragma unroll
+        for (int k = 0; k < 6; k++) d[k] = w[k];
+        uint32_t y[24], z[24], ny[24];
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            uint4 v = w[6 + k];
+            y[4 * k] = v.x;
+            y[4 * k + 1] = v.y;
+            y[4 * k + 2] = v.z;
+            y[4 * k + 3] = v.w;
+            z[4 * k] = z[4 * k + 1] = z[4 * k + 2] = z[4 * k + 3] = 0;
+        }
+        fq_sub_regs(ny, z, y);
+#pragma unroll
+        for (int k = 0; k < 6; k++) d[6 + k] = make_uint4(ny[4 * k], ny[4 * k + 1], ny[4 * k + 2], ny[4 * k + 3]);
+    };
+    for (uint32_t j = 0; j < (uint32_t)K; j++) {
+        const uint32_t s = s0 + j;
+        if (s >= slots) break;
+        while (s >= next_base) {
+            b++;
+            cur_base = next_base;
+            next_base = tree_base(off, b + 1, r + 1);
+        }
+        const uint32_t i = s - cur_base;
+        const uint32_t o = off[b], nb = off[b + 1] - o;
+        const uint32_t cr = (nb + (1u << r) - 1) >> r; // points of this bucket at level r
+        if (i >= ((cr + 1) >> 1)) continue;            // padding slot
+        const uint32_t pos = (r == 0 ? o : (o >> r) + b) + 2 * i;
+        if (2 * i + 1 >= cr) { // odd one out: carried up unchanged
+            copy_point(out + s, pos);
+            continue;
+        }
+        if (quick_inf(point_ptr(pos))) {
+            copy_point(out + s, pos + 1);
+            continue;
+        }
+        if (quick_inf(point_ptr(pos + 1))) {
+            copy_point(out + s, pos);
+            continue;
+        }
+        pidx[na] = pos;
+        oidx[na] = (uint8_t)j;
+        na++;
+    }
+    // Pass 2: forward products of the denominators (x coordinates only), one inversion, backward
+    // additions. The lanes of a warp wait for each other before the inversion so that it is issued
+    // once per warp. (Sharing one inversion among the four warps of the CTA through shared memory
+    // was measured too: the three waiting warps cost more than the three inversions saved.)
+    __syncwarp();
+    if (na == 0) return;
+    SF S;
+    uint32_t act = 0, dbl = 0, rel = VS_COUNT, j = 0, phase = 0;
+    auto load_x = [&](SF &S_, uint32_t jj) {
+        rel = VS_COUNT + jj;
+        vs_set(S_, VS_X, &point_ptr(pidx[jj])->x);
+        vs_set(S_, VS_QX, &point_ptr(pidx[jj] + 1)->x);
+    };
+    auto load_y1 = [&](SF &S_, uint32_t sy, uint32_t pos) {
+        const Affine *pt = point_ptr(pos);
+        if (r == 0 && (entries[pos] >> 31))
+            vs_set_neg(S_, sy, &pt->y);
+        else
+            vs_set(S_, sy, &pt->y);
+    };
+    auto load_pair = [&](SF &S_, uint32_t jj) {
+        load_x(S_, jj);
+        load_y1(S_, VS_Y, pidx[jj]);
+        load_y1(S_, VS_QY, pidx[jj] + 1);
+    };
+    auto next_backward = [&](uint32_t &pc, SF &S_) -> bool {
+        if (!act) return false;
+        j = 31u - (uint32_t)__clz((int)act);
+        load_pair(S_, j);
+        pc = ((dbl >> j) & 1u) ? VPC_TBWD_DBL : VPC_TBWD;
+        return true;
+    };
+    vs_one(S, VS_K1);
+    load_x(S, 0);
+    fqvm_run(
+        S, VPC_TFWD,
+        [&](uint32_t id, uint32_t &pc, SF &S_) -> bool {
+            if (phase == 0) {
+                if (id == 3) { // equal x: the special cases need the y coordinates
+                    load_y1(S_, VS_Y, pidx[j]);
+                    load_y1(S_, VS_QY, pidx[j] + 1);
+                    return true;
+                }
+                if (id == 2) { // equal points: tangent, denominator 2 py already in T0
+                    dbl |= 1u << j;
+                    pc = VPC_TFWD_GO;
+                    return true;
+                }
+                if (id == 0)
+                    act |= 1u << j;
+                else
+                    affine_store_inf(out + s0 + oidx[j]); // P + (-P)
+                if (++j < na) {
+                    load_x(S_, j);
+                    pc = VPC_TFWD;
+                    return true;
+                }
+                __syncwarp(); // lanes with fewer additions wait here
+                if (!act) return false;
+                phase = 1;
+                pc = VPC_TINV; // T4 = 1 / product
+                return true;
+            }
+            if (phase == 2) {
+                tree_store_slots(out + s0 + oidx[j], S_, VS_T2, VS_T3);
+                act &= ~(1u << j);
+            }
+            phase = 2;
+            return next_backward(pc, S_);
+        },
+        rel);
+}
+
+// Bucket values (level R = rounds needed, one point per non-empty bucket) -> partial[task_off[b]] as
+// XYZZ with zz = zzz = 1, the form the running-sum levels read.
+__global__ void k_tree_finish(uint32_t n_buckets, const uint32_t *off, const uint32_t *task_off, const TreeMeta *meta,
+                              const Affine *bases, const uint32_t *entries, const Affine *lvl_odd, const Affine *lvl_even,
+                              XYZZ *partial)
+{
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_buckets) return;
+    const uint32_t o = off[b];
+    if (off[b + 1] == o) return;
+    const uint32_t R = tree_rounds_needed(meta->max_count);
+    FqSlots S;
+    if (R == 0) {
+        tree_load_entry(S, VS_X, VS_Y, bases, entries[o]);
+    } else {
+        const Affine *src = ((R & 1u) ? lvl_odd : lvl_even) + tree_base(off, b, R);
+        vs_set(S, VS_X, &src->x);
+        vs_set(S, VS_Y, &src->y);
+    }
+    XYZZ *dst = partial + task_off[b];
+    if (vs_is_zero(S, VS_X) && vs_is_zero(S, VS_Y)) {
+        xyzz_store_inf(dst);
+        return;
+    }
+    vs_get(&dst->x, S, VS_X);
+    vs_get(&dst->y, S, VS_Y);
+    vs_one(S, VS_T0);
+    vs_get(&dst->zz, S, VS_T0);
+    vs_get(&dst->zzz, S, VS_T0);
 }
 
 // Buckets that were cut into several tasks ("heavy" buckets, listed by k_task_fill; rare by the
@@ -536,7 +824,7 @@ k_fold_heavy(const uint32_t *heavy_list, const uint32_t *heavy_count, const uint
                 FqSlots S;
                 vs_load_acc(S, dst);
                 vs_load_q(S, dst + step);
-                fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &, FqSlots &S_) {
+                fqvm_run_noinv(S, VPC_ADD, [&](uint32_t, uint32_t &, FqSlots &S_) {
                     vs_store_acc(dst, S_);
                     return false;
                 });
@@ -601,7 +889,7 @@ k_reduce_level(ReduceLevel r, const uint32_t *task_off, const XYZZ *inA, const X
             }
         };
         load_item(S, s * L + j);
-        fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        fqvm_run_noinv(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
             if (phase == 0) {
                 if (++sub < nsub) { // next partial of the same bucket
                     vs_load_q(S_, inA + sub_t0 + sub);
@@ -635,7 +923,7 @@ k_reduce_level(ReduceLevel r, const uint32_t *task_off, const XYZZ *inA, const X
         uint32_t j = 1;
         vs_load_acc(S, src);
         vs_load_q(S, src + 1);
-        fqvm_run(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        fqvm_run_noinv(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
             if (++j >= L) {
                 vs_store_acc(outC + (size_t)a * n_out + s, S_);
                 return false;
@@ -758,6 +1046,8 @@ struct MsmBuffers {
     uint32_t *counts, *offsets, *cursor, *ntasks, *task_off, *task_start, *task_len, *task_bucket, *order, *len_hist, *len_cursor,
         *entries, *scan_tmp;
     XYZZ *partial, *lvlA[2], *lvlC[2];
+    Affine *tree_lvl[2]; // pair-tree levels: odd levels in [0], even levels >= 2 in [1]
+    TreeMeta *tree_meta;
     Proj *result;
     size_t total;
 };
@@ -802,13 +1092,34 @@ inline MsmBuffers msm_layout(const MsmPlan &p, uint8_t *base)
         b.lvlA[i] = (XYZZ *)take(n1 * sizeof(XYZZ));
         b.lvlC[i] = (XYZZ *)take(carry_items * sizeof(XYZZ));
     }
+    b.tree_lvl[0] = b.tree_lvl[1] = nullptr;
+    b.tree_meta = (TreeMeta *)take(sizeof(TreeMeta));
+    if (p.acc_mode == MSM_ACC_TREE) {
+        b.tree_lvl[0] = (Affine *)take(((nd >> 1) + nbk + 1) * sizeof(Affine));
+        b.tree_lvl[1] = (Affine *)take(((nd >> 2) + nbk + 1) * sizeof(Affine));
+    }
     b.result = (Proj *)take(sizeof(Proj));
     b.total = off;
     return b;
 }
 
 // Number of kernel launches msm_launch_front + msm_launch_tail issue for plan p.
-inline uint64_t msm_launch_count(const MsmPlan &p) { return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 1 + p.n_levels + 1; }
+inline uint64_t msm_launch_count(const MsmPlan &p)
+{
+    if (p.acc_mode == MSM_ACC_TREE) return 1 + 3 + 1 + 1 + 3 + p.tree_rounds + 1 + p.n_levels + 1;
+    return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 1 + p.n_levels + 1;
+}
+
+// K pairs per thread for a round expected to hold `pairs` additions: a larger K spreads the
+// inversion thinner, a smaller one keeps a full wave of threads (148 SM x 3 CTA x 128) in the air.
+template <int K>
+inline void tree_round_launch(const MsmPlan &p, const MsmBuffers &b, uint32_t r, const Affine *d_bases, cudaStream_t st)
+{
+    const uint64_t slots = (((uint64_t)p.n * p.W) >> (r + 1)) + p.n_buckets;
+    const unsigned blocks = (unsigned)(((slots + K - 1) / K + 127) / 128);
+    k_tree_round<K><<<blocks, 128, 0, st>>>(r, (uint32_t)p.n_buckets, b.offsets, b.tree_meta, d_bases, b.entries,
+                                            r ? b.tree_lvl[(r - 1) & 1] : nullptr, b.tree_lvl[r & 1]);
+}
 
 // First half of an MSM on `st`: digit decomposition, counting sort by bucket, task cutting and
 // the bucket accumulation kernel (the throughput-bound part). d_bases: affine image (G copies of
@@ -826,6 +1137,28 @@ inline cudaError_t msm_launch_front(const MsmPlan &p, const MsmBuffers &b, const
     size_t nd = (size_t)n * p.W;
     k_scatter<<<(unsigned)((nd + 255) / 256), 256, 0, st>>>(p, b.digits, b.cursor, b.entries);
     unsigned gb = (unsigned)((p.n_buckets + 255) / 256);
+    if (p.acc_mode == MSM_ACC_TREE) {
+        cudaMemsetAsync(b.tree_meta, 0, sizeof(TreeMeta), st);
+        k_tree_count<<<gb, 256, 0, st>>>(p, b.counts, b.ntasks, b.tree_meta);
+        exclusive_scan_u32(b.ntasks, p.n_buckets, b.task_off, b.scan_tmp, st);
+        if (acc_ev0) cudaEventRecord(acc_ev0, st);
+        const uint64_t wave = 148ull * 3 * 128;
+        for (uint32_t r = 0; r < p.tree_rounds; r++) {
+            const uint64_t pairs = ((uint64_t)n * p.W) >> (r + 1);
+            static const char *force_k = getenv("ZECALE_GPU_TREE_K"); // experiments: 8 | 16 | 32 for every round
+            const uint32_t fk = force_k ? (uint32_t)atoi(force_k) : 0; // 0 = by size
+            if (fk ? fk == 32 : pairs >= 32 * wave)
+                tree_round_launch<32>(p, b, r, d_bases, st);
+            else if (fk ? fk == 16 : pairs >= 16 * wave)
+                tree_round_launch<16>(p, b, r, d_bases, st);
+            else
+                tree_round_launch<8>(p, b, r, d_bases, st);
+        }
+        k_tree_finish<<<gb, 256, 0, st>>>((uint32_t)p.n_buckets, b.offsets, b.task_off, b.tree_meta, d_bases, b.entries,
+                                          b.tree_lvl[0], b.tree_lvl[1], b.partial);
+        if (acc_ev1) cudaEventRecord(acc_ev1, st);
+        return cudaGetLastError();
+    }
     k_task_count<<<gb, 256, 0, st>>>(p, b.counts, b.ntasks);
     exclusive_scan_u32(b.ntasks, p.n_buckets, b.task_off, b.scan_tmp, st);
     // heavy-bucket list: reuses ntasks (dead after its scan); counter = spare word of len_hist
@@ -846,7 +1179,8 @@ inline cudaError_t msm_launch_front(const MsmPlan &p, const MsmBuffers &b, const
 // buffers.result.
 inline cudaError_t msm_launch_tail(const MsmPlan &p, const MsmBuffers &b, cudaStream_t st)
 {
-    k_fold_heavy<<<MSM_FOLD_BLOCKS, 32, 0, st>>>(b.ntasks, b.len_hist + MSM_LEN_BINS + 1, b.task_off, b.partial);
+    if (p.acc_mode != MSM_ACC_TREE)
+        k_fold_heavy<<<MSM_FOLD_BLOCKS, 32, 0, st>>>(b.ntasks, b.len_hist + MSM_LEN_BINS + 1, b.task_off, b.partial);
     ReduceLevel r{};
     r.n_in = (uint32_t)p.n_buckets;
     const XYZZ *inA = b.partial, *inC = nullptr;
