@@ -205,6 +205,16 @@ int zecale_gpu_qap_pointwise_dev(zecale_gpu_ctx *ctx, void *d_aA, const void *d_
  * libff special form (288 B each), k_i a non-zero 32-bit hash of (seed, i). HOST pointer. */
 int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t n, void *out_points);
 
+/* ---- fixed-base batch exponentiation (the trusted-setup generator's work) ----
+ * out_points[i] = (coeff * scalars[i]) * base, i < n, in libff special form (288 B each; zero =
+ * (0, one, 0)). Replaces libff::batch_exp / batch_exp_with_coeff (libff/algebra/
+ * scalar_multiplication/multiexp.tcc:876-947) followed by batch_to_special (:949-974) as used by
+ * r1cs_gg_ppzksnark_generator (libsnark r1cs_gg_ppzksnark.tcc:330-390) and kc_batch_exp
+ * (knowledge_commitment/kc_multiexp.tcc:115-239). base: one point in special form; scalars:
+ * Montgomery Fr, scalar_stride bytes apart; coeff: one Montgomery Fr or NULL. HOST pointers. */
+int zecale_gpu_batch_exp(zecale_gpu_ctx *ctx, int group, const void *base_point, const void *scalars, size_t scalar_stride,
+                         size_t n, const void *coeff, void *out_points);
+
 /* ---- introspection ----------------------------------------------------------------*/
 /* Number of kernel launches issued by this context so far (bench.py gpu_launches). */
 uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx);

@@ -84,6 +84,13 @@ class Ref:
         (self.L.zref_g1_bases_mul if group == 1 else self.L.zref_g2_bases_mul)(_p(scalars), _sz(scalars.shape[0]), _p(out))
         return out
 
+    def batch_exp(self, base, scalars, group=1, coeff=None):
+        """libff::batch_exp(_with_coeff) + batch_to_special: out[i] = (coeff * scalars[i]) * base."""
+        out = np.zeros((scalars.shape[0], 36), dtype=np.uint64)
+        self.L.zref_batch_exp(int(group), _p(base), _p(scalars), _sz(scalars.shape[0]),
+                              _p(coeff) if coeff is not None else None, _p(out))
+        return out
+
     def group_op(self, op, a, b=None, group=1):
         out = np.zeros_like(a)
         (self.L.zref_g1_op if group == 1 else self.L.zref_g2_op)(op, _p(a), _p(b if b is not None else a), _p(out), _sz(a.shape[0]))

@@ -325,6 +325,28 @@ extern "C" void zref_g2_bases_mul(const void *s, size_t n, void *out)
     bases_mul<G2>((const Fr *)s, n, (G2 *)out);
 }
 
+// The generator's fixed-base path as the reference runs it: get_exp_window_size / get_window_table /
+// batch_exp or batch_exp_with_coeff (multiexp.tcc:776-947), then batch_to_special (:949-974).
+template<typename G> static void ref_batch_exp(const G *base, const Fr *s, size_t n, const Fr *coeff, G *o)
+{
+    const size_t scalar_bits = Fr::size_in_bits();
+    const size_t window = libff::get_exp_window_size<G>(n ? n : 1);
+    libff::window_table<G> table = libff::get_window_table<G>(scalar_bits, window, *base);
+    std::vector<Fr> v(s, s + n);
+    std::vector<G> r = coeff ? libff::batch_exp_with_coeff<G, Fr>(scalar_bits, window, table, *coeff, v)
+                             : libff::batch_exp<G, Fr>(scalar_bits, window, table, v);
+    libff::batch_to_special<G>(r);
+    for (size_t i = 0; i < n; ++i)
+        o[i] = r[i];
+}
+extern "C" void zref_batch_exp(int group, const void *base, const void *s, size_t n, const void *coeff, void *out)
+{
+    if (group == 2)
+        ref_batch_exp<G2>((const G2 *)base, (const Fr *)s, n, (const Fr *)coeff, (G2 *)out);
+    else
+        ref_batch_exp<G1>((const G1 *)base, (const Fr *)s, n, (const Fr *)coeff, (G1 *)out);
+}
+
 // op: 0 operator+, 1 mixed_add (b special), 2 dbl(a), 3 to_special(a), 4 neg(a),
 //     5 add(), 6 scalar-mul by Fr in b's first 48 bytes (b stride = 288)
 template<typename G> static void group_op(int op, const G *a, const G *b, G *o, size_t n)

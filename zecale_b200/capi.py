@@ -64,6 +64,7 @@ EXPORTS = {
     "zecale_gpu_qap_h_async": (_i, [_vp, _i, _vp, _vp, _vp, _u, _vp, _vp]),
     "zecale_gpu_sync": (_i, [_vp]),
     "zecale_gpu_synth_bases": (_i, [_vp, _i, ctypes.c_uint64, _sz, _vp]),
+    "zecale_gpu_batch_exp": (_i, [_vp, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
     "zecale_gpu_kernel_ms": (_i, [_vp, _i, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]),
     "zecale_gpu_launch_count": (ctypes.c_uint64, [_vp]),
     "zecale_gpu_msm_window_bits": (_u, [_sz]),
@@ -277,6 +278,17 @@ class Context:
     def synth_bases(self, n, group=G1, seed=0):
         out = np.zeros((n, 36), dtype=np.uint64)
         self._ck(_lib.zecale_gpu_synth_bases(self._h, group, seed, n, _ptr(out)))
+        return out
+
+    def batch_exp(self, base, scalars, group=G1, coeff=None):
+        """out[i] = (coeff * scalars[i]) * base (libff::batch_exp + batch_to_special)."""
+        scalars = np.ascontiguousarray(scalars)
+        n = scalars.shape[0]
+        out = np.zeros((n, 36), dtype=np.uint64)
+        base = np.ascontiguousarray(base)
+        cf = np.ascontiguousarray(coeff) if coeff is not None else None
+        self._ck(_lib.zecale_gpu_batch_exp(self._h, group, _ptr(base), _ptr(scalars) if n else None, 48, n,
+                                           _ptr(cf) if cf is not None else None, _ptr(out)))
         return out
 
     def kernel_ms(self, kernel_class, reset=True):

@@ -1040,6 +1040,214 @@ __global__ void __launch_bounds__(32, 1) k_final(MsmPlan p, const XYZZ *C, Proj 
     });
 }
 
+// ------------------------------------------------------------------ fixed-base batch exponentiation
+// out[i] = (coeff * s_i) * g for one base g and n scalars: libff::batch_exp / batch_exp_with_coeff
+// (multiexp.tcc:808-947) followed by batch_to_special (:949-974), the work of the trusted setup
+// (r1cs_gg_ppzksnark_generator, r1cs_gg_ppzksnark.tcc:330-390; kc_batch_exp, kc_multiexp.tcc:115-239).
+// The reference builds a table of all window values on one thread and walks it per scalar with
+// general additions; here:
+//   k_bexp_powers : B_w = 2^(c w) g, one thread per window (c w doublings)          -> XYZZ
+//   k_bexp_table  : T[w][j-1] = j B_w, j < 2^c, one thread per entry (double-and-add) -> XYZZ
+//   k_xyzz_to_affine after each (one inversion per 8 points, Montgomery's trick)
+//   k_bexp_eval   : one thread per scalar: sum_w T[w][digit_w(s)] as a chain of mixed additions
+//   k_xyzz_to_affine -> libff special form {x, y, one} / zero {0, one, 0}
+// Window choice is free (the result is a group element, compared in normalised form).
+static constexpr uint32_t BEXP_C = 12;
+static constexpr uint32_t BEXP_W = (FR_SCALAR_BITS + BEXP_C - 1) / BEXP_C; // 32 windows
+static constexpr uint32_t BEXP_ROW = (1u << BEXP_C) - 1;                   // table entries per window
+static constexpr uint32_t TOAFF_K = 8;
+
+// in[i] XYZZ (zz == 0: infinity) -> affine (0,0 = infinity) and/or libff special form.
+__global__ void __launch_bounds__(128, 2)
+k_xyzz_to_affine(const XYZZ *in, uint32_t n, Affine *out_aff, Proj *out_proj, Fq *scratch_prefix)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t i0 = t * TOAFF_K;
+    if (i0 >= n) return;
+    const uint32_t i1 = i0 + TOAFF_K < n ? i0 + TOAFF_K : n;
+    FqSlots S;
+    uint32_t i = i0, stage = 0; // 0 forward products, 1 inverting, 2 backward
+    vs_one(S, VS_K1);
+    auto write_inf = [&](uint32_t k) {
+        if (out_aff) affine_store_inf(out_aff + k);
+        if (out_proj) {
+            uint4 *d = reinterpret_cast<uint4 *>(out_proj + k);
+            for (int q = 0; q < 18; q++) d[q] = make_uint4(0, 0, 0, 0);
+            for (int q = 0; q < 6; q++) d[6 + q] = make_uint4(FQ_ONE[4 * q], FQ_ONE[4 * q + 1], FQ_ONE[4 * q + 2], FQ_ONE[4 * q + 3]);
+        }
+    };
+    auto next_forward = [&](uint32_t &pc, FqSlots &S_) -> bool {
+        while (i < i1) {
+            vs_load_acc(S_, in + i);
+            if (!vs_is_zero(S_, VS_ZZ)) {
+                vs_get(scratch_prefix + i, S_, VS_K1);
+                pc = VPC_PRODSTEP; // K1 *= ZZZ
+                return true;
+            }
+            i++;
+        }
+        return false;
+    };
+    auto next_backward = [&](uint32_t &pc, FqSlots &S_) -> bool {
+        while (i > i0) {
+            i--;
+            vs_load_acc(S_, in + i);
+            if (!vs_is_zero(S_, VS_ZZ)) {
+                vs_set(S_, VS_T3, scratch_prefix + i);
+                pc = VPC_UNSTEP;
+                return true;
+            }
+            write_inf(i);
+        }
+        return false;
+    };
+    uint32_t pc0 = 0;
+    if (!next_forward(pc0, S)) { // all at infinity
+        for (uint32_t k = i0; k < i1; k++) write_inf(k);
+        return;
+    }
+    fqvm_run(S, pc0, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        if (stage == 0) {
+            i++;
+            if (next_forward(pc, S_)) return true;
+            stage = 1;
+            pc = VPC_INVPROD; // T0 = 1 / K1
+            return true;
+        }
+        if (stage == 1) {
+            stage = 2;
+            i = i1;
+            return next_backward(pc, S_);
+        }
+        if (out_aff) {
+            vs_get(&out_aff[i].x, S_, VS_QX);
+            vs_get(&out_aff[i].y, S_, VS_QY);
+        }
+        if (out_proj) {
+            Proj *o = out_proj + i;
+            vs_get(&o->X, S_, VS_QX);
+            vs_get(&o->Y, S_, VS_QY);
+            uint4 *d = reinterpret_cast<uint4 *>(&o->Z);
+            for (int q = 0; q < 6; q++) d[q] = make_uint4(FQ_ONE[4 * q], FQ_ONE[4 * q + 1], FQ_ONE[4 * q + 2], FQ_ONE[4 * q + 3]);
+        }
+        return next_backward(pc, S_);
+    });
+}
+
+// B_w = 2^(c w) g for w < W: thread w doubles g (affine, finite) c*w times.
+__global__ void __launch_bounds__(32, 1) k_bexp_powers(const Affine *g, XYZZ *out)
+{
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= BEXP_W) return;
+    FqSlots S;
+    vs_set(S, VS_X, &g->x);
+    vs_set(S, VS_Y, &g->y);
+    vs_one(S, VS_ZZ);
+    vs_one(S, VS_ZZZ);
+    uint32_t left = BEXP_C * w;
+    if (left == 0) {
+        vs_store_acc(out + w, S);
+        return;
+    }
+    fqvm_run_noinv(S, VPC_DBL, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        if (--left) {
+            pc = VPC_DBL;
+            return true;
+        }
+        vs_store_acc(out + w, S_);
+        return false;
+    });
+}
+
+// T[w][j-1] = j * B_w (B_w affine; (0,0) if the base has small order), 1 <= j <= BEXP_ROW:
+// double-and-add over the bits of j below its top bit.
+__global__ void __launch_bounds__(128, 2) k_bexp_table(const Affine *powers, XYZZ *out)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= BEXP_W * BEXP_ROW) return;
+    const uint32_t w = t / BEXP_ROW, j = t - w * BEXP_ROW + 1;
+    FqSlots S;
+    const Affine *b = powers + w;
+    vs_set(S, VS_QX, &b->x);
+    vs_set(S, VS_QY, &b->y);
+    if (vs_is_zero(S, VS_QX) && vs_is_zero(S, VS_QY)) {
+        xyzz_store_inf(out + t);
+        return;
+    }
+    vs_set(S, VS_X, &b->x);
+    vs_set(S, VS_Y, &b->y);
+    vs_one(S, VS_ZZ);
+    vs_one(S, VS_ZZZ);
+    int bit = 30 - __clz((int)j); // next bit below the top one
+    if (bit < 0) {
+        vs_store_acc(out + t, S);
+        return;
+    }
+    uint32_t phase = 0; // 0: a doubling just ran, 1: an addition just ran
+    fqvm_run_noinv(S, VPC_DBL, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        if (phase == 0 && ((j >> bit) & 1u)) {
+            phase = 1;
+            pc = VPC_MADD;
+            return true;
+        }
+        phase = 0;
+        if (bit == 0) {
+            vs_store_acc(out + t, S_);
+            return false;
+        }
+        bit--;
+        pc = VPC_DBL;
+        return true;
+    });
+}
+
+// out[i] = sum_w T[w][digit_w - 1], digits = BEXP_C-bit windows of the plain integer coeff * s_i.
+__global__ void __launch_bounds__(128, 3)
+k_bexp_eval(const Affine *table, const uint8_t *scalars, size_t sstride, uint32_t n, const Fr *coeff, XYZZ *out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    __align__(8) uint32_t v[14];
+    {
+        uint32_t m[12], t[12];
+        fr_load(m, reinterpret_cast<const Fr *>(scalars + (size_t)i * sstride));
+        if (coeff) {
+            uint32_t cf[12];
+            fr_load(cf, coeff);
+            fr_mul_regs(t, m, cf);
+#pragma unroll
+            for (int k = 0; k < 12; k++) m[k] = t[k];
+        }
+        fr_from_mont(t, m);
+#pragma unroll
+        for (int k = 0; k < 12; k++) v[k] = t[k];
+        v[12] = v[13] = 0;
+    }
+    FqSlots S;
+    vs_acc_inf(S);
+    uint32_t w = 0;
+    auto fetch = [&](uint32_t &pc, FqSlots &S_) -> bool {
+        for (; w < BEXP_W; w++) {
+            const uint32_t bit = w * BEXP_C, lo = bit >> 5, sh = bit & 31u;
+            const uint64_t two = (uint64_t)v[lo] | ((uint64_t)v[lo + 1] << 32);
+            const uint32_t d = (uint32_t)(two >> sh) & BEXP_ROW;
+            if (!d) continue;
+            const Affine *pt = table + (size_t)w * BEXP_ROW + (d - 1);
+            vs_set(S_, VS_QX, &pt->x);
+            vs_set(S_, VS_QY, &pt->y);
+            if (vs_is_zero(S_, VS_QX) && vs_is_zero(S_, VS_QY)) continue; // table entry at infinity
+            w++;
+            pc = VPC_MADD;
+            return true;
+        }
+        vs_store_acc(out + i, S_);
+        return false;
+    };
+    uint32_t pc0 = 0;
+    if (!fetch(pc0, S)) return;
+    fqvm_run_noinv(S, pc0, [&](uint32_t, uint32_t &pc, FqSlots &S_) { return fetch(pc, S_); });
+}
+
 // ------------------------------------------------------------------ workspace
 struct MsmBuffers {
     int32_t *digits;

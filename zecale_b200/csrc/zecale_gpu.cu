@@ -1340,6 +1340,64 @@ int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t
     return 0;
 }
 
+int zecale_gpu_batch_exp(zecale_gpu_ctx *ctx, int group, const void *base_point, const void *scalars, size_t scalar_stride,
+                         size_t n, const void *coeff, void *out_points)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!base_point || !out_points || (n && !scalars) || n >= (1ull << 31) || scalar_stride < sizeof(Fr) || (scalar_stride & 7) ||
+        (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_batch_exp: bad argument");
+    if (n == 0) return 0;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->cur->stream;
+    // workspace: [base affine + flag | powers XYZZ/affine | table XYZZ/affine | scalars | coeff | out XYZZ | prefix | out Proj]
+    const size_t n_tab = (size_t)BEXP_W * BEXP_ROW, n_max = n > n_tab ? n : n_tab;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        size_t o = off;
+        off += align_up(bytes, 256);
+        return o;
+    };
+    const size_t o_base = take(sizeof(Affine)), o_inf = take(256), o_pw_x = take(BEXP_W * sizeof(XYZZ)),
+                 o_pw_a = take(BEXP_W * sizeof(Affine)), o_tab_a = take(n_tab * sizeof(Affine)),
+                 o_sc = take((n - 1) * scalar_stride + sizeof(Fr)), o_cf = take(sizeof(Fr)), o_x = take(n_max * sizeof(XYZZ)),
+                 o_pre = take(n_max * sizeof(Fq)), o_out = take(n * sizeof(Proj));
+    int rc = reserve(ctx, ctx->ws_tmp, off);
+    if (rc) return rc;
+    uint8_t *ws = (uint8_t *)ctx->ws_tmp.p;
+    Affine *d_base = (Affine *)(ws + o_base), *d_pw_a = (Affine *)(ws + o_pw_a), *d_tab = (Affine *)(ws + o_tab_a);
+    XYZZ *d_pw_x = (XYZZ *)(ws + o_pw_x), *d_x = (XYZZ *)(ws + o_x);
+    Fq *d_pre = (Fq *)(ws + o_pre);
+    rc = import_bases(ctx, base_point, sizeof(Proj), 1, d_base, ws + o_inf);
+    if (rc) return rc;
+    uint8_t base_inf = 0;
+    CK(cudaMemcpyAsync(&base_inf, ws + o_inf, 1, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(ws + o_sc, scalars, (n - 1) * scalar_stride + sizeof(Fr), cudaMemcpyHostToDevice, st));
+    if (coeff) CK(cudaMemcpyAsync(ws + o_cf, coeff, sizeof(Fr), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    if (base_inf) { // zero base: every power is zero
+        CK(cudaMemsetAsync(d_x, 0, n * sizeof(XYZZ), st)); // zz == 0 marks infinity
+    } else {
+        k_bexp_powers<<<1, 32, 0, st>>>(d_base, d_pw_x);
+        k_xyzz_to_affine<<<(BEXP_W + TOAFF_K * 128 - 1) / (TOAFF_K * 128), 128, 0, st>>>(d_pw_x, BEXP_W, d_pw_a, nullptr, d_pre);
+        k_bexp_table<<<(unsigned)((n_tab + 127) / 128), 128, 0, st>>>(d_pw_a, d_x);
+        k_xyzz_to_affine<<<(unsigned)((n_tab + TOAFF_K * 128 - 1) / (TOAFF_K * 128)), 128, 0, st>>>(d_x, (uint32_t)n_tab, d_tab,
+                                                                                                       nullptr, d_pre);
+        k_bexp_eval<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_tab, ws + o_sc, scalar_stride, (uint32_t)n,
+                                                                   coeff ? (const Fr *)(ws + o_cf) : nullptr, d_x);
+        ctx->launches += 5;
+    }
+    k_xyzz_to_affine<<<(unsigned)((n + TOAFF_K * 128 - 1) / (TOAFF_K * 128)), 128, 0, st>>>(d_x, (uint32_t)n, nullptr,
+                                                                                          (Proj *)(ws + o_out), d_pre);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_points, ws + o_out, n * sizeof(Proj), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
 int zecale_gpu_kernel_ms(zecale_gpu_ctx *ctx, int kernel_class, int reset, double *total_ms, uint64_t *count)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;

@@ -266,6 +266,27 @@ private:
     size_t log_m_;
 };
 
+// out[i] = (coeff * v[i]) * g on the device (zecale_gpu_batch_exp), special-form points.
+template<typename GroupT>
+inline std::vector<GroupT> batch_exp(int group, const GroupT &g, const std::vector<Fr> &v, size_t n, const Fr *coeff)
+{
+    static_assert(sizeof(GroupT) == 288 && sizeof(Fr) == 48, "libff in-memory layout");
+    if (n > v.size()) {
+        throw std::invalid_argument("batch_exp: num_entries exceeds the scalar vector");
+    }
+    std::vector<GroupT> out(n, GroupT::zero());
+    if (n == 0) {
+        return out;
+    }
+    GroupT base = g;
+    base.to_special();
+    check(
+        zecale_gpu_batch_exp(context(), group, &base, v.data(), sizeof(Fr), n, coeff, out.data()),
+        "zecale_gpu_batch_exp");
+    return out;
+}
+
+
 } // namespace zecale_gpu_hooks
 
 // ---------------------------------------------------------------- the specialisations
@@ -331,6 +352,30 @@ ZECALE_GPU_MSM_SPECIALISE(multi_exp_filter_one_zero, bw6_761_G1, ZECALE_GPU_G1)
 ZECALE_GPU_MSM_SPECIALISE(multi_exp_filter_one_zero, bw6_761_G2, ZECALE_GPU_G2)
 #undef ZECALE_GPU_MSM_SPECIALISE
 
+// Fixed-base exponentiations of the trusted setup (r1cs_gg_ppzksnark_generator, r1cs_gg_ppzksnark.tcc:
+// 349-398: A, H, L queries and gamma_ABC): batch_exp (multiexp.tcc:887-916) and batch_exp_with_coeff
+// (:918-947). The CPU window table is only read for the base point (table[0][1] = 1 * g); the device
+// builds its own table. Points come back in special form, which the generator's following
+// batch_to_special leaves unchanged. (kc_batch_exp for the B query keeps its CPU loop.)
+#define ZECALE_GPU_BATCH_EXP_SPECIALISE(GROUP, GID)                                                    \
+    template<>                                                                                         \
+    inline std::vector<GROUP> batch_exp<GROUP, bw6_761_Fr>(                                            \
+        const size_t, const size_t, const window_table<GROUP> &table, const std::vector<bw6_761_Fr> &v, \
+        size_t num_entries)                                                                            \
+    {                                                                                                  \
+        return zecale_gpu_hooks::batch_exp<GROUP>(GID, table[0][1], v, num_entries, nullptr);          \
+    }                                                                                                  \
+    template<>                                                                                         \
+    inline std::vector<GROUP> batch_exp_with_coeff<GROUP, bw6_761_Fr>(                                 \
+        const size_t, const size_t, const window_table<GROUP> &table, const bw6_761_Fr &coeff,         \
+        const std::vector<bw6_761_Fr> &v)                                                              \
+    {                                                                                                  \
+        return zecale_gpu_hooks::batch_exp<GROUP>(GID, table[0][1], v, v.size(), &coeff);              \
+    }
+ZECALE_GPU_BATCH_EXP_SPECIALISE(bw6_761_G1, ZECALE_GPU_G1)
+ZECALE_GPU_BATCH_EXP_SPECIALISE(bw6_761_G2, ZECALE_GPU_G2)
+#undef ZECALE_GPU_BATCH_EXP_SPECIALISE
+
 } // namespace libff
 
 namespace libsnark
@@ -376,6 +421,44 @@ inline knowledge_commitment<libff::bw6_761_G2, libff::bw6_761_G1> kc_multi_exp_w
     out.g = msm<G2>(ZECALE_GPU_G2, base, sizeof(KC), scalars, index, n);
     out.h = msm<G1>(ZECALE_GPU_G1, base + sizeof(G2), sizeof(KC), scalars, index, n);
     return out;
+}
+
+// The B query of the generator (r1cs_gg_ppzksnark.tcc:360-373): kc_batch_exp (kc_multiexp.tcc:148-239)
+// keeps the non-zero scalars only; their G2 and G1 powers are two device batch exponentiations.
+template<>
+inline knowledge_commitment_vector<libff::bw6_761_G2, libff::bw6_761_G1> kc_batch_exp<
+    libff::bw6_761_G2,
+    libff::bw6_761_G1,
+    libff::bw6_761_Fr>(
+    const size_t,
+    const size_t,
+    const size_t,
+    const libff::window_table<libff::bw6_761_G2> &T1_table,
+    const libff::window_table<libff::bw6_761_G1> &T2_table,
+    const libff::bw6_761_Fr &T1_coeff,
+    const libff::bw6_761_Fr &T2_coeff,
+    const std::vector<libff::bw6_761_Fr> &v,
+    const size_t,
+    bool)
+{
+    knowledge_commitment_vector<libff::bw6_761_G2, libff::bw6_761_G1> res;
+    res.domain_size_ = v.size();
+    std::vector<libff::bw6_761_Fr> nz;
+    for (size_t i = 0; i < v.size(); ++i) {
+        if (!v[i].is_zero()) {
+            nz.push_back(v[i]);
+            res.indices.push_back(i);
+        }
+    }
+    const std::vector<libff::bw6_761_G2> g2 = zecale_gpu_hooks::batch_exp<libff::bw6_761_G2>(
+        ZECALE_GPU_G2, T1_table[0][1], nz, nz.size(), &T1_coeff);
+    const std::vector<libff::bw6_761_G1> g1 = zecale_gpu_hooks::batch_exp<libff::bw6_761_G1>(
+        ZECALE_GPU_G1, T2_table[0][1], nz, nz.size(), &T2_coeff);
+    res.values.reserve(nz.size());
+    for (size_t i = 0; i < nz.size(); ++i) {
+        res.values.emplace_back(knowledge_commitment<libff::bw6_761_G2, libff::bw6_761_G1>(g2[i], g1[i]));
+    }
+    return res;
 }
 
 } // namespace libsnark
