@@ -52,16 +52,40 @@ def gen_mul(N, P, inv, a_op, b_op, r_op, square=False):
     O = [em.fresh() for _ in range(N)]
     top = em.fresh()
     x = None
+    if square:
+        # a^2 = sum_r a_r X_r 2^(32 r). The pair (i, j), j < i, is owed 2 a_i a_j:
+        #   j even: row j carries it doubled (column i), row i drops column j;
+        #   j odd : rows i and j each carry it once.
+        # So an even row is  [odd columns below r: a_c | a_r | (a_(r+1) << 1) | limbs of 2a above],
+        # an odd row is a with the even columns below r dropped, and only EVEN columns below the
+        # diagonal disappear: the even carry chain just starts later, the odd chain stays whole (the
+        # carry of the pending-word fold enters it), no carry has to ripple through empty columns.
+        # Saves N^2/4 wide MADs of the N^2 in the multiply half (144 of 576 for Fq).
+        D = {}
+        for j in range(2, N):
+            D[j] = em.fresh()
+            em.op("shf.l.wrap.b32 %s, %s, %s, 1;" % (D[j], a_op(j - 1), a_op(j)))
     for i in range(N):
         bi = b_op(i)
         m = em.fresh()
+        if square:
+            row = {c: a_op(c) for c in range(N) if not (c < i and c % 2 == 0)}
+            if i % 2 == 0:
+                if i + 1 < N:
+                    row[i + 1] = em.fresh()
+                    em.op("shl.b32 %s, %s, 1;" % (row[i + 1], a_op(i + 1)))
+                for j in range(i + 2, N):
+                    row[j] = D[j]
+            col = lambda j, row=row: row.get(j)
+        else:
+            col = a_op
         if i == 0:
             for j in range(0, N, 2):
-                em.op("mul.lo.u32 %s, %s, %s;" % (E[j], a_op(j), bi))
-                em.op("mul.hi.u32 %s, %s, %s;" % (E[j + 1], a_op(j), bi))
+                em.op("mul.lo.u32 %s, %s, %s;" % (E[j], col(j), bi))
+                em.op("mul.hi.u32 %s, %s, %s;" % (E[j + 1], col(j), bi))
             for j in range(1, N, 2):
-                em.op("mul.lo.u32 %s, %s, %s;" % (O[j - 1], a_op(j), bi))
-                em.op("mul.hi.u32 %s, %s, %s;" % (O[j], a_op(j), bi))
+                em.op("mul.lo.u32 %s, %s, %s;" % (O[j - 1], col(j), bi))
+                em.op("mul.hi.u32 %s, %s, %s;" % (O[j], col(j), bi))
             em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], imm(inv)))
             # even q chain
             for j in range(0, N, 2):
@@ -73,19 +97,30 @@ def gen_mul(N, P, inv, a_op, b_op, r_op, square=False):
             # fold pending word; its carry (weight 2^32) enters the odd chain
             em.op("add.cc.u32 %s, %s, %s;" % (E[0], E[0], x))
             for j in range(1, N, 2):
-                em.op("madc.lo.cc.u32 %s, %s, %s, %s;" % (O[j - 1], a_op(j), bi, O[j - 1]))
+                if col(j) is None:  # no product in this column (squaring): the carry of the fold just ripples
+                    em.op("addc.cc.u32 %s, %s, 0;" % (O[j - 1], O[j - 1]))
+                    em.op("addc.cc.u32 %s, %s, 0;" % (O[j], O[j]))
+                    continue
+                em.op("madc.lo.cc.u32 %s, %s, %s, %s;" % (O[j - 1], col(j), bi, O[j - 1]))
                 if j == N - 1:
                     nw = em.fresh()
-                    em.op("madc.hi.u32 %s, %s, %s, 0;" % (nw, a_op(j), bi))
+                    em.op("madc.hi.u32 %s, %s, %s, 0;" % (nw, col(j), bi))
                     O[j] = nw
                 else:
-                    em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (O[j], a_op(j), bi, O[j]))
+                    em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (O[j], col(j), bi, O[j]))
+            first = True
             for j in range(0, N, 2):
-                c0 = "mad.lo.cc.u32" if j == 0 else "madc.lo.cc.u32"
-                em.op("%s %s, %s, %s, %s;" % (c0, E[j], a_op(j), bi, E[j]))
-                em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], a_op(j), bi, E[j + 1]))
+                if col(j) is None:  # below the diagonal: nothing to add and no carry yet
+                    continue
+                c0 = "mad.lo.cc.u32" if first else "madc.lo.cc.u32"
+                first = False
+                em.op("%s %s, %s, %s, %s;" % (c0, E[j], col(j), bi, E[j]))
+                em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], col(j), bi, E[j + 1]))
             top = em.fresh()
-            em.op("addc.u32 %s, 0, 0;" % top)
+            if first:
+                em.op("add.u32 %s, 0, 0;" % top)
+            else:
+                em.op("addc.u32 %s, 0, 0;" % top)
             em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], imm(inv)))
             for j in range(0, N, 2):
                 c0 = "mad.lo.cc.u32" if j == 0 else "madc.lo.cc.u32"
@@ -185,8 +220,8 @@ def gen_field(tag, N, P, inv):
     s = []
     s.append(wrap("%s_mul_regs" % tag, N, gen_mul(N, P, inv, a_op, b_op, r_op), 2,
                   "r = a*b/R mod p  (Montgomery product, fully reduced). %d wide MADs." % (2 * N * N)))
-    s.append(wrap("%s_sqr_regs" % tag, N, gen_mul(N, P, inv, a_op, a_op, r_op), 1,
-                  "r = a*a/R mod p."))
+    s.append(wrap("%s_sqr_regs" % tag, N, gen_mul(N, P, inv, a_op, a_op, r_op, square=True), 1,
+                  "r = a*a/R mod p. %d wide MADs (even columns below the diagonal dropped)." % (2 * N * N - N * N // 4)))
     s.append(wrap("%s_add_regs" % tag, N, gen_add(N, P, a_op, b_op, r_op), 2, "r = a+b mod p."))
     s.append(wrap("%s_sub_regs" % tag, N, gen_sub(N, P, a_op, b_op, r_op), 2, "r = a-b mod p."))
     return "\n".join(s)

@@ -44,6 +44,11 @@ def run(lines, regs):
             regs[args[0]] = s & M32
             if sets_cc:
                 cc = 1 if s < 0 else 0
+        elif base == "shf":   # shf.l.wrap.b32 d, lo, hi, c
+            lo, hi, c = val(args[1]), val(args[2]), val(args[3]) & 31
+            regs[args[0]] = (((hi << 32) | lo) << c >> 32) & M32
+        elif base == "shl":
+            regs[args[0]] = (val(args[1]) << (val(args[2]) & 31)) & M32
         elif base == "and":
             regs[args[0]] = val(args[1]) & val(args[2])
         elif base == "setp":
