@@ -155,7 +155,7 @@ class ClockSampler:
 class Workload:
     """Synthetic batch-8 proving key image + witness, on one GPU."""
 
-    def __init__(self, device, seed=1, depth=2):
+    def __init__(self, device, seed=1, depth=3):
         import torch
         import zecale_b200 as z
         self.torch, self.z = torch, z
@@ -442,7 +442,7 @@ def run_b200(args, rank, world, local_rank):
                          "hbm_algorithmic_bytes_per_launch_avg": (madds + sum(v["tasks"] for v in shapes.values())) * 192 / 5,
                          "in_step": overlapped,
                          "madds_per_step": madds, "msm_shapes": shapes,
-                         "traffic": 2.54e9, "traffic_source": "ncu r01, A-query launch: dram read 1.31 GB + write 1.23 GB (profiles/r01_k_accumulate_raw.md)"},
+                         "traffic": 2.19e9, "traffic_source": "ncu r01, A-query launch: dram read 1.24 GB + write 0.95 GB (profiles/r01_k_accumulate_raw.md; the writes are the VM slot file leaving L1, the partial sums are 26 MB)"},
             "roofline_ntt": {"bound": "hbm", "kernel": "k_ntt_pass (Fr radix-2 NTT, 7 transforms per step)",
                              "achieved": ntt_bytes / ntt_s / 1e9 if ntt_s > 0 else None, "peak": peaks["hbm_gbs"],
                              "unit": "GB/s", "frac": (ntt_bytes / ntt_s / 1e9) / peaks["hbm_gbs"] if ntt_s > 0 else None,
@@ -547,7 +547,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--depth", type=int, default=2, help="proofs kept in flight per GPU (1 = strictly one at a time)")
+    ap.add_argument("--depth", type=int, default=3, help="proofs kept in flight per GPU (1 = strictly one at a time)")
     ap.add_argument("--skip-msm20", action="store_true")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     args = ap.parse_args()

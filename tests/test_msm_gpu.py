@@ -163,3 +163,31 @@ def test_async_lanes_match_blocking_calls(gpu, ref):
     finally:
         for p in pins.values():
             p.release()
+
+
+@pytest.mark.parametrize("group,log_n", [(1, 20), (2, 18)])
+def test_msm_full_size_properties(gpu, ref, group, log_n):
+    """BASELINE config 2 / the headline MSM size (2^20), where libff takes too long to be the checker:
+    size-independent properties instead — linearity in the scalars, msm(a) + msm(b) == msm(a + b), and
+    additivity over a split of the points (pinned prefix + un-pinned tail == whole), with the group
+    additions done by the reference on the CPU."""
+    n = 1 << log_n
+    bases = gpu.synth_bases(n, group, seed=2024 + group)
+    a, b = ref.fr_rng(5 << 32, n), ref.fr_rng(6 << 32, n)
+    c = ref.fr_op(0, a, b)
+
+    def add(p, q):
+        s = ref.group_op(0, p[None, :].copy(), q[None, :].copy(), group)
+        return ref.group_op(3, s, None, group)[0]
+
+    pinned = gpu.pin_bases(bases, group)
+    try:
+        pa, pb, pc = (gpu.msm_pinned(pinned, s) for s in (a, b, c))
+        assert np.array_equal(add(pa, pb), pc)
+        half = n // 2 + 12345
+        head = gpu.msm_pinned(pinned, a, n=half)
+    finally:
+        pinned.release()
+    f = gpu.msm_g1 if group == 1 else gpu.msm_g2
+    tail = f(np.ascontiguousarray(bases[half:]), np.ascontiguousarray(a[half:]))
+    assert np.array_equal(add(head, tail), pa)
