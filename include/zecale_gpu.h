@@ -103,6 +103,16 @@ int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_str
  * n * 192 B * ceil(378/c) bytes) and the doubling chain disappears from every later MSM. */
 int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
                             int expand, zecale_gpu_bases **handle);
+/* Same device image, made straight from the proving key's ON-DISK bytes: n points,
+ * `stride` bytes apart (multiple of 4), each X || Y with the coordinate as a plain big-endian integer
+ * (libzeth group_element_write_bytes, core/group_element_utils.tcc:93-100; zero = (0, 1)). For a
+ * query written by group_elements_write_bytes (groth16_snark.tcc:105-109) pass file + 8 and stride
+ * 192; for the sparse B query (knowledge_commitment_vector_write_bytes, serialization/
+ * stream_utils.tcc:111-122: entries of index(8) | g(192) | h(192) after a 16-byte header) pass
+ * file + 24 (G2 part) or file + 216 (G1 part) with stride 392. Byte order and the conversion to
+ * Montgomery form (the host's Fp_model(bigint), fp.tcc:246-252) are done on the device. */
+int zecale_gpu_pin_bases_bytes(zecale_gpu_ctx *ctx, const void *bytes, size_t stride, size_t n, int group, int expand,
+                               zecale_gpu_bases **handle);
 int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *handle);
 /* MSM over the first n pinned bases. */
 int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *handle, const void *scalars,

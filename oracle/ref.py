@@ -91,6 +91,25 @@ class Ref:
                               _p(coeff) if coeff is not None else None, _p(out))
         return out
 
+    def points_write_bytes(self, pts, group=1):
+        """libzeth::group_elements_write_bytes of a vector of points (the on-disk form of a pk query)."""
+        cap = 8 + 192 * pts.shape[0]
+        out = np.zeros(cap, dtype=np.uint8)
+        self.L.zref_points_write_bytes.restype = ctypes.c_size_t
+        n = self.L.zref_points_write_bytes(int(group), _p(pts), _sz(pts.shape[0]), _p(out), _sz(cap))
+        assert n == cap, n
+        return out
+
+    def kc_write_bytes(self, values, indices, domain):
+        """libzeth::knowledge_commitment_vector_write_bytes of a sparse G2/G1 query (values: n x 72 u64)."""
+        cap = 16 + 392 * values.shape[0]
+        out = np.zeros(cap, dtype=np.uint8)
+        self.L.zref_kc_write_bytes.restype = ctypes.c_size_t
+        idx = np.ascontiguousarray(indices, dtype=np.uint64)
+        n = self.L.zref_kc_write_bytes(_p(values), _p(idx), _sz(values.shape[0]), _sz(domain), _p(out), _sz(cap))
+        assert n == cap, n
+        return out
+
     def group_op(self, op, a, b=None, group=1):
         out = np.zeros_like(a)
         (self.L.zref_g1_op if group == 1 else self.L.zref_g2_op)(op, _p(a), _p(b if b is not None else a), _p(out), _sz(a.shape[0]))

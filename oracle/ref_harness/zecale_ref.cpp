@@ -347,6 +347,43 @@ extern "C" void zref_batch_exp(int group, const void *base, const void *s, size_
         ref_batch_exp<G1>((const G1 *)base, (const Fr *)s, n, (const Fr *)coeff, (G1 *)out);
 }
 
+// The proving key's on-disk codec as libzeth writes it (groth16_snark.tcc:93-110): a query of n points
+// through group_elements_write_bytes, a sparse G2/G1 query through knowledge_commitment_vector_write_bytes.
+// Returns the number of bytes written (0 if `cap` is too small).
+template<typename G> static size_t points_write_bytes(const G *pts, size_t n, void *out, size_t cap)
+{
+    std::vector<G> v(pts, pts + n);
+    std::ostringstream ss;
+    libzeth::group_elements_write_bytes(v, ss);
+    const std::string b = ss.str();
+    if (b.size() > cap)
+        return 0;
+    std::memcpy(out, b.data(), b.size());
+    return b.size();
+}
+extern "C" size_t zref_points_write_bytes(int group, const void *pts, size_t n, void *out, size_t cap)
+{
+    return group == 2 ? points_write_bytes<G2>((const G2 *)pts, n, out, cap) : points_write_bytes<G1>((const G1 *)pts, n, out, cap);
+}
+extern "C" size_t zref_kc_write_bytes(const void *values, const size_t *indices, size_t n, size_t domain, void *out, size_t cap)
+{
+    typedef libsnark::knowledge_commitment<G2, G1> kc_t;
+    libsnark::knowledge_commitment_vector<G2, G1> v;
+    v.domain_size_ = domain;
+    const kc_t *src = (const kc_t *)values;
+    for (size_t i = 0; i < n; ++i) {
+        v.values.push_back(src[i]);
+        v.indices.push_back(indices[i]);
+    }
+    std::ostringstream ss;
+    libzeth::knowledge_commitment_vector_write_bytes(v, ss);
+    const std::string b = ss.str();
+    if (b.size() > cap)
+        return 0;
+    std::memcpy(out, b.data(), b.size());
+    return b.size();
+}
+
 // op: 0 operator+, 1 mixed_add (b special), 2 dbl(a), 3 to_special(a), 4 neg(a),
 //     5 add(), 6 scalar-mul by Fr in b's first 48 bytes (b stride = 288)
 template<typename G> static void group_op(int op, const G *a, const G *b, G *o, size_t n)

@@ -64,6 +64,7 @@ EXPORTS = {
     "zecale_gpu_qap_h_async": (_i, [_vp, _i, _vp, _vp, _vp, _u, _vp, _vp]),
     "zecale_gpu_sync": (_i, [_vp]),
     "zecale_gpu_synth_bases": (_i, [_vp, _i, ctypes.c_uint64, _sz, _vp]),
+    "zecale_gpu_pin_bases_bytes": (_i, [_vp, _vp, _sz, _sz, _i, _i, ctypes.POINTER(_vp)]),
     "zecale_gpu_batch_exp": (_i, [_vp, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
     "zecale_gpu_kernel_ms": (_i, [_vp, _i, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]),
     "zecale_gpu_launch_count": (ctypes.c_uint64, [_vp]),
@@ -279,6 +280,13 @@ class Context:
         out = np.zeros((n, 36), dtype=np.uint64)
         self._ck(_lib.zecale_gpu_synth_bases(self._h, group, seed, n, _ptr(out)))
         return out
+
+    def pin_bases_bytes(self, buf, offset, stride, n, group=G1, expand=True):
+        """Pin n points from key-file bytes (numpy uint8 buffer): X || Y big-endian plain, `stride` apart."""
+        h = ctypes.c_void_p()
+        self._ck(_lib.zecale_gpu_pin_bases_bytes(self._h, ctypes.c_void_p(buf.ctypes.data + offset), stride, n, group,
+                                                 1 if expand else 0, ctypes.byref(h)))
+        return PinnedBases(self, h, n, group)
 
     def batch_exp(self, base, scalars, group=G1, coeff=None):
         """out[i] = (coeff * scalars[i]) * base (libff::batch_exp + batch_to_special)."""

@@ -152,6 +152,44 @@ __global__ void k_import_special(const uint8_t *raw, size_t stride, uint32_t n, 
     for (int k = 0; k < 12; k++) dst[k] = src[k];
 }
 
+// Key-file points -> device affine image + flags. libzeth writes a group element as
+// X || Y, each coordinate the PLAIN integer in big-endian bytes (group_element_write_bytes,
+// libzeth/core/group_element_utils.tcc:93-100 -> libff field_write<encoding_binary, form_plain>,
+// field_serialization.tcc:197-207); zero is (0, 1) (group_element_read_bytes :102-113). `raw` is
+// 4-byte aligned, points `stride` bytes apart. Byte-reverse, then one Montgomery product with R^2 per
+// coordinate — what Fp_model(bigint) does on the host (fp.tcc:246-252).
+__global__ void __launch_bounds__(128) k_import_bytes(const uint8_t *raw, size_t stride, uint32_t n, Affine *out, uint8_t *is_inf)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(raw + (size_t)i * stride);
+    uint32_t x[24], y[24], r2[24], mx[24], my[24];
+    uint32_t xor_ = 0, yne = 0;
+#pragma unroll
+    for (int k = 0; k < 24; k++) {
+        x[k] = __byte_perm(src[23 - k], 0, 0x0123);
+        y[k] = __byte_perm(src[47 - k], 0, 0x0123);
+        r2[k] = FQ_R2[k];
+        xor_ |= x[k];
+        yne |= y[k] ^ (k == 0 ? 1u : 0u);
+    }
+    uint4 *dst = reinterpret_cast<uint4 *>(out + i);
+    if (xor_ == 0 && yne == 0) {
+#pragma unroll
+        for (int k = 0; k < 12; k++) dst[k] = make_uint4(0, 0, 0, 0);
+        is_inf[i] = 1;
+        return;
+    }
+    is_inf[i] = 0;
+    fq_mul_regs(mx, x, r2);
+    fq_mul_regs(my, y, r2);
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        dst[k] = make_uint4(mx[4 * k], mx[4 * k + 1], mx[4 * k + 2], mx[4 * k + 3]);
+        dst[6 + k] = make_uint4(my[4 * k], my[4 * k + 1], my[4 * k + 2], my[4 * k + 3]);
+    }
+}
+
 // ------------------------------------------------------------------ synthetic bases
 // out[i] = k_i * generator in libff special form, k_i = 32-bit hash of (seed, i), never 0.
 // Used by bench.py / tests to make distinct valid curve points without a CPU library.

@@ -277,6 +277,20 @@ int import_bases(zecale_gpu_ctx *ctx, const void *bases, size_t stride, size_t n
     return 0;
 }
 
+int import_bases_bytes(zecale_gpu_ctx *ctx, const void *bytes, size_t stride, size_t n, Affine *d_out, uint8_t *d_inf)
+{
+    // the host buffer may sit at any address of a key file: stage it from a 4-byte aligned copy point
+    size_t raw = (n - 1) * stride + sizeof(Affine);
+    int rc = reserve(ctx, ctx->ws_in, raw);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(ctx->ws_in.p, bytes, raw, cudaMemcpyHostToDevice, ctx->cur->stream));
+    k_import_bytes<<<(unsigned)((n + 127) / 128), 128, 0, ctx->cur->stream>>>((const uint8_t *)ctx->ws_in.p, stride, (uint32_t)n,
+                                                                          d_out, d_inf);
+    ctx->launches++;
+    CK(cudaStreamSynchronize(ctx->cur->stream));
+    return 0;
+}
+
 // d_bases: affine image on device; scalars: device pointer. Result -> host out (288 B).
 int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf, uint32_t c, uint32_t V,
                uint32_t copy_stride, const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, size_t n,
@@ -817,14 +831,15 @@ static uint32_t pinned_c(size_t n)
     return c;
 }
 
-int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group, int expand,
-                            zecale_gpu_bases **handle)
+// format 0: libff in-memory special-form points (288 B); 1: libzeth key-file bytes (X || Y, 192 B big-endian plain)
+static int pin_bases_impl(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group, int expand,
+                          zecale_gpu_bases **handle, int format)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
     ctx->cur = &ctx->lanes[0];
-    if (!bases || !handle || !n || base_stride < sizeof(Proj) || n >= (1ull << 26) ||
-        (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
+    if (!bases || !handle || !n || base_stride < (format ? sizeof(Affine) : sizeof(Proj)) || (format && (base_stride & 3)) ||
+        n >= (1ull << 26) || (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_pin_bases: bad argument");
     CK(cudaSetDevice(ctx->device));
     zecale_gpu_bases *h = new zecale_gpu_bases();
@@ -856,7 +871,8 @@ int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_
         delete h;
         return fail(ctx, ZECALE_GPU_E_NOMEM, "pin_bases: %s", cudaGetErrorString(e));
     }
-    int rc = import_bases(ctx, bases, base_stride, n, h->d, h->is_inf);
+    int rc = format ? import_bases_bytes(ctx, bases, base_stride, n, h->d, h->is_inf)
+                    : import_bases(ctx, bases, base_stride, n, h->d, h->is_inf);
     if (rc == 0 && G > 1) {
         rc = reserve(ctx, ctx->ws_tmp, n * (sizeof(XYZZ) + sizeof(Fq)));
         if (rc == 0) {
@@ -880,6 +896,18 @@ int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_
     }
     *handle = h;
     return 0;
+}
+
+int zecale_gpu_pin_bases_ex(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group, int expand,
+                            zecale_gpu_bases **handle)
+{
+    return pin_bases_impl(ctx, bases, base_stride, n, group, expand, handle, 0);
+}
+
+int zecale_gpu_pin_bases_bytes(zecale_gpu_ctx *ctx, const void *bytes, size_t stride, size_t n, int group, int expand,
+                               zecale_gpu_bases **handle)
+{
+    return pin_bases_impl(ctx, bytes, stride, n, group, expand, handle, 1);
 }
 
 int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group,
