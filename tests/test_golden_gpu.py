@@ -72,3 +72,32 @@ def test_groth16_small(gpu):
            gpu.msm_g1(g["L_query"], np.ascontiguousarray(w[ni + 1:]))]
     for k in range(5):
         assert np.array_equal(got[k], g["msm5"][k]), k
+
+
+@pytest.mark.parametrize("grp", [1, 2])
+def test_batch_exp(gpu, grp):
+    """SURVEY 8(f3): libff::batch_exp(_with_coeff) + batch_to_special, recorded by make_golden_setup.py."""
+    g = G.load("setup_batch_exp")
+    base, sc = g["base_g%d" % grp], g["scalars_g%d" % grp]
+    assert np.array_equal(gpu.batch_exp(base, sc, grp), g["exp_g%d" % grp])
+    assert np.array_equal(gpu.batch_exp(base, sc, grp, coeff=g["coeff_g%d" % grp]), g["exp_coeff_g%d" % grp])
+
+
+def test_keyfile_bytes(gpu):
+    """SURVEY 8(f4): key-file bytes written by libzeth's codec -> device image; MSMs equal libff::multi_exp."""
+    g = G.load("keyfile_bytes")
+    for grp in (1, 2):
+        raw, sc = np.ascontiguousarray(g["bytes_g%d" % grp]), g["scalars_g%d" % grp]
+        pin = gpu.pin_bases_bytes(raw, 8, 192, sc.shape[0], grp)
+        try:
+            assert np.array_equal(gpu.msm_pinned(pin, sc), g["msm_g%d" % grp])
+        finally:
+            pin.release()
+    raw = np.ascontiguousarray(g["kc_bytes"])
+    sc = np.ascontiguousarray(g["kc_witness"][g["kc_indices"].astype(np.int64)])
+    for grp, off in ((2, 24), (1, 216)):
+        pin = gpu.pin_bases_bytes(raw, off, 392, sc.shape[0], grp)
+        try:
+            assert np.array_equal(gpu.msm_pinned(pin, sc), g["kc_msm_g%d" % grp])
+        finally:
+            pin.release()

@@ -137,3 +137,53 @@ def test_ntt_vs_ref_random(port, ref):
     for fl in range(4):
         exp, _ = ref.ntt(a, fl, g15 if fl & 2 else None)
         assert np.array_equal(port.ntt(a, fl, g15 if fl & 2 else None), exp), fl
+
+
+@pytest.mark.parametrize("grp", [1, 2])
+def test_batch_exp_golden(port, grp):
+    """SURVEY 8(f3) on the CPU: (coeff * s_i) * g restated as one-point sums of the C oracle, against
+    libff::batch_exp(_with_coeff) + batch_to_special recorded by tests/golden/make_golden_setup.py."""
+    g = G.load("setup_batch_exp")
+    base, sc, coeff = g["base_g%d" % grp][None, :], g["scalars_g%d" % grp], g["coeff_g%d" % grp]
+    scaled = port.fr_op(2, sc, np.repeat(coeff, sc.shape[0], axis=0))      # Montgomery product in Fr
+    for i in range(sc.shape[0]):
+        assert np.array_equal(port.msm(base, sc[i:i + 1]), g["exp_g%d" % grp][i]), i
+        assert np.array_equal(port.msm(base, scaled[i:i + 1]), g["exp_coeff_g%d" % grp][i]), i
+
+
+def _decode_points(port, raw, offset, stride, n, one):
+    """Key-file points (X || Y, plain big-endian, libzeth group_element_write_bytes) -> libff special form:
+    the CPU restatement of k_import_bytes (byte reversal, to-Montgomery, (0, 1) = zero)."""
+    pts = np.zeros((n, 36), dtype=np.uint64)
+    for i in range(n):
+        rec = raw[offset + i * stride: offset + i * stride + 192]
+        x = np.frombuffer(rec[:96][::-1].tobytes(), dtype=np.uint64)       # little-endian limbs of the plain integer
+        y = np.frombuffer(rec[96:][::-1].tobytes(), dtype=np.uint64)
+        if not x.any() and y[0] == 1 and not y[1:].any():
+            pts[i, 12:24] = one
+            continue
+        pts[i, :12] = port.fq_op(7, x[None, :].copy())[0]
+        pts[i, 12:24] = port.fq_op(7, y[None, :].copy())[0]
+        pts[i, 24:36] = one
+    return pts
+
+
+def test_keyfile_bytes_golden(port):
+    """SURVEY 8(f4) on the CPU: bytes written by libzeth's codec decode to the in-memory points, and the
+    oracle's MSM over the decoded points equals libff::multi_exp over the originals."""
+    g = G.load("keyfile_bytes")
+    one = g["bases_g1"][0, 24:36]
+    for grp in (1, 2):
+        raw = g["bytes_g%d" % grp]
+        n = int(raw[:8].view(np.uint64)[0])
+        pts = _decode_points(port, raw, 8, 192, n, one)
+        assert np.array_equal(pts, g["bases_g%d" % grp])
+        assert np.array_equal(port.msm(pts, g["scalars_g%d" % grp]), g["msm_g%d" % grp])
+    raw = g["kc_bytes"]
+    nnz = int(raw[8:16].view(np.uint64)[0])
+    idx = np.array([int(raw[16 + 392 * i: 24 + 392 * i].view(np.uint64)[0]) for i in range(nnz)], dtype=np.uint64)
+    assert np.array_equal(idx, g["kc_indices"])
+    sc = np.ascontiguousarray(g["kc_witness"][idx.astype(np.int64)])
+    for grp, off in ((2, 24), (1, 216)):
+        pts = _decode_points(port, raw, off, 392, nnz, one)
+        assert np.array_equal(port.msm(pts, sc), g["kc_msm_g%d" % grp])

@@ -11,9 +11,11 @@
 // with invariants a = y u, b = y v (mod q). 52 rounds x 30 steps >= 1521; once a reaches 0,
 // b = gcd = 1 and v = y^-1 stay fixed. (T. Pornin, "Optimized binary GCD for modular
 // inversion", 2020: the approximation never costs an extra step.)
-// Cost: 52 x 240 wide multiply-adds (~11 Montgomery products) on the multiply pipe plus ~40k
-// ALU instructions, and no data-dependent branch: a warp's 32 lanes invert 32 different
-// values in lock-step. The shift/subtract version is ~1500 divergent 4-way iterations.
+// Cost: 52 x 240 multiply-adds of a 32-bit limb by a signed 31-bit factor plus the branch-free inner
+// loops: ~140 k SASS instructions per warp as compiled (ncu), i.e. ~100 Montgomery products' worth
+// of issue slots but mostly on the ALU pipe, and no data-dependent branch: a warp's 32 lanes invert 32
+// different values in lock-step (2^19 inversions: 3.4 ms against 26 ms for the shift/subtract
+// version, whose ~1500 iterations diverge four ways).
 //
 // The code is plain integer C++ so the same text compiles for the host (tests/test_inv_cpu.py
 // checks it against Python's pow(y, -1, q)).
