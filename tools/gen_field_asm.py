@@ -252,6 +252,8 @@ def gen_consts():
     for tag, P, N, K in (("FQ", C.Q, C.FQ_LIMBS32, C.FQ), ("FR", C.R, C.FR_LIMBS32, C.FR)):
         o += carr("%s_P" % tag, C.limbs32(P, N))
         o += carr("%s_ONE" % tag, C.limbs32(K["one"], N))
+        # host-side copy (the runtime fills zero points / unit coset factors without a device round trip)
+        o += "static const uint32_t %s_ONE_HOST[%d] = {%s};\n" % (tag, N, ", ".join("0x%08xu" % v for v in C.limbs32(K["one"], N)))
         o += carr("%s_R2" % tag, C.limbs32(K["r2"], N))
         o += carr("%s_PM2" % tag, C.limbs32(P - 2, N))
         o += "static constexpr uint32_t %s_INV32 = 0x%08xu;\n" % (tag, K["inv32"])

@@ -18,11 +18,10 @@
 //   * buckets are cut into tasks of <= S entries, tasks are sorted by length so the 32
 //     lanes of a warp run equally long chains of mixed additions (k_accumulate, one
 //     thread per task, XYZZ accumulator in the Fq VM);
-//   * sum_b (b+1) B_b is a log-depth blocked running sum: each level folds segments of
-//     L buckets with the running-sum trick (multiexp_accumulate_buckets, :90-125) and
-//     carries the per-level weighted sums upwards (k_reduce_level), so the serial chain
-//     is ~2L*log_L(NB) additions instead of 2*NB;
-//   * k_final: Horner over levels and bucket sets, normalise to libff special form.
+//   * sum_b (b+1) B_b (multiexp_accumulate_buckets, :90-125) is a binary tree over the bucket
+//     index with one bit tree per index bit riding along (k_tail_level: 2 NB additions, depth
+//     c-1), then parallel doublings, a pair-tree sum and the normalisation to libff special
+//     form; every launch of the tail serves all MSMs of a proof (TailBatch).
 //
 // No 0/1 filter is needed: a zero scalar has all-zero digits, a one is an ordinary
 // bucket entry, and base points at infinity never produce entries.
@@ -36,10 +35,8 @@
 namespace zecale {
 
 static constexpr int FR_SCALAR_BITS = 377;
-static constexpr int MSM_MAX_LEVELS = 24;
 static constexpr uint32_t MSM_MAX_TASKS_PER_BUCKET = 256;
 static constexpr uint64_t MSM_TARGET_TASKS = 3ull * 148 * 3 * 128;
-static constexpr uint32_t MSM_INLINE_FOLD = 4; // buckets cut into <= 4 tasks are folded inside k_reduce_level
 
 struct MsmPlan {
     uint32_t n;            // (base, scalar) pairs
@@ -50,8 +47,6 @@ struct MsmPlan {
     uint32_t NB;           // buckets per set = 2^(c-1)
     uint32_t S;            // max entries per accumulate task
     uint32_t copy_stride;  // points per base copy
-    uint32_t n_levels;     // reduction levels
-    uint32_t lbits[MSM_MAX_LEVELS]; // log2 segment length per level
     uint64_t n_buckets;    // V * NB
     uint64_t max_tasks;
     uint32_t acc_mode;     // MSM_ACC_XYZZ | MSM_ACC_TREE
@@ -100,8 +95,8 @@ inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_s
     // products, folding two partial sums 14 — and at least what keeps the task count near 3 waves
     // of the 148 SM x 3 CTA x 128 thread accumulate grid for very large n. SM load balance comes
     // from the length-sorted task order and from the sibling MSMs of a proof running concurrently.
-    // Buckets cut into <= MSM_INLINE_FOLD tasks are folded on the fly by the first running-sum
-    // level; genuinely heavy ones (many equal small scalars) go through k_fold_heavy.
+    // Buckets that do get cut (a Poisson tail, many equal small scalars, or the few buckets a short
+    // top window feeds) are folded by k_tail_fold, one warp per bucket.
     uint64_t avg = ((uint64_t)n * p.W + (uint64_t)p.V * p.NB - 1) / ((uint64_t)p.V * p.NB);
     uint64_t S = ((uint64_t)n * p.W + MSM_TARGET_TASKS - 1) / MSM_TARGET_TASKS;
     uint64_t sq = 0;
@@ -113,13 +108,6 @@ inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_s
     while ((1ull << p.tree_rounds) < (uint64_t)n * p.G) p.tree_rounds++;
     p.n_buckets = (uint64_t)p.V * p.NB;
     p.max_tasks = ((uint64_t)n * p.W) / p.S + p.n_buckets + 1;
-    uint32_t rem = c - 1;
-    p.n_levels = 0;
-    while (rem) {
-        uint32_t l = rem >= 2 ? 2 : rem;
-        p.lbits[p.n_levels++] = l;
-        rem -= l;
-    }
     return p;
 }
 
@@ -528,7 +516,7 @@ __global__ void k_task_fill(MsmPlan p, const uint32_t *counts, const uint32_t *o
     size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= p.n_buckets) return;
     uint32_t t0 = task_off[b], nt = task_off[b + 1] - t0;
-    if (nt > MSM_INLINE_FOLD) heavy_list[atomicAdd(heavy_count, 1u)] = (uint32_t)b; // folded by k_fold_heavy
+    if (nt > 1) heavy_list[atomicAdd(heavy_count, 1u)] = (uint32_t)b; // folded by k_tail_fold
     uint64_t cnt = counts[b];
     uint32_t off = offsets[b];
     for (uint32_t k = 0; k < nt; k++) {
@@ -842,23 +830,75 @@ __global__ void k_tree_finish(uint32_t n_buckets, const uint32_t *off, const uin
     vs_get(&dst->zzz, S, VS_T0);
 }
 
-// Buckets that were cut into several tasks ("heavy" buckets, listed by k_task_fill; rare by the
-// choice of S): one warp per heavy bucket folds the bucket's partials into the first one by a
-// pairwise tree, level j: partial[i] += partial[i + 2^j] for i a multiple of 2^(j+1); the pairs
-// of a level are spread over the 32 lanes. One launch, log2(MSM_MAX_TASKS_PER_BUCKET) levels deep.
-static constexpr uint32_t MSM_FOLD_BLOCKS = 148 * 8;
-__global__ void __launch_bounds__(32, 1)
-k_fold_heavy(const uint32_t *heavy_list, const uint32_t *heavy_count, const uint32_t *task_off, XYZZ *partial)
+// ------------------------------------------------------------------ tail: sum_b (b+1) B_b, batched over MSMs
+// The second half of an MSM turns the bucket sums B_b (b < NB = 2^(c-1), per bucket set v) into
+//     R_v = sum_b (b + 1) B_b = Root_v + sum_j 2^j S_{j,v},   S_j = sum of the buckets whose index has bit j set,
+// and the result sum_v 2^(c v) R_v into libff special form. libff does this with a serial running sum per
+// window (multiexp_accumulate_buckets, multiexp.tcc:90-125: 2 NB dependent additions) and c doublings
+// between windows (:614-616). A dependent point addition costs ~50 us on one warp (14 products of ~3.5 us
+// dependent-issue latency each), so the tail is latency-bound and is organised for DEPTH, one point
+// operation per thread per launch, every launch serving all MSMs of a proof (TailBatch):
+//   k_tail_fold   : buckets that were cut into several accumulate tasks are folded into their first partial
+//                   (one warp per bucket, pair tree; nothing to do for ordinary buckets)
+//   k_tail_level  : launch k = 1 .. c-1: X_k[s] = X_{k-1}[2s] + X_{k-1}[2s+1] (X_0 = buckets), and, riding
+//                   along, the bit trees: Y_j starts as the odd items of X_j and is halved by every later
+//                   launch, so that all S_j are complete after launch c-2 and the root after launch c-1.
+//                   Work 2 NB additions (the running sum's), depth c-1.
+//   k_tail_scale  : D_{v,j} = 2^(j + c v) S_{j,v} (j + c v doublings, in parallel), D_{v,c-1} = 2^(c v) Root_v
+//   k_tail_sum    : pair-tree sum of all D (one CTA per MSM)
+//   k_tail_norm   : to_special (one inversion per MSM, all MSMs of the batch side by side)
+// Critical path for a pinned image (V = 1): c-1 additions + c-2 doublings + log2(c) additions + one
+// inversion, about 2 ms, against ~75 dependent additions + the inversion (4.6 ms) for the radix-4 blocked
+// running sum with a one-thread Horner that it replaces.
+static constexpr uint32_t TAIL_MAX_JOBS = 8;
+static constexpr uint32_t TAIL_FOLD_BLOCKS = 148 * 2; // warps per MSM folding cut buckets
+
+struct TailJob {
+    const uint32_t *task_off;    // [V*NB + 1]: bucket b's partial sums are partial[task_off[b] .. task_off[b+1])
+    const uint32_t *heavy_list;  // buckets cut into > 1 task ...
+    const uint32_t *heavy_count; // ... and how many
+    XYZZ *partial;
+    XYZZ *lvl[2];                // level-k buffer = lvl[k & 1]: [X_k | Y_0 | ... | Y_{k-1}]
+    XYZZ *fin;                   // V * c scaled terms
+    Proj *result;
+    uint32_t cm1;                // c - 1 = log2(NB)
+    uint32_t V;
+};
+
+struct TailBatch {
+    uint32_t n_jobs;
+    uint32_t first_block[TAIL_MAX_JOBS + 1]; // CTA range of each job in the current launch
+    TailJob job[TAIL_MAX_JOBS];
+};
+
+__device__ __forceinline__ uint32_t tail_find_job(const TailBatch &tb, uint32_t blk)
 {
-    const uint32_t n_heavy = *heavy_count;
-    for (uint32_t h = blockIdx.x; h < n_heavy; h += gridDim.x) {
-        const uint32_t b = heavy_list[h];
-        const uint32_t t0 = task_off[b], nt = task_off[b + 1] - t0;
+    uint32_t j = 0;
+    while (j + 1 < tb.n_jobs && blk >= tb.first_block[j + 1]) j++;
+    return j;
+}
+
+// threads of launch k for one job
+__host__ __device__ __forceinline__ uint32_t tail_level_threads(uint32_t cm1, uint32_t V, uint32_t k)
+{
+    if (k > cm1) return 0;
+    const uint32_t nk = (1u << cm1) >> k;
+    return V * nk + (k < cm1 ? k * V * (nk >> 1) : 0);
+}
+
+__global__ void __launch_bounds__(32, 1) k_tail_fold(TailBatch tb)
+{
+    const uint32_t j = tail_find_job(tb, blockIdx.x);
+    const TailJob &J = tb.job[j];
+    const uint32_t n_heavy = *J.heavy_count, nblk = tb.first_block[j + 1] - tb.first_block[j];
+    for (uint32_t h = blockIdx.x - tb.first_block[j]; h < n_heavy; h += nblk) {
+        const uint32_t b = J.heavy_list[h];
+        const uint32_t t0 = J.task_off[b], nt = J.task_off[b + 1] - t0;
         for (uint32_t step = 1; step < nt; step <<= 1) {
-            // pairs (i, i + step), i = 2*step*k, k < ceil((nt - step) / (2 step))
+            // pairs (i, i + step), i = 2*step*q, q < ceil((nt - step) / (2 step))
             const uint32_t n_pairs = (nt - step + 2 * step - 1) / (2 * step);
-            for (uint32_t k = threadIdx.x; k < n_pairs; k += 32) {
-                XYZZ *dst = partial + t0 + 2 * step * k;
+            for (uint32_t q = threadIdx.x; q < n_pairs; q += 32) {
+                XYZZ *dst = J.partial + t0 + 2 * step * q;
                 FqSlots S;
                 vs_load_acc(S, dst);
                 vs_load_q(S, dst + step);
@@ -873,208 +913,131 @@ k_fold_heavy(const uint32_t *heavy_list, const uint32_t *heavy_count, const uint
     }
 }
 
-// ------------------------------------------------------------------ reduce
-// One level of the blocked running sum. Arrays are "item arrays" of XYZZ:
-//   A      : n_in items (per bucket set: n_in_per_set, segments never straddle sets)
-//   C[a]   : k carried arrays of n_in items, stored back to back
-// Thread (a, s), s < n_out = n_in >> l:
-//   a == 0 : running sum over A[s*L .. s*L+L): outA[s] = sum_j A_j, outC[0][s] = sum_j (j + w0) A_j
-//            (w0 = 1 at level 0, where bucket b has weight b+1; 0 above)
-//   a >= 1 : outC[a][s] = plain sum of C[a-1][s*L .. s*L+L)
-// At level 0 the items are bucket values looked up through task_off (empty bucket = infinity).
-struct ReduceLevel {
-    uint32_t l;        // log2 L
-    uint32_t k;        // carried arrays on input
-    uint32_t n_in;     // items per array on input (all sets)
-    uint32_t level0;   // 1: A is addressed through task_off into partial
-};
-
-__global__ void __launch_bounds__(128, 2)
-k_reduce_level(ReduceLevel r, const uint32_t *task_off, const XYZZ *inA, const XYZZ *inC, XYZZ *outA, XYZZ *outC)
+__global__ void __launch_bounds__(128, 3) k_tail_level(TailBatch tb, uint32_t k)
 {
-    const uint32_t n_out = r.n_in >> r.l;
-    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= (r.k + 1) * n_out) return;
-    const uint32_t a = tid / n_out, s = tid - a * n_out;
-    const uint32_t L = 1u << r.l;
-    FqSlots S;
-    if (a == 0) {
-        // running sum, top item first: acc = run, R = weighted sum
-        int j = (int)L - 1;
-        uint32_t phase = 0; // 0: acc += item j ; 1: R += acc
-        vs_acc_inf(S);
-        vs_zero(S, VS_RX);
-        vs_one(S, VS_RY);
-        vs_zero(S, VS_RZZ);
-        vs_zero(S, VS_RZZZ);
-        // level 0: item = bucket; a bucket cut into nsub <= MSM_INLINE_FOLD tasks is summed here
-        // (partials t0 .. t0+nsub-1), a heavier one was already folded into partial[t0]
-        uint32_t sub = 0, nsub = 1, sub_t0 = 0;
-        auto load_item = [&](FqSlots &S_, uint32_t idx) {
-            sub = 0;
-            nsub = 1;
-            if (r.level0) {
-                uint32_t t0 = task_off[idx], t1 = task_off[idx + 1];
-                if (t0 == t1) {
-                    vs_zero(S_, VS_QZZ); // infinity: the add program only tests QZZ
-                    return;
-                }
-                sub_t0 = t0;
-                if (t1 - t0 <= MSM_INLINE_FOLD) nsub = t1 - t0;
-                vs_load_q(S_, inA + t0);
-            } else {
-                vs_load_q(S_, inA + idx);
-            }
-        };
-        load_item(S, s * L + j);
-        fqvm_run_noinv(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
-            if (phase == 0) {
-                if (++sub < nsub) { // next partial of the same bucket
-                    vs_load_q(S_, inA + sub_t0 + sub);
-                    pc = VPC_ADD;
-                    return true;
-                }
-                // acc now holds run_j
-                if (j > 0 || r.level0) {
-                    phase = 1;
-                    pc = VPC_ADD_R;
-                    return true;
-                }
-            }
-            // after R += acc (or skipped): next item
-            phase = 0;
-            if (--j < 0) {
-                vs_store_acc(outA + s, S_);
-                XYZZ *o = outC + s;
-                vs_get(&o->x, S_, VS_RX);
-                vs_get(&o->y, S_, VS_RY);
-                vs_get(&o->zz, S_, VS_RZZ);
-                vs_get(&o->zzz, S_, VS_RZZZ);
-                return false;
-            }
-            load_item(S_, s * L + j);
-            pc = VPC_ADD;
-            return true;
-        });
+    const uint32_t j = tail_find_job(tb, blockIdx.x);
+    const TailJob &J = tb.job[j];
+    const uint32_t tid = (blockIdx.x - tb.first_block[j]) * blockDim.x + threadIdx.x;
+    if (tid >= tail_level_threads(J.cm1, J.V, k)) return;
+    const uint32_t nk = (1u << J.cm1) >> k, n_main = J.V * nk, n_tree = J.V * (nk >> 1);
+    const XYZZ *in = J.lvl[(k - 1) & 1];
+    XYZZ *out = J.lvl[k & 1];
+    // operand items a, b (nullptr = infinity) and the output slot
+    const XYZZ *a, *b;
+    XYZZ *dst;
+    auto x_prev = [&](uint32_t i) -> const XYZZ * { // item i of X_{k-1}
+        if (k > 1) return in + i;
+        const uint32_t t0 = J.task_off[i];
+        return t0 == J.task_off[i + 1] ? nullptr : J.partial + t0;
+    };
+    if (tid < n_main) {
+        a = x_prev(2 * tid);
+        b = x_prev(2 * tid + 1);
+        dst = out + tid;
     } else {
-        const XYZZ *src = inC + (size_t)(a - 1) * r.n_in + (size_t)s * L;
-        uint32_t j = 1;
-        vs_load_acc(S, src);
-        vs_load_q(S, src + 1);
-        fqvm_run_noinv(S, VPC_ADD, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
-            if (++j >= L) {
-                vs_store_acc(outC + (size_t)a * n_out + s, S_);
-                return false;
-            }
-            vs_load_q(S_, src + j);
-            pc = VPC_ADD;
+        const uint32_t t = tid - n_main, tj = t / n_tree, u = t - tj * n_tree;
+        if (tj == k - 1) { // first halving of tree k-1: the odd items of X_{k-1}
+            a = x_prev(4 * u + 1);
+            b = x_prev(4 * u + 3);
+        } else {           // Y_tj of the previous launch: 2 n_tree items behind the 2 n_main of X_{k-1}
+            const XYZZ *y = in + 2 * n_main + (size_t)tj * (2 * n_tree);
+            a = y + 2 * u;
+            b = y + 2 * u + 1;
+        }
+        dst = out + n_main + (size_t)tj * n_tree + u;
+    }
+    FqSlots S;
+    if (a)
+        vs_load_acc(S, a);
+    else
+        vs_acc_inf(S);
+    if (b)
+        vs_load_q(S, b);
+    else
+        vs_zero(S, VS_QZZ); // the add program only tests QZZ
+    fqvm_run_noinv(S, VPC_ADD, [&](uint32_t, uint32_t &, FqSlots &S_) {
+        vs_store_acc(dst, S_);
+        return false;
+    });
+}
+
+// fin[v*c + j] = 2^(j + c v) S_{j,v} for j < c-1, fin[v*c + c-1] = 2^(c v) Root_v
+__global__ void __launch_bounds__(128, 3) k_tail_scale(TailBatch tb)
+{
+    const uint32_t jb = tail_find_job(tb, blockIdx.x);
+    const TailJob &J = tb.job[jb];
+    const uint32_t tid = (blockIdx.x - tb.first_block[jb]) * blockDim.x + threadIdx.x;
+    const uint32_t c = J.cm1 + 1, V = J.V;
+    if (tid >= V * c) return;
+    const uint32_t v = tid / c, j = tid - v * c;
+    const XYZZ *s2 = J.lvl[(J.cm1 - 1) & 1]; // level c-2: X (2 per set) | Y_0 .. Y_{c-3} (1 per set)
+    const XYZZ *src;
+    uint32_t ndbl = c * v;
+    if (j == J.cm1) {
+        src = J.lvl[J.cm1 & 1] + v; // root
+    } else {
+        src = j + 1 == J.cm1 ? s2 + 2 * v + 1 : s2 + 2 * V + (size_t)j * V + v;
+        ndbl += j;
+    }
+    FqSlots S;
+    vs_load_acc(S, src);
+    XYZZ *dst = J.fin + tid;
+    if (ndbl == 0 || vs_is_zero(S, VS_ZZ)) {
+        vs_store_acc(dst, S);
+        return;
+    }
+    fqvm_run_noinv(S, VPC_DBL, [&](uint32_t, uint32_t &pc, FqSlots &S_) {
+        if (--ndbl) {
+            pc = VPC_DBL;
             return true;
-        });
+        }
+        vs_store_acc(dst, S_);
+        return false;
+    });
+}
+
+// fin[0] = sum of the job's V*c terms: pair tree, one CTA per job
+__global__ void __launch_bounds__(128, 1) k_tail_sum(TailBatch tb)
+{
+    const TailJob &J = tb.job[blockIdx.x];
+    const uint32_t n = J.V * (J.cm1 + 1);
+    for (uint32_t step = 1; step < n; step <<= 1) {
+        const uint32_t n_pairs = (n - step + 2 * step - 1) / (2 * step);
+        for (uint32_t q = threadIdx.x; q < n_pairs; q += blockDim.x) {
+            XYZZ *dst = J.fin + 2 * step * q;
+            FqSlots S;
+            vs_load_acc(S, dst);
+            vs_load_q(S, dst + step);
+            fqvm_run_noinv(S, VPC_ADD, [&](uint32_t, uint32_t &, FqSlots &S_) {
+                vs_store_acc(dst, S_);
+                return false;
+            });
+        }
+        __threadfence_block();
+        __syncthreads();
     }
 }
 
-// After the last level every array has V items (one per bucket set). For set v:
-//   R_v = T_0 + L_0 (T_1 + L_1 (T_2 + ...)),  T_i = C[n_levels-1-i][v]
-// result = sum_v 2^(c v) R_v (Horner, top set first), normalised to libff special form
-// (to_special, bw6_761_g1.cpp:58-77). One thread.
-__global__ void __launch_bounds__(32, 1) k_final(MsmPlan p, const XYZZ *C, Proj *out)
+// result = fin[0] in libff special form (to_special, bw6_761_g1.cpp:58-77); thread i serves job i
+__global__ void __launch_bounds__(32, 1) k_tail_norm(TailBatch tb)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (threadIdx.x >= tb.n_jobs) return;
+    const TailJob &J = tb.job[threadIdx.x];
     FqSlots S;
-    const uint32_t nl = p.n_levels, V = p.V;
-    int v = (int)V - 1;
-    // state machine: for each set v (top first): acc = c doublings of acc (skip for the top set),
-    // then inner Horner into R (kept in ACC via Q adds): we compute R_v in the R slots? Simpler:
-    // keep the overall result in ACC and build R_v by Horner *inside ACC* using linearity:
-    //   result = (((prev * 2^c) + stuff)) -- not linear in that way, so R_v is built in ACC after
-    // saving prev to `out` scratch... Instead: build R_v first in ACC, then add 2^c * prev kept in R:
-    //   R slots hold prev (already multiplied); sequence per set: R = 2^c R (dbl_r x c); ACC = R_v; R += ACC.
-    vs_zero(S, VS_RX);
-    vs_one(S, VS_RY);
-    vs_zero(S, VS_RZZ);
-    vs_zero(S, VS_RZZZ);
-    uint32_t stage = 0;   // 0: doubling R (c times)  1: inner Horner doubling  2: inner add  3: R += ACC  4: normalise
-    uint32_t dbl_left = 0; // doublings left in the current run
-    int lev = 0;           // current level in the inner Horner (from nl-1 down to 0)
-    // kick off: first set needs no doublings of R (R = inf)
-    auto start_set = [&](uint32_t &pc, FqSlots &S_) {
-        // ACC = T_{nl-1} = C[0][v]
-        vs_load_acc(S_, C + (size_t)0 * V + v);
-        lev = (int)nl - 1;
-        // next: multiply by L_{lev-1}... handled by stage 1
-        if (lev == 0) {
-            stage = 3;
-            pc = VPC_ADD_R;
+    vs_load_acc(S, J.fin);
+    Proj *out = J.result;
+    fqvm_run(S, VPC_TOAFF, [&](uint32_t id, uint32_t &, FqSlots &S_) {
+        vs_one(S_, VS_T0);
+        if (id == 2) { // infinity: (0, one, 0)
+            uint4 *d = reinterpret_cast<uint4 *>(out);
+            for (int q = 0; q < 18; q++) d[q] = make_uint4(0, 0, 0, 0);
+            vs_get(&out->Y, S_, VS_T0);
         } else {
-            stage = 1;
-            dbl_left = p.lbits[lev - 1];
-            pc = VPC_DBL;
+            vs_get(&out->X, S_, VS_QX);
+            vs_get(&out->Y, S_, VS_QY);
+            vs_get(&out->Z, S_, VS_T0);
         }
-    };
-    uint32_t pc0 = 0;
-    start_set(pc0, S);
-    fqvm_run(S, pc0, [&](uint32_t id, uint32_t &pc, FqSlots &S_) {
-        if (stage == 4) {
-            // id 1: affine in QX, QY ; id 2: infinity
-            if (id == 2) {
-                uint4 *d = reinterpret_cast<uint4 *>(out);
-                for (int k = 0; k < 18; k++) d[k] = make_uint4(0, 0, 0, 0);
-                vs_one(S_, VS_T0);
-                vs_get(&out->Y, S_, VS_T0);
-            } else {
-                vs_get(&out->X, S_, VS_QX);
-                vs_get(&out->Y, S_, VS_QY);
-                vs_one(S_, VS_T0);
-                vs_get(&out->Z, S_, VS_T0);
-            }
-            return false;
-        }
-        if (stage == 1) { // inner doubling run
-            if (--dbl_left > 0) {
-                pc = VPC_DBL;
-                return true;
-            }
-            // ACC = L_{lev-1} * (...) ; add T_{lev-1} = C[nl-1-(lev-1)][v]
-            lev--;
-            vs_load_q(S_, C + (size_t)(nl - 1 - lev) * V + v);
-            stage = 2;
-            pc = VPC_ADD;
-            return true;
-        }
-        if (stage == 2) {
-            if (lev == 0) {
-                stage = 3;
-                pc = VPC_ADD_R; // R += ACC
-            } else {
-                stage = 1;
-                dbl_left = p.lbits[lev - 1];
-                pc = VPC_DBL;
-            }
-            return true;
-        }
-        if (stage == 3) { // R += R_v done
-            if (--v < 0) {
-                // result = R -> ACC, normalise
-                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_X * 6]), S_, VS_RX);
-                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_Y * 6]), S_, VS_RY);
-                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_ZZ * 6]), S_, VS_RZZ);
-                vs_get(reinterpret_cast<Fq *>(&S_.w[VS_ZZZ * 6]), S_, VS_RZZZ);
-                stage = 4;
-                pc = VPC_TOAFF;
-                return true;
-            }
-            stage = 0;
-            dbl_left = p.c;
-            pc = VPC_DBL_R;
-            return true;
-        }
-        // stage 0: doubling R
-        if (--dbl_left > 0) {
-            pc = VPC_DBL_R;
-            return true;
-        }
-        start_set(pc, S_);
-        return true;
+        return false;
     });
 }
 
@@ -1291,7 +1254,7 @@ struct MsmBuffers {
     int32_t *digits;
     uint32_t *counts, *offsets, *cursor, *ntasks, *task_off, *task_start, *task_len, *task_bucket, *order, *len_hist, *len_cursor,
         *entries, *scan_tmp;
-    XYZZ *partial, *lvlA[2], *lvlC[2];
+    XYZZ *partial, *lvl[2], *fin;
     Affine *tree_lvl[2]; // pair-tree levels: odd levels in [0], even levels >= 2 in [1]
     TreeMeta *tree_meta;
     Proj *result;
@@ -1326,18 +1289,9 @@ inline MsmBuffers msm_layout(const MsmPlan &p, uint8_t *base)
     b.entries = (uint32_t *)take(nd * 4);
     b.scan_tmp = (uint32_t *)take((nbk / (SCAN_BLOCK * SCAN_ITEMS) + 2) * 4);
     b.partial = (XYZZ *)take(p.max_tasks * sizeof(XYZZ));
-    // level arrays: after level 0 there are n_buckets >> l0 items per array and up to n_levels arrays
-    size_t n1 = nbk >> p.lbits[0];
-    size_t carry_items = 0, items = n1;
-    for (uint32_t k = 0; k < p.n_levels; k++) {
-        size_t need = (size_t)(k + 1) * items;
-        if (need > carry_items) carry_items = need;
-        if (k + 1 < p.n_levels) items >>= p.lbits[k + 1];
-    }
-    for (int i = 0; i < 2; i++) {
-        b.lvlA[i] = (XYZZ *)take(n1 * sizeof(XYZZ));
-        b.lvlC[i] = (XYZZ *)take(carry_items * sizeof(XYZZ));
-    }
+    // tail level buffers: launch k writes V * (n_k + k * n_k / 2) items, largest at k = 1 (3/4 of the buckets)
+    for (int i = 0; i < 2; i++) b.lvl[i] = (XYZZ *)take((nbk - nbk / 4) * sizeof(XYZZ));
+    b.fin = (XYZZ *)take((size_t)p.V * p.c * sizeof(XYZZ));
     b.tree_lvl[0] = b.tree_lvl[1] = nullptr;
     b.tree_meta = (TreeMeta *)take(sizeof(TreeMeta));
     if (p.acc_mode == MSM_ACC_TREE) {
@@ -1349,11 +1303,11 @@ inline MsmBuffers msm_layout(const MsmPlan &p, uint8_t *base)
     return b;
 }
 
-// Number of kernel launches msm_launch_front + msm_launch_tail issue for plan p.
-inline uint64_t msm_launch_count(const MsmPlan &p)
+// Number of kernel launches msm_launch_front issues for plan p (the tail counts its own).
+inline uint64_t msm_front_launch_count(const MsmPlan &p)
 {
-    if (p.acc_mode == MSM_ACC_TREE) return 1 + 3 + 1 + 1 + 3 + p.tree_rounds + 1 + p.n_levels + 1;
-    return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1 + 1 + p.n_levels + 1;
+    if (p.acc_mode == MSM_ACC_TREE) return 1 + 3 + 1 + 1 + 3 + p.tree_rounds + 1;
+    return 1 + 3 + 1 + 1 + 3 + 1 + 3 + 1 + 1;
 }
 
 // K pairs per thread for a round expected to hold `pairs` additions: a larger K spreads the
@@ -1420,29 +1374,60 @@ inline cudaError_t msm_launch_front(const MsmPlan &p, const MsmBuffers &b, const
     return cudaGetLastError();
 }
 
-// Second half: fold of split buckets, blocked running sums, Horner + normalisation — a chain of
-// small dependent kernels (latency-bound). Result (libff special form, 288 B) is left in
-// buffers.result.
-inline cudaError_t msm_launch_tail(const MsmPlan &p, const MsmBuffers &b, cudaStream_t st)
+// Second half of up to TAIL_MAX_JOBS MSMs whose bucket accumulation is done (or ordered before this
+// on `st`): see the tail section above. Each result (libff special form, 288 B) is left in its
+// buffers.result. Returns the number of launches through *n_launches.
+inline TailJob msm_tail_job(const MsmPlan &p, const MsmBuffers &b)
 {
-    if (p.acc_mode != MSM_ACC_TREE)
-        k_fold_heavy<<<MSM_FOLD_BLOCKS, 32, 0, st>>>(b.ntasks, b.len_hist + MSM_LEN_BINS + 1, b.task_off, b.partial);
-    ReduceLevel r{};
-    r.n_in = (uint32_t)p.n_buckets;
-    const XYZZ *inA = b.partial, *inC = nullptr;
-    for (uint32_t k = 0; k < p.n_levels; k++) {
-        r.l = p.lbits[k];
-        r.k = k;
-        r.level0 = k == 0;
-        XYZZ *outA = b.lvlA[k & 1], *outC = b.lvlC[k & 1];
-        uint32_t n_out = r.n_in >> r.l;
-        uint32_t threads = (k + 1) * n_out;
-        k_reduce_level<<<(threads + 127) / 128, 128, 0, st>>>(r, b.task_off, inA, inC, outA, outC);
-        inA = outA;
-        inC = outC;
-        r.n_in = n_out;
+    TailJob j{};
+    j.task_off = b.task_off;
+    j.heavy_list = b.ntasks; // reused by k_task_fill once the task scan has consumed it
+    j.heavy_count = b.len_hist + MSM_LEN_BINS + 1;
+    j.partial = b.partial;
+    j.lvl[0] = b.lvl[0];
+    j.lvl[1] = b.lvl[1];
+    j.fin = b.fin;
+    j.result = b.result;
+    j.cm1 = p.c - 1;
+    j.V = p.V;
+    return j;
+}
+
+inline cudaError_t msm_launch_tail_batch(const TailJob *jobs, uint32_t n_jobs, cudaStream_t st, uint64_t *n_launches = nullptr)
+{
+    if (n_jobs == 0 || n_jobs > TAIL_MAX_JOBS) return cudaErrorInvalidValue;
+    TailBatch tb{};
+    tb.n_jobs = n_jobs;
+    uint32_t max_cm1 = 0;
+    for (uint32_t i = 0; i < n_jobs; i++) {
+        tb.job[i] = jobs[i];
+        if (jobs[i].cm1 > max_cm1) max_cm1 = jobs[i].cm1;
     }
-    k_final<<<1, 32, 0, st>>>(p, inC, b.result);
+    uint64_t nl = 0;
+    // blocks(i) CTAs of `threads` per job
+    auto ranges = [&](auto blocks) -> uint32_t {
+        uint32_t acc = 0;
+        for (uint32_t i = 0; i < n_jobs; i++) {
+            tb.first_block[i] = acc;
+            acc += blocks(tb.job[i]);
+        }
+        for (uint32_t i = n_jobs; i <= TAIL_MAX_JOBS; i++) tb.first_block[i] = acc;
+        return acc;
+    };
+    uint32_t g = ranges([](const TailJob &) { return TAIL_FOLD_BLOCKS; });
+    k_tail_fold<<<g, 32, 0, st>>>(tb);
+    nl++;
+    for (uint32_t k = 1; k <= max_cm1; k++) {
+        g = ranges([k](const TailJob &J) { return (tail_level_threads(J.cm1, J.V, k) + 127) / 128; });
+        k_tail_level<<<g, 128, 0, st>>>(tb, k);
+        nl++;
+    }
+    g = ranges([](const TailJob &J) { return (J.V * (J.cm1 + 1) + 127) / 128; });
+    k_tail_scale<<<g, 128, 0, st>>>(tb);
+    k_tail_sum<<<n_jobs, 128, 0, st>>>(tb);
+    k_tail_norm<<<1, 32, 0, st>>>(tb);
+    nl += 3;
+    if (n_launches) *n_launches = nl;
     return cudaGetLastError();
 }
 

@@ -20,6 +20,7 @@
 // w^-k = -w^(m/2-k) from the same table.
 #pragma once
 #include <cstdint>
+#include <cstring>
 #include <map>
 #include <utility>
 #include <vector>
@@ -457,10 +458,8 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
     cudaError_t e = ntt_get_twiddles(tabs, log_m, st, &tw, launches);
     if (e != cudaSuccess) return e;
     const Fr *ctab = nullptr;
-    Fr one_g;
-    if (!coset) { // plain iFFT still needs the 1/m scaling: table for g = 1
-        cudaMemcpyFromSymbol(&one_g, FR_ONE, sizeof(Fr));
-    }
+    Fr one_g; // plain iFFT still needs the 1/m scaling: table for g = 1
+    memcpy(one_g.l, FR_ONE_HOST, sizeof(Fr));
     if (coset || inverse) {
         e = ntt_get_coset(tabs, log_m, coset ? *coset_g : one_g, inverse, st, &ctab, launches);
         if (e != cudaSuccess) return e;
@@ -605,7 +604,7 @@ inline cudaError_t ntt_dist_phase(NttTables &tabs, const Fr *in, Fr *out, uint32
     if (e != cudaSuccess) return e;
     const Fr *ctab = nullptr;
     Fr one_g;
-    if (!coset) cudaMemcpyFromSymbol(&one_g, FR_ONE, sizeof(Fr));
+    memcpy(one_g.l, FR_ONE_HOST, sizeof(Fr));
     if (coset || inverse) {
         e = ntt_get_coset(tabs, log_m, coset ? *coset_g : one_g, inverse, st, &ctab, launches);
         if (e != cudaSuccess) return e;

@@ -1,6 +1,7 @@
 // C ABI of libzecale_gpu.so (see include/zecale_gpu.h). One translation unit: the
 // device functions are header-defined so that each kernel gets a single out-of-line
 // copy of fq_mul & co.
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -167,26 +168,33 @@ void trace_mark(zecale_gpu_ctx *ctx, const char *label, cudaStream_t st, int lan
     ctx->marks.push_back({label, lane >= 0 ? lane : (int)(ctx->cur - ctx->lanes), e});
 }
 
-// Enqueue the second half of every pending asynchronous MSM: each on its lane's high-priority
-// stream, gated on the accumulation kernels of ALL pending MSMs, then joined back into the lane.
+// Enqueue the second half of every pending asynchronous MSM as ONE batch (each launch of the tail
+// serves all of them, msm_launch_tail_batch) on the first pending lane's high-priority stream, gated
+// on the accumulation kernels of all pending MSMs, then joined back into every lane.
 int flush_tails(zecale_gpu_ctx *ctx)
 {
-    for (Lane &L : ctx->lanes) {
-        if (!L.tail_pending) continue;
-        for (Lane &O : ctx->lanes)
-            if (O.tail_pending) CK(cudaStreamWaitEvent(L.hi, O.ev_acc, 0));
-    }
-    for (Lane &L : ctx->lanes) {
-        if (!L.tail_pending) continue;
-        const int lane = (int)(&L - ctx->lanes);
-        trace_mark(ctx, "tail0", L.hi, lane);
-        CK(msm_launch_tail(L.tail_plan, L.tail_buf, L.hi));
-        CK(cudaMemcpyAsync(&L.h->result, L.tail_buf.result, sizeof(Proj), cudaMemcpyDeviceToHost, L.hi));
-        CK(cudaEventRecord(L.ev_back, L.hi));
-        CK(cudaStreamWaitEvent(L.stream, L.ev_back, 0));
-        trace_mark(ctx, "tail1", L.stream, lane);
-    }
+    TailJob jobs[ZECALE_GPU_LANES];
+    Lane *owner[ZECALE_GPU_LANES];
+    uint32_t n = 0;
+    for (Lane &L : ctx->lanes)
+        if (L.tail_pending) {
+            jobs[n] = msm_tail_job(L.tail_plan, L.tail_buf);
+            owner[n++] = &L;
+        }
+    if (n == 0) return 0;
     for (Lane &L : ctx->lanes) L.tail_pending = false;
+    Lane &F = *owner[0];
+    const int lane = (int)(&F - ctx->lanes);
+    for (uint32_t i = 0; i < n; i++) CK(cudaStreamWaitEvent(F.hi, owner[i]->ev_acc, 0));
+    trace_mark(ctx, "tail0", F.hi, lane);
+    uint64_t nl = 0;
+    CK(msm_launch_tail_batch(jobs, n, F.hi, &nl));
+    ctx->launches += nl;
+    for (uint32_t i = 0; i < n; i++)
+        CK(cudaMemcpyAsync(&owner[i]->h->result, owner[i]->tail_buf.result, sizeof(Proj), cudaMemcpyDeviceToHost, F.hi));
+    CK(cudaEventRecord(F.ev_back, F.hi));
+    for (uint32_t i = 0; i < n; i++) CK(cudaStreamWaitEvent(owner[i]->stream, F.ev_back, 0));
+    trace_mark(ctx, "tail1", F.stream, lane);
     return 0;
 }
 
@@ -242,20 +250,29 @@ int sync_lanes(zecale_gpu_ctx *ctx)
     return rc;
 }
 
-void drain_timers(zecale_gpu_ctx *ctx)
+// Fold event pairs into the per-class totals. block = true (zecale_gpu_kernel_ms, shutdown) waits
+// for all lanes first; block = false (called from the enqueue paths when many pairs are pending)
+// only harvests the pairs that have already completed and never synchronises.
+void drain_timers(zecale_gpu_ctx *ctx, bool block = true)
 {
-    sync_lanes(ctx);
+    if (block) sync_lanes(ctx);
     for (int k = 0; k < 2; k++) {
-        for (auto &pr : ctx->ev_pending[k]) {
+        auto &v = ctx->ev_pending[k];
+        size_t keep = 0;
+        for (size_t i = 0; i < v.size(); i++) {
+            if (!block && cudaEventQuery(v[i].second) != cudaSuccess) {
+                v[keep++] = v[i];
+                continue;
+            }
             float ms = 0.f;
-            if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) {
+            if (cudaEventElapsedTime(&ms, v[i].first, v[i].second) == cudaSuccess) {
                 ctx->kernel_ms[k] += ms;
                 ctx->kernel_n[k]++;
             }
-            ctx->ev_pool.push_back(pr.first);
-            ctx->ev_pool.push_back(pr.second);
+            ctx->ev_pool.push_back(v[i].first);
+            ctx->ev_pool.push_back(v[i].second);
         }
-        ctx->ev_pending[k].clear();
+        v.resize(keep);
     }
 }
 
@@ -300,9 +317,7 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
         // empty sum = zero point (0, one, 0), as libff::multi_exp returns GroupT::zero()
         Proj z;
         memset(&z, 0, sizeof z);
-        uint32_t one[24];
-        CK(cudaMemcpyFromSymbol(one, FQ_ONE, sizeof one));
-        memcpy(z.Y.l, one, sizeof one);
+        memcpy(z.Y.l, FQ_ONE_HOST, sizeof z.Y.l);
         memcpy(out_point, &z, sizeof z);
         if (elapsed_ms) *elapsed_ms = 0.f;
         return 0;
@@ -327,8 +342,8 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
     } else {
         ctx->ev_pending[0].emplace_back(a0, a1);
     }
-    if (ctx->ev_pending[0].size() > 256) drain_timers(ctx);
-    ctx->launches += msm_launch_count(plan);
+    if (ctx->ev_pending[0].size() > 256) drain_timers(ctx, false);
+    ctx->launches += msm_front_launch_count(plan);
     CK(cudaMemcpyAsync(&L.h->stats[0], b.offsets + plan.n_buckets, 4, cudaMemcpyDeviceToHost, L.stream));
     CK(cudaMemcpyAsync(&L.h->stats[1], b.task_off + plan.n_buckets, 4, cudaMemcpyDeviceToHost, L.stream));
     if (nosync) { // the tail is issued by flush_tails (at the next sync), with its siblings
@@ -337,7 +352,10 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
         L.tail_plan = plan;
         L.tail_buf = b;
     } else {
-        CK(msm_launch_tail(plan, b, L.stream));
+        TailJob job = msm_tail_job(plan, b);
+        uint64_t nl = 0;
+        CK(msm_launch_tail_batch(&job, 1, L.stream, &nl));
+        ctx->launches += nl;
         if (elapsed_ms) CK(cudaEventRecord(L.ev1, L.stream));
         CK(cudaMemcpyAsync(&L.h->result, b.result, sizeof(Proj), cudaMemcpyDeviceToHost, L.stream));
     }
@@ -418,7 +436,7 @@ int ntt_device(zecale_gpu_ctx *ctx, Fr *d_a, unsigned log_m, unsigned flags, con
     CK(ntt_launch(ctx->ntt, d_a, (Fr *)ctx->cur->ws_ntt.p, log_m, flags, coset_g, ctx->cur->stream, &nl));
     CK(cudaEventRecord(e1, ctx->cur->stream));
     ctx->ev_pending[1].emplace_back(e0, e1);
-    if (ctx->ev_pending[1].size() > 256) drain_timers(ctx);
+    if (ctx->ev_pending[1].size() > 256) drain_timers(ctx, false);
     ctx->launches += nl;
     return 0;
 }
@@ -819,16 +837,31 @@ int zecale_gpu_msm_g2(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride
     return msm_host(ctx, bases, base_stride, scalars, scalar_stride, scalar_index, n, out_point);
 }
 
-// Window size for a fully expanded image (one bucket set): fewer windows as n grows, bucket
-// count 2^(c-1) kept near n/2 so the running-sum reduction stays a few percent of the work.
+// Window size for a fully expanded image (one bucket set shared by all W = ceil(378/c) windows):
+// the c that minimises the Fq products of one MSM over n points,
+//     10 * (n W - non-empty buckets)   mixed additions (the first entry of a bucket is a copy)
+//   + 14 * 2 * 2^(c-1) * 1.5           additions of the tail (main tree + bit trees; weighted 1.5 because the
+//                                      tail runs latency-bound, below the accumulation's pipe utilisation),
+// with a surcharge when the top window holds so few bits that its entries pile up in a handful of
+// buckets (those are cut into tasks and folded, which lengthens the latency-bound tail). For the
+// batch-8 queries (n = 88 k ... 262 k) this gives c = 18: 378 = 21 * 18, no ragged top window.
 static uint32_t pinned_c(size_t n)
 {
-    uint32_t lg = 0;
-    while ((2ull << lg) <= n) lg++;
-    uint32_t c = lg;
-    if (c < 8) c = 8;
-    if (c > 20) c = 20;
-    return c;
+    uint32_t best_c = 8;
+    double best = 1e300;
+    for (uint32_t c = 8; c <= 20; c++) {
+        const double W = (double)((FR_SCALAR_BITS + 1 + c - 1) / c), NB = (double)(1u << (c - 1));
+        const double entries = (double)n * W;
+        const double nonempty = NB * (1.0 - exp(-entries / NB));
+        double cost = 10.0 * (entries - nonempty) + 42.0 * NB;
+        const uint32_t top_bits = FR_SCALAR_BITS + 1 - ((uint32_t)W - 1) * c; // data bits of the top window (incl. the carry bit)
+        if (top_bits + 4 < c && (double)n / (double)(1u << top_bits) > 8.0 * (entries / NB + 8.0)) cost *= 1.03;
+        if (cost < best) {
+            best = cost;
+            best_c = c;
+        }
+    }
+    return best_c;
 }
 
 // format 0: libff in-memory special-form points (288 B); 1: libzeth key-file bytes (X || Y, 192 B big-endian plain)
@@ -1086,7 +1119,7 @@ int zecale_gpu_ntt_dist_phase(zecale_gpu_ctx *ctx, const void *d_in, void *d_out
     CK(e);
     CK(cudaEventRecord(e1, ctx->cur->stream));
     ctx->ev_pending[1].emplace_back(e0, e1);
-    if (ctx->ev_pending[1].size() > 256) drain_timers(ctx);
+    if (ctx->ev_pending[1].size() > 256) drain_timers(ctx, false);
     ctx->launches += nl;
     if (sync) CK(cudaStreamSynchronize(ctx->cur->stream));
     return 0;
