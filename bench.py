@@ -14,7 +14,10 @@ distinct curve points (k_i * generator), the witness an aggregator-like mix, all
 
     value : proofs/s, inputs resident in HBM, timed with CUDA events (max over ranks)
     e2e   : proofs/s through the host-pointer C ABI (pinned host buffers, H2D/D2H inside)
-    --impl reference : the reference's own libff/libfqfft code (oracle/_ref) on the host cores
+    --impl reference : the SAME statement (same constraint matrices, witness and B index list) through the
+            reference's own code (oracle/_ref): libsnark::r1cs_to_qap_witness_map (serial mat-vecs + 7 libfqfft
+            transforms), multi_exp_filter_one_zero (A, L), kc_multi_exp_with_mixed_addition (B), multi_exp (H)
+            - the five calls of r1cs_gg_ppzksnark_prover - on all host cores, every step full size.
 
 N > 1: one process per GPU, each proving its own stream of proofs (replicas; no data-path
 collective) -> weak scaling, value = N * proofs / max-over-ranks time.
@@ -102,6 +105,53 @@ def fr_generator():
     return np.array([(x >> (64 * k)) & 0xFFFFFFFFFFFFFFFF for k in range(6)], dtype=np.uint64)
 
 
+class Statement:
+    """The synthetic batch-8-shaped statement both arms prove: constraint matrices, assignment, the index
+    list of the sparse B query and the coset generator. Seeded, so `--impl reference` sees the same bytes."""
+
+    def __init__(self, seed=1):
+        rng = np.random.default_rng(seed)
+        self.b_index = np.sort(rng.choice(N_A, N_B, replace=False)).astype(np.uint64)
+        self.w = witness_like(rng, N_A)
+        one = self.w[0].copy()
+        self.csr = [synthetic_csr(rng, nz, one) for nz in NNZ]
+        self.g = fr_generator()
+
+
+WORKLOAD = ("batch-8 aggregator Groth16 prove hot path (r1cs_gg_ppzksnark_prover): r1cs_to_qap_witness_map "
+            "(A.w, B.w, C.w mat-vecs + 7 NTT, m=2^18) + MSM A / B (G2,G1 pair) / H / L")
+
+
+def bench_config():
+    """Identical in both arms (the driver compares it)."""
+    return {"workload": WORKLOAD,
+            "msm_sizes": {"A": N_A, "B_g2": N_B, "B_g1": N_B, "H": N_H, "L": N_L}, "ntt_log_m": LOG_M,
+            "r1cs": {"constraints": N_CONSTRAINTS, "variables": N_VARS, "inputs": N_INPUTS, "nnz_abc": list(NNZ)},
+            "l2": "no flush needed: every step gathers ~3 GB of distinct base points from a 4 GB key image (L2 is 126 MB)"}
+
+
+def host_cpu():
+    """CPU model, logical and physical core counts of this box."""
+    model, phys = None, set()
+    try:
+        pid = cid = None
+        for ln in open("/proc/cpuinfo"):
+            k, _, v = ln.partition(":")
+            k, v = k.strip(), v.strip()
+            if k == "model name" and model is None:
+                model = v
+            elif k == "physical id":
+                pid = v
+            elif k == "core id":
+                cid = v
+            elif k == "" and pid is not None:
+                phys.add((pid, cid))
+                pid = cid = None
+    except OSError:
+        pass
+    return {"model": model, "logical": os.cpu_count(), "physical": len(phys) or os.cpu_count()}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -165,7 +215,8 @@ class Workload:
         # scratch); the pinned proving key is shared by all of them
         self.ctxs = [z.Context(device) for _ in range(max(1, depth))]
         self.ctx = self.ctxs[0]
-        rng = np.random.default_rng(seed)
+        st = Statement(seed)
+        rng = np.random.default_rng(seed + 1000)
         ctx = self.ctx
         # proving-key queries: distinct curve points, pinned (device-resident) once, like a loaded pk
         self.pk = {}
@@ -174,18 +225,17 @@ class Workload:
             pts = ctx.synth_bases(n, grp, seed=sd + 100 * seed)
             self.pk[name] = ctx.pin_bases(pts, grp)
             del pts
-        self.b_index = np.sort(rng.choice(N_A, N_B, replace=False)).astype(np.uint64)
-        self.g = fr_generator()
+        self.b_index = st.b_index
+        self.g = st.g
         # host inputs (pinned) of one proof
         def pinned(a):
             t = torch.from_numpy(a.view(np.int64)).pin_memory()
             return t, t.numpy().view(np.uint64)
         m = 1 << LOG_M
-        self.t_w, self.h_w = pinned(witness_like(rng, N_A))
+        self.t_w, self.h_w = pinned(st.w)
         # constraint system image: the evaluations <A_i,w>, <B_i,w>, <C_i,w> are computed
         # on the device from the assignment, as the specialised prover of the hooks does
-        one = self.h_w[0].copy()
-        self.r1cs = ctx.r1cs_load(N_CONSTRAINTS, N_INPUTS, N_VARS, [synthetic_csr(rng, nz, one) for nz in NNZ])
+        self.r1cs = ctx.r1cs_load(N_CONSTRAINTS, N_INPUTS, N_VARS, st.csr)
         assert ctx.r1cs_log_domain(self.r1cs) == LOG_M
         self.t_abc, self.h_abc = [], []
         for _ in range(3):
@@ -203,12 +253,12 @@ class Workload:
         self.last = None
         self.results = [None] * len(self.ctxs)
 
-    def run(self, steps, mode):
-        """`steps` proofs, `len(self.ctxs)` of them in flight: proof i is enqueued on context i mod
-        depth as soon as proof i - depth (same context) has delivered its results. Returns the
-        results of the last proof."""
+    def run(self, steps, mode, depth=None):
+        """`steps` proofs, `depth` (default: all contexts) of them in flight: proof i is enqueued on
+        context i mod depth as soon as proof i - depth (same context) has delivered its results.
+        Returns the results of the last proof."""
         enqueue = self.enqueue_resident if mode == "resident" else self.enqueue_e2e
-        d = len(self.ctxs)
+        d = min(depth or len(self.ctxs), len(self.ctxs))
         for i in range(steps):
             k = i % d
             if self.results[k] is not None:
@@ -242,6 +292,7 @@ class Workload:
         ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=idx, device=True)
         ctx.msm_pinned_async(4, self.pk["B1"], w, out[2], n=N_B, index=idx, device=True)
         ctx.msm_pinned_async(0, self.pk["H"], None, out[3], n=N_H, from_qap=True)
+        ctx.flush()
         return out
 
     def enqueue_e2e(self, slot=0):
@@ -257,6 +308,7 @@ class Workload:
         ctx.msm_pinned_async(3, self.pk["B2"], w, out[1], n=N_B, index=self.b_index)
         ctx.msm_pinned_async(4, self.pk["B1"], w, out[2], n=N_B, index=self.b_index)
         ctx.msm_pinned_async(0, self.pk["H"], None, out[3], n=N_H, from_qap=True)
+        ctx.flush()
         return out
 
     def step_blocking(self):
@@ -331,6 +383,19 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """DRAM bytes per k_accumulate launch from the committed ncu --set full capture (profiles/r02_traffic.json,
+    written from the .ncu-rep by tools/ncu_summary.py); None if no capture of this kernel version exists."""
+    p = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return None
+
+
+PAPER_PEAK_PRODUCTS = 148 * 32 * 1.965e9   # 148 SM x 32 IMAD.WIDE / clk x 1.965 GHz = 9.3e12 (SURVEY.md 8(d))
+
+
 def imad_peak(ctx):
     """Measured integer-multiply ceiling of this GPU: best Fq products/s of a dependent-chain
     Montgomery-product kernel over a few occupancies, in 32x32 products per second."""
@@ -356,39 +421,38 @@ def run_b200(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed(mode, steps, depth=None):
+        """(seconds, launches) of `steps` proofs; CUDA events around host-synchronising calls, wall clock kept if larger."""
+        l0 = wl.launch_count()
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        t0 = time.perf_counter()
+        wl.run(steps, mode, depth)       # returns after every context has synchronised its lanes
+        torch.cuda.synchronize()
+        ev1.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        t = ev0.elapsed_time(ev1) * 1e-3
+        barrier()
+        # the library runs on its own streams, bracketed by host-synchronising calls: the events enclose it
+        return max(t, wall) if t < 0.5 * wall else t, wl.launch_count() - l0
+
     # ---- device-resident arm (value)
     wl.run(args.warmup, "resident")
-    wl.kernel_ms(0)
-    wl.kernel_ms(1)
-    launches0 = wl.launch_count()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    t0 = time.perf_counter()
-    wl.run(args.steps, "resident")   # returns after every context has synchronised its lanes
-    torch.cuda.synchronize()
-    ev1.record()
-    barrier()
-    t_res = max(ev0.elapsed_time(ev1) * 1e-3, 0.0)
-    wall_res = time.perf_counter() - t0
-    # the library runs on its own stream; its work is bracketed by host-synchronising calls, so the
-    # torch events above enclose it; keep the larger of the two clocks to be safe
-    t_res = max(t_res, wall_res) if t_res < 0.5 * wall_res else t_res
+    t_res, launches = timed("resident", args.steps)
     clocks = sampler.stop()
-    launches = wl.launch_count() - launches0
-    acc_ms, acc_n = wl.kernel_ms(0)
-    ntt_ms, ntt_n = wl.kernel_ms(1)
 
     # ---- end-to-end arm (host pointers)
     wl.run(max(args.depth, min(args.warmup, 2)), "e2e")   # every context in flight takes one host-pointer step (staging buffers) first
-    barrier()
-    t0 = time.perf_counter()
-    wl.run(args.steps, "e2e")
-    torch.cuda.synchronize()
-    t_e2e = time.perf_counter() - t0
-    barrier()
+    t_e2e, _ = timed("e2e", args.steps)
+
+    # ---- one proof at a time (what a caller without a pipeline reaches)
+    wl.run(2, "e2e", depth=1)
+    t_d1, _ = timed("e2e", max(3, min(args.steps, 10)), depth=1)
+    t_d1 /= max(3, min(args.steps, 10))
 
     # ---- secondary headline: G1 MSM 2^20 latency (rank 0, N = 1 only)
     msm20 = None
@@ -396,58 +460,79 @@ def run_b200(args, rank, world, local_rank):
         n = 1 << 20
         pts = ctx.synth_bases(n, wl.z.G1, seed=77)
         pin = ctx.pin_bases(pts)
-        sc = torch.from_numpy(random_fr(np.random.default_rng(5), n).view(np.int64)).cuda()
+        sc_h = random_fr(np.random.default_rng(5), n)
+        t_sc = torch.from_numpy(sc_h.view(np.int64)).pin_memory()
+        sc = t_sc.cuda()
         torch.cuda.synchronize()
         ts = [ctx.msm_pinned_dev(pin, sc.data_ptr(), n)[1] for _ in range(4)]
-        msm20 = min(ts[1:])
+        h_sc = t_sc.numpy().view(np.uint64)
+        th = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            ctx.msm_pinned(pin, h_sc)
+            th.append((time.perf_counter() - t0) * 1e3)
+        msm20 = {"device_resident_ms": min(ts[1:]), "host_to_host_pinned_key_ms": min(th), "c": ctx.msm_last_stats()["c"]}
         pin.release()
         del sc, pts
 
     if world > 1:
-        tt = torch.tensor([t_res, t_e2e], dtype=torch.float64, device="cuda")
+        tt = torch.tensor([t_res, t_e2e, t_d1], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_res, t_e2e = tt.tolist()
+        t_res, t_e2e, t_d1 = tt.tolist()
     out = None
     if rank == 0:
         peaks, peaks_src = measured_peaks()
         peak_prod = imad_peak(ctx)
         madds, shapes, iso_acc_ms, iso_ntt_ms, iso_ntt_n = wl.isolated_kernels()
         acc_s = iso_acc_ms * 1e-3                            # the step's 5 accumulate launches, each timed alone
-        achieved = madds * FQ_MUL_PER_MADD * PRODUCTS_PER_FQ_MUL / acc_s if acc_s > 0 else 0.0
-        ntt_bytes = 7 * 192 * (1 << LOG_M)                   # 2 passes x (48 B read + 48 B write) per element
+        prod_step = madds * FQ_MUL_PER_MADD * PRODUCTS_PER_FQ_MUL
+        achieved = prod_step / acc_s if acc_s > 0 else 0.0
+        step_s = t_res / args.steps
+        m = 1 << LOG_M
+        ntt_bytes = 7 * 192 * m                              # 2 passes x (48 B read + 48 B write) per element
+        ntt_products = 7 * 300 * (m // 2 * LOG_M + m)        # butterflies + the one scaling pass of each transform
         ntt_s = iso_ntt_ms * 1e-3                            # the step's 7 transforms, timed alone
-        overlapped = {"accumulate_ms_per_step": acc_ms / max(args.steps, 1), "ntt_ms_per_step": ntt_ms / max(args.steps, 1),
-                      "note": "event brackets inside the timed region (kernels co-scheduled with sibling lanes / the other proof)"}
+        traffic = ncu_traffic()
         out = {
             "metric": METRIC, "value": world * args.steps / t_res, "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * step_s,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32x24 (761-bit Fq) / u32x12 (377-bit Fr)",
-            "data": "synthetic (seeded curve points k_i*G, aggregator-like witness)",
-            "config": {"workload": "batch-8 aggregator Groth16 prove hot path: witness map (A.w,B.w,C.w mat-vecs + 7 NTT, m=2^18) + MSM A/B(G2,G1)/H/L",
-                       "msm_sizes": {"A": N_A, "B_g2": N_B, "B_g1": N_B, "H": N_H, "L": N_L}, "ntt_log_m": LOG_M,
-                       "r1cs": {"constraints": N_CONSTRAINTS, "nnz_abc": list(NNZ)},
-                       "parallelism": "replicas (one proof stream per GPU)" if world > 1 else "single GPU",
-                       "proofs_in_flight": args.depth,
-                       "l2": "inputs larger than L2 (158 MB of bases per step)"},
+            "data": "synthetic (seeded curve points k_i*G, aggregator-like witness and constraint matrices)",
+            "config": bench_config(),
+            "arm": {"parallelism": "replicas (one proof stream per GPU, no data-path collective)" if world > 1 else "single GPU",
+                    "proofs_in_flight": args.depth,
+                    "value_depth1": world / t_d1, "ms_per_step_depth1": 1e3 * t_d1,
+                    "value_depth1_note": "host-pointer C ABI, ONE proof in flight: what a caller that proves strictly one at a time reaches"},
             "e2e": {"value": world * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": Workload.E2E_H2D,
                     "d2h_bytes_per_step": Workload.E2E_D2H},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "imad", "bound_note": "integer-multiply pipe (sm__pipe_fmaheavy): neither HBM- nor tensor-bound, SURVEY.md 8(d)", "kernel": "k_accumulate (MSM bucket accumulation)", "achieved": achieved / 1e12,
+            "roofline": {"bound": "imad", "bound_note": "integer-multiply pipe (sm__pipe_fmaheavy): neither HBM- nor tensor-bound, SURVEY.md 8(d)",
+                         "kernel": "k_accumulate (MSM bucket accumulation)", "achieved": achieved / 1e12,
                          "peak": peak_prod / 1e12, "unit": "T(32x32 products)/s", "frac": achieved / peak_prod if peak_prod else None,
                          "peak_source": "measured in this run: dependent-chain Fq Montgomery products (k_bench_fq_mul)",
-                         "share_of_step": acc_s / (t_res / args.steps), "launches_per_step": acc_n / max(args.steps, 1),
-                         "launch_ms_avg": 1e3 * acc_s / 5, "timing": "CUDA events on the launching stream, each launch alone on the GPU",
-                         "algorithmic_products_per_launch_avg": madds * FQ_MUL_PER_MADD * PRODUCTS_PER_FQ_MUL / 5,
+                         "peak_paper": PAPER_PEAK_PRODUCTS / 1e12, "frac_of_paper_peak": achieved / PAPER_PEAK_PRODUCTS,
+                         "launches_per_step": 5, "launch_ms_avg": 1e3 * acc_s / 5,
+                         "timing": "CUDA events on the launching stream, each of the step's five launches alone on the GPU",
+                         "algorithmic_products_per_launch_avg": prod_step / 5,
                          "hbm_algorithmic_bytes_per_launch_avg": (madds + sum(v["tasks"] for v in shapes.values())) * 192 / 5,
-                         "in_step": overlapped,
+                         "in_step_achieved": prod_step / step_s / 1e12,
+                         "in_step_frac": prod_step / step_s / peak_prod if peak_prod else None,
+                         "in_step_note": "the accumulate products of one step / the driver-timed ms_per_step: a lower bound on the pipe's "
+                                         "useful load inside the timed region (tails, transforms and sorting excluded from the numerator)",
                          "madds_per_step": madds, "msm_shapes": shapes,
-                         "traffic": 2.19e9, "traffic_source": "ncu r01, A-query launch: dram read 1.24 GB + write 0.95 GB (profiles/r01_k_accumulate_raw.md; the writes are the VM slot file leaving L1, the partial sums are 26 MB)"},
+                         "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
+                         "traffic_source": traffic["source"] if traffic else "no ncu capture of this kernel version committed yet"},
             "roofline_ntt": {"bound": "hbm", "kernel": "k_ntt_pass (Fr radix-2 NTT, 7 transforms per step)",
                              "achieved": ntt_bytes / ntt_s / 1e9 if ntt_s > 0 else None, "peak": peaks["hbm_gbs"],
                              "unit": "GB/s", "frac": (ntt_bytes / ntt_s / 1e9) / peaks["hbm_gbs"] if ntt_s > 0 else None,
-                             "peak_source": peaks_src, "share_of_step": ntt_s / (t_res / args.steps), "traffic": None},
-            "msm_g1_2e20_ms": msm20,
+                             "peak_source": peaks_src,
+                             "achieved_imad": ntt_products / ntt_s / 1e12 if ntt_s > 0 else None,
+                             "frac_imad": ntt_products / ntt_s / peak_prod if ntt_s > 0 and peak_prod else None,
+                             "imad_note": "300 products per Fr product x (m/2 log2 m butterflies + m scalings) per transform; the 377-bit "
+                                          "NTT is integer-multiply bound (SURVEY.md 8(d)), the HBM fraction is what north_star asks to see",
+                             "transforms_ms": iso_ntt_ms, "share_of_step": ntt_s / step_s, "traffic": None},
+            "msm_g1_2e20": msm20,
         }
     wl.close()
     if world > 1:
@@ -456,51 +541,54 @@ def run_b200(args, rank, world, local_rank):
 
 
 class ReferenceWorkload:
-    """The same step on the host cores with the UNMODIFIED reference (oracle/_ref):
-    libfqfft transforms of r1cs_to_qap_witness_map and libff::multi_exp (BDLO12_signed, special
-    bases, chunks = all threads) / kc-style pair MSM at the batch-8 sizes. `frac` < 1 takes the
-    first frac*n points of every MSM (bounded sample); MSM time is then scaled by 1/frac."""
+    """The same statement on the host cores with the UNMODIFIED reference (oracle/_ref), through the
+    calls r1cs_gg_ppzksnark_prover makes (r1cs_gg_ppzksnark.tcc:477-580): r1cs_to_qap_witness_map
+    (serial mat-vecs + 7 libfqfft transforms), multi_exp_filter_one_zero for A and L,
+    kc_multi_exp_with_mixed_addition for the sparse (G2, G1) B query, multi_exp for H; BDLO12_signed,
+    special bases, chunks = threads. Always full size. Bases are (i+1)*G (the cost of a Pippenger pass
+    does not depend on which distinct points it sums)."""
 
-    def __init__(self, frac=1.0):
+    def __init__(self, threads=None):
         from oracle import ref as R
-        self.R = R
         self.ref = R.Ref()
-        self.threads = self.ref.threads
-        self.frac = frac
-        rng = np.random.default_rng(1)
-        nmax = int(max(N_A, N_H) * frac)
-        self.g1 = self.ref.bases_seq(nmax, 1)
-        self.g2 = self.ref.bases_seq(int(N_B * frac), 2)
-        self.w = witness_like(rng, N_A)
-        self.abc = [random_fr(rng, 1 << LOG_M) for _ in range(3)]
-        self.b_index = np.sort(rng.choice(N_A, N_B, replace=False))
+        self.threads = self.ref.set_threads(threads or os.cpu_count())   # torchrun exports OMP_NUM_THREADS=1
+        st = Statement(1)
+        self.st = st
+        self.g1 = self.ref.bases_seq(max(N_A, N_H), 1)
+        g2 = self.ref.bases_seq(N_B, 2)
+        self.kc = np.ascontiguousarray(np.hstack([g2, self.g1[:N_B]]))
+        assert self.ref.session_from_csr(N_CONSTRAINTS, N_INPUTS, N_VARS, st.csr, st.w) == 0
 
     def step(self):
-        """Returns (seconds for one proof's hot path scaled to full size, split)."""
-        ref, f = self.ref, self.frac
-        h, t_h = ref.qap_h(*self.abc)
-        nA, nB, nH, nL = (int(n * f) for n in (N_A, N_B, N_H, N_L))
-        wB = np.ascontiguousarray(self.w[self.b_index[:nB]])
-        _, tA = ref.msm(self.g1[:nA], self.w[:nA], 1)
-        _, tB2 = ref.msm(self.g2[:nB], wB, 2)
-        _, tB1 = ref.msm(self.g1[:nB], wB, 1)
-        _, tH = ref.msm(self.g1[:nH], h[:nH], 1)
-        _, tL = ref.msm(self.g1[:nL], self.w[N_INPUTS + 1:N_INPUTS + 1 + nL], 1)
-        t_msm = (tA + tB2 + tB1 + tH + tL) / f
-        return t_h + t_msm, {"h_poly_s": t_h, "msm_s": t_msm}
+        """Seconds of one proof's hot path (sum of the reference's own timed calls) and the split."""
+        ref, st = self.ref, self.st
+        h, t_map = ref.session_witness_map(1 << LOG_M)
+        _, tA = ref.msm(self.g1[:N_A], st.w, 1, method=1)
+        _, tB = ref.msm_kc(self.kc, st.b_index, N_A, st.w)
+        _, tH = ref.msm(self.g1[:N_H], h[:N_H], 1, method=0)
+        _, tL = ref.msm(self.g1[:N_L], st.w[N_INPUTS + 1:], 1, method=1)
+        return t_map + tA + tB + tH + tL, {"witness_map_s": t_map, "msm_a_s": tA, "msm_b_s": tB, "msm_h_s": tH, "msm_l_s": tL}
 
 
 def cpu_baseline_sample():
-    """cpu_baseline leg of the default run: one bounded sample of the step on the host cores."""
+    """cpu_baseline leg of the default run: one full-size step on all host cores, and one on 8 threads
+    (the count BASELINE.md's survey-container numbers were taken with)."""
     from oracle import ref as R
+    cpu = host_cpu()
     if not R.available():
-        return {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
+        return {"value": None, "unit": UNIT, "cores": cpu["logical"], "kind": "reference", "cpu": cpu,
                 "sample": "oracle/_ref not built on this box"}
-    rw = ReferenceWorkload(1.0)
+    rw = ReferenceWorkload()
     t, split = rw.step()
-    return {"value": 1.0 / t, "unit": UNIT, "cores": rw.threads, "kind": "reference",
-            "sample": "one full step, once: 7 libfqfft transforms at m=2^18 + the five libff::multi_exp<BDLO12_signed, special> "
-                      "calls at the batch-8 sizes (h_poly %.2f s, msm %.2f s)" % (split["h_poly_s"], split["msm_s"])}
+    out = {"value": 1.0 / t, "unit": UNIT, "cores": rw.threads, "kind": "reference", "cpu": cpu,
+           "sample": "one full-size step, once: libsnark r1cs_to_qap_witness_map (mat-vecs + 7 transforms, m=2^18) + multi_exp_filter_one_zero "
+                     "(A, L) + kc_multi_exp_with_mixed_addition (B) + multi_exp (H) at the batch-8 sizes",
+           "split_s": split}
+    if rw.threads > 8:
+        rw.threads = rw.ref.set_threads(8)
+        t8, _ = rw.step()
+        out["value_8_threads"] = 1.0 / t8
+    return out
 
 
 def run_reference(args, rank, world):
@@ -509,25 +597,27 @@ def run_reference(args, rank, world):
     from oracle import ref as R
     if not R.available():
         return {"impl": "reference", "unavailable": "oracle/_ref/libzecale_ref.so is not built (needs /root/reference at build time)"}
-    total = max(args.steps, 1) + 1
-    # a full step is ~15-25 s of 16-core CPU time; keep the whole run within a few minutes
-    frac = 1.0 if total <= 9 else (0.5 if total <= 18 else 0.25)
-    rw = ReferenceWorkload(frac)
-    ReferenceWorkload(0.02).step()  # warm-up on a small sample (page faults, OpenMP pool); W full CPU steps would only burn minutes
-    ts, split = [], None
+    rw = ReferenceWorkload()
+    cpu = host_cpu()
+    n_warm = 1 if args.warmup > 0 else 0
+    for _ in range(n_warm):
+        rw.step()
+    ts, splits = [], []
     for _ in range(max(args.steps, 1)):
-        t, split = rw.step()
+        t, sp = rw.step()
         ts.append(t)
+        splits.append(sp)
     t = sum(ts) / len(ts)
-    sample = ("each step: 7 libfqfft transforms (m=2^18; the serial A.w/B.w/C.w mat-vecs of the reference, ~0.3 s, are NOT included) + five libff::multi_exp<BDLO12_signed, special> calls on the first "
-              "%d%% of each base vector, MSM seconds scaled by %.0fx; warm-up = one 2%% step" % (int(frac * 100), 1 / frac))
+    split = {k: sum(sp[k] for sp in splits) / len(splits) for k in splits[0]}
+    sample = ("every step full size (no sub-sampling, no extrapolation): the unmodified reference's r1cs_to_qap_witness_map + the four "
+              "multi-exponentiation calls of r1cs_gg_ppzksnark_prover on the same statement as the b200 arm; %d timed steps after %d "
+              "full-size warm-up step (a CPU step is ~5 s; more warm-up would only burn minutes)" % (len(ts), n_warm))
     return {"impl": "reference", "metric": METRIC, "value": 1.0 / t, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64x12 (761-bit Fq) / u64x6 (377-bit Fr), GMP mpn", "data": "synthetic (seeded)",
-            "config": {"workload": "batch-8 aggregator Groth16 prove hot path: H-poly (7 NTT, m=2^18) + MSM A/B(G2,G1)/H/L",
-                       "msm_sizes": {"A": N_A, "B_g2": N_B, "B_g1": N_B, "H": N_H, "L": N_L}, "ntt_log_m": LOG_M,
-                       "parallelism": "OpenMP, %d threads" % rw.threads},
-            "cpu_baseline": {"value": 1.0 / t, "unit": UNIT, "cores": rw.threads, "kind": "reference", "sample": sample},
+            "config": bench_config(),
+            "arm": {"parallelism": "OpenMP, %d threads" % rw.threads, "cpu": cpu},
+            "cpu_baseline": {"value": 1.0 / t, "unit": UNIT, "cores": rw.threads, "kind": "reference", "sample": sample, "cpu": cpu},
             "e2e": {"value": 1.0 / t, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "split": split}
 

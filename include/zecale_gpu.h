@@ -183,6 +183,16 @@ int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_
 int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const void *aB, const void *aC,
                            unsigned log_m, const void *coset_g, void *out_h);
 int zecale_gpu_sync(zecale_gpu_ctx *ctx);
+/* Enqueue what the async calls since the last sync/flush deferred (the latency-bound second halves of
+ * their MSMs, issued together as one batch) without waiting for anything: a caller that keeps several
+ * proofs in flight (one context each) calls this after the last *_async call of a proof, so that the
+ * device can finish the proof while the host is already enqueueing the next one. zecale_gpu_sync
+ * implies it. */
+int zecale_gpu_flush(zecale_gpu_ctx *ctx);
+/* Page-locked host memory for buffers handed to the async calls (a pageable buffer makes every
+ * host-to-device copy synchronous). Not tied to a context; free with zecale_gpu_host_free. */
+void *zecale_gpu_host_alloc(size_t bytes);
+void zecale_gpu_host_free(void *p);
 
 /* ---- multi-GPU building blocks (one process per GPU; the exchange itself is the caller's:
  * NCCL through torch.distributed in zecale_b200/dist.py) --------------------------------

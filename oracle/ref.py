@@ -35,13 +35,21 @@ class Ref:
             raise FileNotFoundError(path + " (run `make -C oracle ref ref-agg` where /root/reference exists)")
         L = ctypes.CDLL(path)
         for f in ("zref_msm_g1", "zref_msm_g2", "zref_msm_g1_naive", "zref_msm_kc", "zref_ntt", "zref_qap_h",
-                  "zref_session_setup", "zref_session_prove_stock"):
+                  "zref_session_setup", "zref_session_prove_stock", "zref_session_witness_map",
+                  "zref_session_witness_gen_seconds", "zref_session_prove_pipeline", "zref_session_prove_threads",
+                  "zref_session_keypair_write", "zref_session_keypair_read"):
             getattr(L, f).restype = _d
         L.zref_fr_signed_digit.restype = ctypes.c_long
         L.zref_session_abc.restype = ctypes.c_long
         L.zref_optimal_c.restype = _sz
         self.L = L
         self.threads = L.zref_init()
+
+    def set_threads(self, n):
+        """OpenMP threads of the reference from here on (overrides OMP_NUM_THREADS, which torchrun sets to 1)."""
+        self.L.zref_set_threads(int(n))
+        self.threads = int(self.L.zref_threads())
+        return self.threads
 
     # ---- fields -------------------------------------------------------------------
     def fq_op(self, op, a, b=None):
@@ -164,6 +172,39 @@ class Ref:
     def session_setup(self, seed):
         return self.L.zref_session_setup(_u64(seed))
 
+    def session_keypair_write(self, path):
+        t = self.L.zref_session_keypair_write(path.encode())
+        if t < 0:
+            raise RuntimeError("keypair_write failed: %r" % t)
+        return t
+
+    def session_keypair_read(self, path):
+        t = self.L.zref_session_keypair_read(path.encode())
+        if t < 0:
+            raise RuntimeError("keypair_read failed: %r" % t)
+        return t
+
+    def session_from_csr(self, n_constraints, n_inputs, n_variables, csr, full):
+        """Session over a constraint system given as three (row_ptr u64, col u32, val (nnz, 6) u64) CSR
+        matrices and the assignment [1, primary, aux]."""
+        keep = [(np.ascontiguousarray(rp, dtype=np.uint64), np.ascontiguousarray(c, dtype=np.uint32),
+                 np.ascontiguousarray(v, dtype=np.uint64)) for rp, c, v in csr]
+        arr = lambda k: (_vp * 3)(*[t[k].ctypes.data for t in keep])
+        return self.L.zref_session_from_csr(_sz(n_constraints), _sz(n_inputs), _sz(n_variables), arr(0), arr(1), arr(2),
+                                            _p(np.ascontiguousarray(full)))
+
+    def session_witness_map(self, m=None):
+        """libsnark::r1cs_to_qap_witness_map (mat-vecs + 7 transforms) on the session; returns
+        (coefficients_for_H (m + 1, 6) or None when m is not given, seconds)."""
+        h = np.zeros((m + 1, 6), dtype=np.uint64) if m else None
+        t = self.L.zref_session_witness_map(_p(h))
+        if t < 0:
+            raise RuntimeError("no session")
+        return h, t
+
+    def session_witness_gen_seconds(self):
+        return float(self.L.zref_session_witness_gen_seconds())
+
     def session_sizes(self):
         sz = np.zeros(16, dtype=np.uint64)
         rc = self.L.zref_session_sizes(_p(sz))
@@ -252,6 +293,23 @@ class Ref:
 
     def hooks_unpin(self):
         return self.L.zref_hooks_unpin()
+
+    def session_prove_pipeline(self, count, rs_pairs):
+        """Hooked build: `count` proofs back to back through prove_async / collect; rs_pairs: (k, 2, 6) u64.
+        Returns (proofs (count, 576) u8, seconds)."""
+        rs = np.ascontiguousarray(rs_pairs, dtype=np.uint64)
+        proofs = np.zeros((count, 576), dtype=np.uint8)
+        t = self.L.zref_session_prove_pipeline(_sz(count), _p(rs), _sz(rs.shape[0]), _p(proofs))
+        if t < 0:
+            raise RuntimeError("zref_session_prove_pipeline failed: %r" % t)
+        return proofs, t
+
+    def session_prove_threads(self, n_threads, per_thread, r, s):
+        proofs = np.zeros((n_threads * per_thread, 576), dtype=np.uint8)
+        t = self.L.zref_session_prove_threads(_sz(n_threads), _sz(per_thread), _p(r), _p(s), _p(proofs))
+        if t < 0:
+            raise RuntimeError("zref_session_prove_threads failed: %r" % t)
+        return proofs, t
 
 
 def ints_to_limbs(vals, n64):

@@ -27,6 +27,8 @@
 #include <vector>
 
 #include <libff/algebra/curves/bw6_761/bw6_761_pp.hpp>
+#include <thread>
+
 #include <libff/algebra/scalar_multiplication/multiexp.hpp>
 #include <libff/common/profiling.hpp>
 #include <libff/common/rng.hpp>
@@ -84,6 +86,9 @@ struct session_t {
     G2 Bt_g;
     double t_witness_map = 0, t_msm_a = 0, t_msm_b = 0, t_msm_h = 0,
            t_msm_l = 0, t_total = 0;
+    // aggregator sessions: seconds spent in the generate_r1cs_witness statements of
+    // aggregator_circuit::prove (aggregator_circuit.tcc:136-157), i.e. SURVEY 8(f2)
+    double t_witness_gen = 0;
 };
 
 std::unique_ptr<session_t> S_ptr(new session_t());
@@ -625,6 +630,7 @@ template<size_t N> static int aggregator_session(uint64_t seed)
     // (aggregator_circuit.tcc:136-157) without the final generate_proof call
     // (built with -fno-access-control so the protoboard can be read back).
     std::array<const libsnark::r1cs_primary_input<libff::Fr<npp>> *, N> nested_inputs{};
+    const double tw0 = now_s();
     for (size_t i = 0; i < N; ++i) {
         nested_inputs[i] = &batch[i]->get_primary_inputs();
         agg._nested_proofs[i]->generate_r1cs_witness(batch[i]->get_proof());
@@ -633,7 +639,9 @@ template<size_t N> static int aggregator_session(uint64_t seed)
     agg._nested_vk_hash_gadget->generate_r1cs_witness();
     agg._aggregator_gadget->generate_r1cs_witness(nested_inputs);
     agg._nested_proof_results_packer->generate_r1cs_witness_from_bits();
+    const double tw1 = now_s();
 
+    S.t_witness_gen = tw1 - tw0;
     S.cs = agg.get_constraint_system();
     S.primary = agg._pb.primary_input();
     S.aux = agg._pb.auxiliary_input();
@@ -650,6 +658,8 @@ extern "C" int zref_session_aggregator(size_t batch, uint64_t seed)
     case 2: return aggregator_session<2>(seed);
     case 4: return aggregator_session<4>(seed);
     case 8: return aggregator_session<8>(seed);
+    case 16: return aggregator_session<16>(seed);
+    case 32: return aggregator_session<32>(seed);
     default: return -2;
     }
 #else
@@ -657,6 +667,89 @@ extern "C" int zref_session_aggregator(size_t batch, uint64_t seed)
     (void)seed;
     return -3;
 #endif
+}
+
+extern "C" double zref_session_witness_gen_seconds(void) { return S.t_witness_gen; }
+
+// A session whose constraint system is given as three CSR matrices (row i of matrix k =
+// constraints[i].{a,b,c}.terms; col 0 = the constant one) and whose assignment is `full` =
+// [1, primary..., aux...]: lets bench.py hand the SAME synthetic batch-8-shaped system to the
+// reference's own r1cs_to_qap_witness_map and to the device path.
+extern "C" int zref_session_from_csr(
+    size_t n_constraints, size_t n_inputs, size_t n_variables,
+    const uint64_t *const row_ptr[3], const uint32_t *const col[3], const void *const val[3],
+    const void *full)
+{
+    S_ptr.reset(new session_t());
+    S.cs.primary_input_size = n_inputs;
+    S.cs.auxiliary_input_size = n_variables - n_inputs;
+    S.cs.constraints.reserve(n_constraints);
+    for (size_t i = 0; i < n_constraints; ++i) {
+        libsnark::linear_combination<Fr> lc[3];
+        for (int k = 0; k < 3; ++k) {
+            const Fr *v = (const Fr *)val[k];
+            for (uint64_t t = row_ptr[k][i]; t < row_ptr[k][i + 1]; ++t)
+                lc[k].terms.emplace_back(libsnark::linear_term<Fr>(libsnark::variable<Fr>(col[k][t]), v[t]));
+        }
+        S.cs.constraints.emplace_back(libsnark::r1cs_constraint<Fr>(lc[0], lc[1], lc[2]));
+    }
+    const Fr *f = (const Fr *)full;
+    S.primary.assign(f + 1, f + 1 + n_inputs);
+    S.aux.assign(f + 1 + n_inputs, f + 1 + n_variables);
+    S.have_cs = true;
+    return 0;
+}
+
+// The reference's own r1cs_to_qap_witness_map (r1cs_to_qap.tcc:210-344: serial mat-vecs + 7 transforms)
+// on the session's system and assignment, d1 = d2 = d3 = 0 as the Groth16 prover calls it. h (may be
+// NULL) receives the m + 1 coefficients. Returns seconds.
+extern "C" double zref_session_witness_map(void *h)
+{
+    if (!S.have_cs)
+        return -1;
+    const double t0 = now_s();
+    const libsnark::qap_witness<Fr> w = libsnark::r1cs_to_qap_witness_map(
+        S.cs, S.primary, S.aux, Fr::zero(), Fr::zero(), Fr::zero(), true);
+    const double t1 = now_s();
+    if (h)
+        copy_out(h, w.coefficients_for_H);
+    return t1 - t0;
+}
+
+// The session's keypair to / from a file in libzeth's on-disk format (groth16_snark::keypair_write_bytes /
+// keypair_read_bytes, groth16_snark.tcc:178-191): lets the plain build prove with a key the hooked
+// build generated (large circuits: the CPU generator takes minutes). The reader
+// needs a session with the same constraint system. Returns seconds, or a negative code.
+extern "C" double zref_session_keypair_write(const char *path)
+{
+    if (!S.have_keys)
+        return -1;
+    const double t0 = now_s();
+    std::ofstream f(path, std::ios::binary);
+    if (!f)
+        return -2;
+    snark::keypair_write_bytes(*S.kp_ptr, f);
+    f.close();
+    return now_s() - t0;
+}
+
+extern "C" double zref_session_keypair_read(const char *path)
+{
+    if (!S.have_cs)
+        return -1;
+    const double t0 = now_s();
+    std::ifstream f(path, std::ios::binary);
+    if (!f)
+        return -2;
+    try {
+        S.kp_ptr.reset(new libsnark::r1cs_gg_ppzksnark_keypair<ppT>());
+        snark::keypair_read_bytes(*S.kp_ptr, f);
+    } catch (const std::exception &e) {
+        std::cerr << "zref_session_keypair_read: " << e.what() << std::endl;
+        return -3;
+    }
+    S.have_keys = true;
+    return now_s() - t0;
 }
 
 extern "C" double zref_session_setup(uint64_t seed)
@@ -957,6 +1050,84 @@ extern "C" int zref_session_prove_fused(const void *r48, const void *s48, void *
     return snark::verify(S.primary, proof, S.kp_ptr->vk) ? 0 : 1;
 #else
     (void)r48; (void)s48; (void)proof576; (void)msm5; (void)timings;
+    return -3;
+#endif
+}
+
+// Hooked build only: `count` proofs of the session's statement back to back through
+// zecale_gpu_hooks::prove_async / collect (up to pipeline_depth() in flight), proof i using the
+// randomness pair rs[i % n_rs] (each 96 bytes: r then s). proofs receives count x 576 bytes.
+// Returns the wall-clock seconds for all of them (host assembly and serialisation included),
+// or a negative code.
+extern "C" double zref_session_prove_pipeline(size_t count, const void *rs, size_t n_rs, void *proofs)
+{
+#ifdef ZECALE_GPU_HOOKS_HPP
+    if (!S.have_keys || !n_rs)
+        return -1;
+    namespace H = zecale_gpu_hooks;
+    const Fr *rsv = (const Fr *)rs;
+    const size_t depth = H::pipeline_depth();
+    std::vector<H::ticket_t *> tickets(count, nullptr);
+    try {
+        const double t0 = now_s();
+        for (size_t i = 0; i < count + depth; ++i) {
+            if (i >= depth && i - depth < count) {
+                const size_t j = i - depth;
+                auto proof = H::collect(tickets[j]);
+                tickets[j] = nullptr;
+                proof_bytes(proof, (char *)proofs + 576 * j);
+            }
+            if (i < count) {
+                tickets[i] = H::prove_async(S.kp_ptr->pk, S.primary, S.aux, true, rsv[2 * (i % n_rs)], rsv[2 * (i % n_rs) + 1]);
+                if (!tickets[i])
+                    return -4; // key not resident
+            }
+        }
+        return now_s() - t0;
+    } catch (const std::exception &e) {
+        std::cerr << "zref_session_prove_pipeline: " << e.what() << std::endl;
+        return -2;
+    }
+#else
+    (void)count; (void)rs; (void)n_rs; (void)proofs;
+    return -3;
+#endif
+}
+
+// Hooked build only: `n_threads` host threads prove the session's statement at the same time, each
+// `per_thread` times, through the specialised prover body with (r, s) given — what concurrent gRPC
+// workers would do (aggregator_server.cpp:399-415). proofs: n_threads * per_thread x 576 bytes.
+extern "C" double zref_session_prove_threads(size_t n_threads, size_t per_thread, const void *r48, const void *s48, void *proofs)
+{
+#ifdef ZECALE_GPU_HOOKS_HPP
+    if (!S.have_keys)
+        return -1;
+    Fr r, s;
+    std::memcpy((void *)&r, r48, 48);
+    std::memcpy((void *)&s, s48, 48);
+    std::vector<std::thread> th;
+    std::vector<int> rc(n_threads, 0);
+    const double t0 = now_s();
+    for (size_t t = 0; t < n_threads; ++t)
+        th.emplace_back([&, t] {
+            try {
+                for (size_t k = 0; k < per_thread; ++k) {
+                    auto proof = zecale_gpu_hooks::prove_with_rs(S.kp_ptr->pk, S.primary, S.aux, true, r, s, nullptr);
+                    proof_bytes(proof, (char *)proofs + 576 * (t * per_thread + k));
+                }
+            } catch (const std::exception &e) {
+                std::cerr << "zref_session_prove_threads: " << e.what() << std::endl;
+                rc[t] = 1;
+            }
+        });
+    for (auto &x : th)
+        x.join();
+    for (int v : rc)
+        if (v)
+            return -2;
+    return now_s() - t0;
+#else
+    (void)n_threads; (void)per_thread; (void)r48; (void)s48; (void)proofs;
     return -3;
 #endif
 }

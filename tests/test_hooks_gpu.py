@@ -112,5 +112,63 @@ def test_hooked_reference_prover_aggregator_batch8(pair, capsys):
             print("[batch-8 aggregator setup (generator_from_secrets)] reference CPU: %.2f s; hooked (A/B/H/L queries and gamma_ABC"
                   " as device batch exponentiations): %.2f s; proofs from both keys are byte-identical"
                   % (SETUP_SECONDS["cpu"], SETUP_SECONDS["hooked"]))
+        # --- the drop-in at pipelined throughput: K proofs back to back through prove_async / collect,
+        # alternating between two (r, s) pairs whose bytes the CPU build fixes
+        r2, s2 = cpu.fr_rng(0xD00D, 1)[0], cpu.fr_rng(0xF00D, 1)[0]
+        exp2 = cpu.session_prove(r2, s2)
+        assert exp2["verified"]
+        want = [exp["proof"].tobytes(), exp2["proof"].tobytes()]
+        rs = np.stack([np.stack([r, s]), np.stack([r2, s2])])
+        hooked.session_prove_pipeline(3, rs)          # every proof slot takes one proof first (tables, scratch)
+        k = 8
+        proofs, secs = hooked.session_prove_pipeline(k, rs)
+        for i in range(k):
+            assert proofs[i].tobytes() == want[i % 2], "pipelined proof %d differs" % i
+        # --- two host threads proving at the same time (the aggregator server's gRPC workers)
+        tproofs, tsecs = hooked.session_prove_threads(2, 3, r, s)
+        for i in range(6):
+            assert tproofs[i].tobytes() == want[0], "concurrent proof %d differs" % i
+        with capsys.disabled():
+            print("[batch-8 aggregator, hooked prover pipelined] %d proofs in %.3f s = %.1f proofs/s (prove_async/collect, real statement, "
+                  "host assembly + serialisation included); 2 threads x 3 proofs concurrently: %.3f s = %.1f proofs/s; witness generation "
+                  "(aggregator_circuit::prove's generate_r1cs_witness calls, reference CPU code, 1 thread): %.3f s"
+                  % (k, secs, k / secs, tsecs, 6 / tsecs, cpu.session_witness_gen_seconds()))
+        assert k / secs > 15.0
+    finally:
+        hooked.hooks_unpin()
+
+
+def test_hooked_reference_prover_aggregator_batch32(pair, capsys, tmp_path):
+    """BASELINE config 5's circuit for real: aggregator over 32 nested BLS12-377 proofs (920 718 constraints,
+    m = 2^20; aggregator_circuit.tcc:119-170). The hooked build generates the key (device batch
+    exponentiations) and writes it in libzeth's on-disk format; the plain CPU build reads that file and
+    proves; the hooked prover must return the same 576 bytes."""
+    import os
+    import time
+    cpu, hooked = pair
+    assert hooked.session_aggregator(32, 5) == 0
+    t0 = time.perf_counter()
+    hooked.session_setup(9)
+    t_setup = time.perf_counter() - t0
+    path = os.path.join(str(tmp_path), "agg32.keypair")
+    t_write = hooked.session_keypair_write(path)
+    assert cpu.session_aggregator(32, 5) == 0
+    t_read = cpu.session_keypair_read(path)
+    os.remove(path)
+    assert hooked.session_set_assignment(cpu.session_assignment()) == 0
+    sz = cpu.session_sizes()
+    assert sz["m"] == 1 << 20 and sz["num_constraints"] > 900000
+    r, s = cpu.fr_rng(0x3232, 1)[0], cpu.fr_rng(0x2323, 1)[0]
+    exp = cpu.session_prove(r, s)
+    assert exp["verified"]
+    assert hooked.hooks_pin_pk() == 0
+    try:
+        _check_fused(hooked, r, s, exp)
+        t_fused = min(_check_fused(hooked, r, s, exp) for _ in range(2))
+        with capsys.disabled():
+            print("\n[batch-32 aggregator, %d constraints, m = 2^20, MSM sizes A %d / B %d / H %d / L %d] hooked setup %.1f s "
+                  "(key file %.1f s to write, %.1f s to read); reference CPU prove (%d threads) %.2f s; specialised prover on the GPU %.3f s; "
+                  "identical proof bytes" % (sz["num_constraints"], sz["n_A"], sz["nnz_B"], sz["n_H"], sz["n_L"], t_setup, t_write, t_read,
+                                             cpu.threads, exp["timings"]["total"], t_fused))
     finally:
         hooked.hooks_unpin()

@@ -191,3 +191,24 @@ def test_msm_full_size_properties(gpu, ref, group, log_n):
     f = gpu.msm_g1 if group == 1 else gpu.msm_g2
     tail = f(np.ascontiguousarray(bases[half:]), np.ascontiguousarray(a[half:]))
     assert np.array_equal(add(head, tail), pa)
+
+
+@pytest.mark.parametrize("group,log_n", [(1, 18), (2, 18), (1, 20), (2, 20)])
+def test_msm_full_size_vs_libff(gpu, ref, group, log_n):
+    """BASELINE config 2 at 2^18 and at the headline size 2^20, G1 and G2, bit-exact against
+    libff::multi_exp<BDLO12_signed, special> (multiexp.tcc:648-688) on the reference's own bases
+    P_i = (i+1) G and SHA512_rng scalars: the pinned (expanded image, one bucket set) and the un-pinned
+    (one bucket set per window + doubling chain) entry points must both give libff's normalised point."""
+    n = 1 << log_n
+    bases = ref.bases_seq(n, group)
+    scalars = ref.fr_rng((group << 40) + n, n)
+    exp, _ = ref.msm(bases, scalars, group)
+    pinned = gpu.pin_bases(bases, group)
+    try:
+        assert np.array_equal(gpu.msm_pinned(pinned, scalars), exp), "pinned MSM differs from libff"
+        st = gpu.msm_last_stats()
+        assert st["bucket_sets"] == 1 and st["base_copies"] > 1
+    finally:
+        pinned.release()
+    f = gpu.msm_g1 if group == 1 else gpu.msm_g2
+    assert np.array_equal(f(bases, scalars), exp), "un-pinned MSM differs from libff"

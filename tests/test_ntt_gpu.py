@@ -51,6 +51,21 @@ def test_ntt_roundtrip_large(gpu, ref, log_m):
     assert np.array_equal(x, a)
 
 
+@pytest.mark.parametrize("log_m,flag_set", [(21, (0, 3)), (22, (0, 1, 2, 3)), (23, (0, 3)), (24, (0, 1, 2, 3))])
+def test_ntt_large_vs_libfqfft(gpu, ref, log_m, flag_set):
+    """BASELINE config 3 at its full sizes, bit for bit against libfqfft's basic_radix2_domain
+    (basic_radix2_domain.tcc:55-88): 2^21 / 2^22 are the largest two-pass transforms, 2^23 / 2^24 run the
+    three-pass factorisation (ntt.cuh, m = R1*R2*R3), which no smaller size reaches."""
+    m = 1 << log_m
+    a = ref.fr_rng(0xA5A5 + log_m, m)
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    for flags in flag_set:
+        exp, _ = ref.ntt(a, flags, g)
+        got = gpu.ntt(a.copy(), flags, g if flags & 2 else None)
+        assert np.array_equal(got, exp), (log_m, flags)
+        del exp, got
+
+
 def test_ntt_2_20_vs_libfqfft(gpu, ref):
     m = 1 << 20
     a = ref.fr_rng(123456, m)

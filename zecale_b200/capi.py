@@ -63,6 +63,9 @@ EXPORTS = {
     "zecale_gpu_msm_pinned_async": (_i, [_vp, _i, _vp, _vp, _sz, _vp, _sz, _vp, _u]),
     "zecale_gpu_qap_h_async": (_i, [_vp, _i, _vp, _vp, _vp, _u, _vp, _vp]),
     "zecale_gpu_sync": (_i, [_vp]),
+    "zecale_gpu_flush": (_i, [_vp]),
+    "zecale_gpu_host_alloc": (_vp, [_sz]),
+    "zecale_gpu_host_free": (None, [_vp]),
     "zecale_gpu_synth_bases": (_i, [_vp, _i, ctypes.c_uint64, _sz, _vp]),
     "zecale_gpu_pin_bases_bytes": (_i, [_vp, _vp, _sz, _sz, _i, _i, ctypes.POINTER(_vp)]),
     "zecale_gpu_batch_exp": (_i, [_vp, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
@@ -275,6 +278,10 @@ class Context:
 
     def sync(self):
         self._ck(_lib.zecale_gpu_sync(self._h))
+
+    def flush(self):
+        """Enqueue the deferred MSM tails of the async calls so far, without waiting."""
+        self._ck(_lib.zecale_gpu_flush(self._h))
 
     def synth_bases(self, n, group=G1, seed=0):
         out = np.zeros((n, 36), dtype=np.uint64)

@@ -1383,6 +1383,26 @@ int zecale_gpu_sync(zecale_gpu_ctx *ctx)
     return sync_lanes(ctx);
 }
 
+int zecale_gpu_flush(zecale_gpu_ctx *ctx)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    return flush_tails(ctx);
+}
+
+void *zecale_gpu_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (!bytes || cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+    return p;
+}
+
+void zecale_gpu_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
 int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t n, void *out_points)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;

@@ -23,6 +23,7 @@
 #ifndef ZECALE_GPU_HOOKS_HPP
 #define ZECALE_GPU_HOOKS_HPP
 
+#include <condition_variable>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -57,6 +58,19 @@ static_assert(sizeof(size_t) == 8, "sparse_vector indices are passed as u64");
 struct state_t {
     std::mutex mu;
     zecale_gpu_ctx *ctx = nullptr;
+    // Proof slots of the fused prover: each in-flight proof owns one context (its own lanes, streams
+    // and scratch; the pinned key images are shared) and a pinned staging buffer for its assignment.
+    // A thread that proves takes a free slot for the whole enqueue + synchronise sequence, so
+    // concurrent provers (the aggregator server's gRPC workers, aggregator_server.cpp:399-415) never
+    // interleave on a context, and prove_async() keeps several proofs in flight from one thread.
+    struct slot_t {
+        zecale_gpu_ctx *ctx = nullptr;
+        void *staging = nullptr;
+        size_t staging_bytes = 0;
+        bool busy = false;
+    };
+    std::vector<slot_t> slots;
+    std::condition_variable slot_free;
     // explicit residency registry: first-base address -> pinned image (see pin_bases below)
     struct pin_t {
         zecale_gpu_bases *handle;
@@ -182,8 +196,64 @@ inline void shutdown()
     unpin_all();
     state_t &s = state();
     std::lock_guard<std::mutex> lk(s.mu);
+    for (auto &sl : s.slots) {
+        if (sl.staging) zecale_gpu_host_free(sl.staging);
+        if (sl.ctx) zecale_gpu_shutdown(sl.ctx);
+    }
+    s.slots.clear();
     if (s.ctx) zecale_gpu_shutdown(s.ctx);
     s.ctx = nullptr;
+}
+
+/// Number of proofs the fused prover keeps in flight ($ZECALE_GPU_PIPELINE, default 3).
+inline size_t pipeline_depth()
+{
+    const char *v = std::getenv("ZECALE_GPU_PIPELINE");
+    const int d = v ? std::atoi(v) : 3;
+    return d < 1 ? 1 : (d > 8 ? 8 : (size_t)d);
+}
+
+/// Take a free proof slot (waits while all are busy); the slot's context is created on first use, on
+/// the device of the process-wide context.
+inline size_t acquire_slot(size_t staging_bytes)
+{
+    context();
+    state_t &s = state();
+    std::unique_lock<std::mutex> lk(s.mu);
+    if (s.slots.empty()) s.slots.resize(pipeline_depth());
+    size_t k = 0;
+    s.slot_free.wait(lk, [&] {
+        for (k = 0; k < s.slots.size(); k++)
+            if (!s.slots[k].busy) return true;
+        return false;
+    });
+    state_t::slot_t &sl = s.slots[k];
+    if (!sl.ctx) {
+        const char *dev = std::getenv("ZECALE_GPU_DEVICE");
+        int d = dev ? std::atoi(dev) : 0;
+        if (zecale_gpu_init(dev ? &d : nullptr, dev ? 1 : 0, &sl.ctx) != ZECALE_GPU_OK) {
+            sl.ctx = nullptr;
+            throw std::runtime_error("zecale_gpu_init failed for a proof slot");
+        }
+    }
+    if (sl.staging_bytes < staging_bytes) {
+        if (sl.staging) zecale_gpu_host_free(sl.staging);
+        sl.staging = zecale_gpu_host_alloc(staging_bytes);
+        sl.staging_bytes = sl.staging ? staging_bytes : 0;
+        if (!sl.staging) throw std::runtime_error("zecale_gpu_host_alloc failed");
+    }
+    sl.busy = true;
+    return k;
+}
+
+inline void release_slot(size_t k)
+{
+    state_t &s = state();
+    {
+        std::lock_guard<std::mutex> lk(s.mu);
+        s.slots[k].busy = false;
+    }
+    s.slot_free.notify_one();
 }
 
 /// out = sum_i scalars[index ? index[i] : i] * base(i); group 1 = G1, 2 = G2.
@@ -480,11 +550,117 @@ struct evaluations_t {
     G1 Lt;
 };
 
-/// Fused path for a key made resident with pin_proving_key: the assignment is uploaded once, the
-/// sparse mat-vecs and the seven transforms of r1cs_to_qap_witness_map run on the device, the H MSM
-/// reads coefficients_for_H from device memory, the five MSMs overlap on the context's lanes, and
-/// one synchronisation returns 5 x 288 bytes. Returns false if the key is not resident or the
-/// reference would not use the power-of-two domain for it.
+/// One proof in flight on the fused path (prove_async .. collect).
+struct ticket_t {
+    size_t slot;
+    const proving_key_t *pk;
+    size_t nnz_b;
+    libff::bw6_761_Fr r, s;
+    unsigned char pt[5][288];
+};
+
+/// Fused path for a key made resident with pin_proving_key: the assignment is staged in pinned memory
+/// and uploaded once, the sparse mat-vecs and the seven transforms of r1cs_to_qap_witness_map run on
+/// the device, the H MSM reads coefficients_for_H from device memory, the five MSMs overlap on the
+/// lanes of the proof's own context. Enqueues everything and returns a ticket (nullptr if the key is
+/// not resident or the reference would not use the power-of-two domain for it); collect_evaluations
+/// waits for the 5 x 288 result bytes and frees the slot.
+inline ticket_t *evaluate_fused_async(
+    const proving_key_t &pk,
+    const std::vector<Fr> &primary_input,
+    const std::vector<Fr> &auxiliary_input,
+    bool force_pow_2_domain)
+{
+    state_t::key_t key;
+    {
+        state_t &s = state();
+        std::lock_guard<std::mutex> lk(s.mu);
+        auto it = s.keys.find(pk.A_query.data());
+        if (it == s.keys.end()) return nullptr;
+        key = it->second;
+    }
+    const auto &cs = pk.constraint_system;
+    const size_t nv = cs.num_variables(), ni = cs.num_inputs();
+    const size_t min_n = cs.num_constraints() + ni + 1;
+    const size_t m = (size_t)1 << zecale_gpu_r1cs_log_domain(key.r1cs);
+    if (!force_pow_2_domain && min_n != m) return nullptr;
+    if (primary_input.size() != ni || primary_input.size() + auxiliary_input.size() != nv ||
+        pk.A_query.size() != nv + 1 || pk.H_query.size() != m - 1 || pk.L_query.size() != nv - ni ||
+        !key.A || !key.H || !key.L) {
+        return nullptr;
+    }
+    const size_t slot = acquire_slot((nv + 1) * sizeof(Fr));
+    std::unique_ptr<ticket_t> t(new ticket_t());
+    t->slot = slot;
+    t->pk = &pk;
+    t->nnz_b = pk.B_query.indices.size();
+    try {
+        zecale_gpu_ctx *ctx;
+        Fr *full;
+        {
+            state_t &s = state();
+            std::lock_guard<std::mutex> lk(s.mu);
+            ctx = s.slots[slot].ctx;
+            full = static_cast<Fr *>(s.slots[slot].staging);
+        }
+        // const_padded_assignment of the reference (r1cs_gg_ppzksnark.tcc:523-528), in pinned memory
+        const Fr one = Fr::one();
+        std::memcpy(static_cast<void *>(full), static_cast<const void *>(&one), sizeof(Fr));
+        if (ni) std::memcpy(static_cast<void *>(full + 1), static_cast<const void *>(primary_input.data()), ni * sizeof(Fr));
+        if (nv > ni)
+            std::memcpy(static_cast<void *>(full + 1 + ni), static_cast<const void *>(auxiliary_input.data()), (nv - ni) * sizeof(Fr));
+        const Fr g = Fr::multiplicative_generator; // the coset of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:270)
+        auto ck = [&](int rc, const char *what) {
+            if (rc != ZECALE_GPU_OK) throw std::runtime_error(std::string(what) + ": " + zecale_gpu_last_error(ctx));
+        };
+        ck(zecale_gpu_qap_h_from_witness_async(ctx, 0, key.r1cs, full, &g, nullptr, 0), "zecale_gpu_qap_h_from_witness_async");
+        ck(zecale_gpu_msm_pinned_async(ctx, 1, key.A, full, sizeof(Fr), nullptr, nv + 1, t->pt[0], 0), "msm A");
+        ck(zecale_gpu_msm_pinned_async(ctx, 4, key.L, full + ni + 1, sizeof(Fr), nullptr, nv - ni, t->pt[4], 0), "msm L");
+        if (t->nnz_b) {
+            ck(zecale_gpu_msm_pinned_async(ctx, 2, key.B2, full, sizeof(Fr), pk.B_query.indices.data(), t->nnz_b, t->pt[1], 0), "msm B (G2)");
+            ck(zecale_gpu_msm_pinned_async(ctx, 3, key.B1, full, sizeof(Fr), pk.B_query.indices.data(), t->nnz_b, t->pt[2], 0), "msm B (G1)");
+        }
+        ck(zecale_gpu_msm_pinned_async(ctx, 0, key.H, nullptr, sizeof(Fr), nullptr, m - 1, t->pt[3], ZECALE_GPU_SCALARS_FROM_QAP), "msm H");
+        ck(zecale_gpu_flush(ctx), "zecale_gpu_flush");
+    } catch (...) {
+        zecale_gpu_ctx *ctx = nullptr;
+        {
+            state_t &s = state();
+            std::lock_guard<std::mutex> lk(s.mu);
+            ctx = s.slots[slot].ctx;
+        }
+        if (ctx) zecale_gpu_sync(ctx);
+        release_slot(slot);
+        throw;
+    }
+    return t.release();
+}
+
+inline void collect_evaluations(ticket_t *ticket, evaluations_t &out)
+{
+    std::unique_ptr<ticket_t> t(ticket);
+    zecale_gpu_ctx *ctx;
+    {
+        state_t &s = state();
+        std::lock_guard<std::mutex> lk(s.mu);
+        ctx = s.slots[t->slot].ctx;
+    }
+    const int rc = zecale_gpu_sync(ctx);
+    const std::string err = rc == ZECALE_GPU_OK ? std::string() : std::string(zecale_gpu_last_error(ctx));
+    release_slot(t->slot);
+    if (rc != ZECALE_GPU_OK) throw std::runtime_error("zecale_gpu_sync: " + err);
+    std::memcpy(static_cast<void *>(&out.At), t->pt[0], 288);
+    if (t->nnz_b) {
+        std::memcpy(static_cast<void *>(&out.Bt_g), t->pt[1], 288);
+        std::memcpy(static_cast<void *>(&out.Bt_h), t->pt[2], 288);
+    } else {
+        out.Bt_g = G2::zero();
+        out.Bt_h = G1::zero();
+    }
+    std::memcpy(static_cast<void *>(&out.Ht), t->pt[3], 288);
+    std::memcpy(static_cast<void *>(&out.Lt), t->pt[4], 288);
+}
+
 inline bool evaluate_fused(
     const proving_key_t &pk,
     const std::vector<Fr> &primary_input,
@@ -492,53 +668,9 @@ inline bool evaluate_fused(
     bool force_pow_2_domain,
     evaluations_t &out)
 {
-    state_t::key_t key;
-    {
-        state_t &s = state();
-        std::lock_guard<std::mutex> lk(s.mu);
-        auto it = s.keys.find(pk.A_query.data());
-        if (it == s.keys.end()) return false;
-        key = it->second;
-    }
-    const auto &cs = pk.constraint_system;
-    const size_t nv = cs.num_variables(), ni = cs.num_inputs();
-    const size_t min_n = cs.num_constraints() + ni + 1;
-    const size_t m = (size_t)1 << zecale_gpu_r1cs_log_domain(key.r1cs);
-    if (!force_pow_2_domain && min_n != m) return false;
-    if (primary_input.size() != ni || primary_input.size() + auxiliary_input.size() != nv ||
-        pk.A_query.size() != nv + 1 || pk.H_query.size() != m - 1 || pk.L_query.size() != nv - ni ||
-        !key.A || !key.H || !key.L) {
-        return false;
-    }
-    zecale_gpu_ctx *ctx = context();
-    // const_padded_assignment of the reference (r1cs_gg_ppzksnark.tcc:523-528)
-    std::vector<Fr> full;
-    full.reserve(nv + 1);
-    full.push_back(Fr::one());
-    full.insert(full.end(), primary_input.begin(), primary_input.end());
-    full.insert(full.end(), auxiliary_input.begin(), auxiliary_input.end());
-    const Fr g = Fr::multiplicative_generator; // the coset of r1cs_to_qap_witness_map (r1cs_to_qap.tcc:270)
-    unsigned char pt[5][288];
-    const size_t nnz_b = pk.B_query.indices.size();
-    check(zecale_gpu_qap_h_from_witness_async(ctx, 0, key.r1cs, full.data(), &g, nullptr, 0), "zecale_gpu_qap_h_from_witness_async");
-    check(zecale_gpu_msm_pinned_async(ctx, 1, key.A, full.data(), sizeof(Fr), nullptr, nv + 1, pt[0], 0), "msm A");
-    if (nnz_b) {
-        check(zecale_gpu_msm_pinned_async(ctx, 2, key.B2, full.data(), sizeof(Fr), pk.B_query.indices.data(), nnz_b, pt[1], 0), "msm B (G2)");
-        check(zecale_gpu_msm_pinned_async(ctx, 3, key.B1, full.data(), sizeof(Fr), pk.B_query.indices.data(), nnz_b, pt[2], 0), "msm B (G1)");
-    }
-    check(zecale_gpu_msm_pinned_async(ctx, 4, key.L, full.data() + ni + 1, sizeof(Fr), nullptr, nv - ni, pt[4], 0), "msm L");
-    check(zecale_gpu_msm_pinned_async(ctx, 0, key.H, nullptr, sizeof(Fr), nullptr, m - 1, pt[3], ZECALE_GPU_SCALARS_FROM_QAP), "msm H");
-    check(zecale_gpu_sync(ctx), "zecale_gpu_sync");
-    std::memcpy(static_cast<void *>(&out.At), pt[0], 288);
-    if (nnz_b) {
-        std::memcpy(static_cast<void *>(&out.Bt_g), pt[1], 288);
-        std::memcpy(static_cast<void *>(&out.Bt_h), pt[2], 288);
-    } else {
-        out.Bt_g = G2::zero();
-        out.Bt_h = G1::zero();
-    }
-    std::memcpy(static_cast<void *>(&out.Ht), pt[3], 288);
-    std::memcpy(static_cast<void *>(&out.Lt), pt[4], 288);
+    ticket_t *t = evaluate_fused_async(pk, primary_input, auxiliary_input, force_pow_2_domain);
+    if (!t) return false;
+    collect_evaluations(t, out);
     return true;
 }
 
@@ -571,9 +703,19 @@ inline void evaluate_sequential(
         pk.L_query.begin(), pk.L_query.end(), padded.begin() + qap_wit.num_inputs() + 1, padded.begin() + nv + 1, 1);
 }
 
+/// Proof assembly: the reference's formulae (r1cs_gg_ppzksnark.tcc:582-599) on its own CPU group arithmetic.
+inline proof_t assemble(const proving_key_t &pk, const evaluations_t &e, const Fr &r, const Fr &s)
+{
+    G1 g1_A = pk.alpha_g1 + e.At + r * pk.delta_g1;
+    G1 g1_B = pk.beta_g1 + e.Bt_h + s * pk.delta_g1;
+    G2 g2_B = pk.beta_g2 + e.Bt_g + s * pk.delta_g2;
+    G1 g1_C = e.Ht + e.Lt + s * g1_A + r * g1_B - (r * s) * pk.delta_g1;
+    return proof_t(std::move(g1_A), std::move(g2_B), std::move(g1_C));
+}
+
 /// r1cs_gg_ppzksnark_prover with the prover randomness as parameters (the reference samples r, s
-/// from std::random_device, r1cs_gg_ppzksnark.tcc:502-503); assembly is the reference's formulae
-/// (:582-599) on its own CPU group arithmetic.
+/// from std::random_device, r1cs_gg_ppzksnark.tcc:502-503). Safe to call from several threads: each
+/// call owns a proof slot until its results are back.
 inline proof_t prove_with_rs(
     const proving_key_t &pk,
     const std::vector<Fr> &primary_input,
@@ -588,11 +730,37 @@ inline proof_t prove_with_rs(
         evaluate_sequential(pk, primary_input, auxiliary_input, force_pow_2_domain, e);
     }
     if (evaluations_out) *evaluations_out = e;
-    G1 g1_A = pk.alpha_g1 + e.At + r * pk.delta_g1;
-    G1 g1_B = pk.beta_g1 + e.Bt_h + s * pk.delta_g1;
-    G2 g2_B = pk.beta_g2 + e.Bt_g + s * pk.delta_g2;
-    G1 g1_C = e.Ht + e.Lt + s * g1_A + r * g1_B - (r * s) * pk.delta_g1;
-    return proof_t(std::move(g1_A), std::move(g2_B), std::move(g1_C));
+    return assemble(pk, e, r, s);
+}
+
+/// Pipelined use of the fused prover from one thread: prove_async enqueues a proof on a free slot and
+/// returns at once (nullptr if the key is not resident: use prove_with_rs), collect waits for it and
+/// assembles. Up to pipeline_depth() proofs are in flight; the host-side assembly of proof i overlaps
+/// the device work of proof i+1. pk must outlive the ticket.
+inline ticket_t *prove_async(
+    const proving_key_t &pk,
+    const std::vector<Fr> &primary_input,
+    const std::vector<Fr> &auxiliary_input,
+    bool force_pow_2_domain,
+    const Fr &r,
+    const Fr &s)
+{
+    ticket_t *t = evaluate_fused_async(pk, primary_input, auxiliary_input, force_pow_2_domain);
+    if (t) {
+        t->r = r;
+        t->s = s;
+    }
+    return t;
+}
+
+inline proof_t collect(ticket_t *t, evaluations_t *evaluations_out = nullptr)
+{
+    const proving_key_t &pk = *t->pk;
+    const Fr r = t->r, s = t->s;
+    evaluations_t e;
+    collect_evaluations(t, e);
+    if (evaluations_out) *evaluations_out = e;
+    return assemble(pk, e, r, s);
 }
 
 } // namespace zecale_gpu_hooks
