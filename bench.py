@@ -535,9 +535,99 @@ def run_b200(args, rank, world, local_rank):
             "msm_g1_2e20": msm20,
         }
     wl.close()
+    del wl
+    torch.cuda.empty_cache()
+    # ---- config 5 (strong scaling of one proof): rank 0 drives all N GPUs through one multi-device
+    # context (the drop-in is a single-process prover); the other ranks have released their GPUs and wait
+    if not args.skip_sharded:
+        if world > 1:
+            cpu_group = dist.new_group(backend="gloo")
+            dist.barrier(group=cpu_group)
+        if rank == 0:
+            try:
+                out["sharded"] = sharded_block(args, world, list(range(world)))
+            except Exception as e:  # noqa: BLE001 - the headline line must still be printed
+                out["sharded"] = {"error": repr(e)}
+        if world > 1:
+            dist.barrier(group=cpu_group)
     if world > 1:
         dist.destroy_process_group()
     return out
+
+
+# ---- BASELINE config 5: ONE batch-32-shaped proof, MSM points sharded over the GPUs (strong scaling) ----
+B32 = {"log_m": 20, "n_vars": 920960, "n_inputs": 34, "n_b": 329934, "n_constraints": 920718,
+       "nnz": (1720900, 1923000, 3398900)}   # sizes of the real batch-32 aggregator circuit (tests/test_hooks_gpu.py prints them)
+
+
+def sharded_block(args, world, devices):
+    """One proof of the batch-32 shape at a time on a multi-device context spanning `devices` (zecale_gpu_init
+    with n_devices = N): every pinned query is sharded by points, each device runs a Pippenger per shard, the
+    384-byte partial sums are peer-copied to devices[0] and combined there; the witness map runs on devices[0]
+    and the H coefficients are sliced out to the other devices over NVLink. Host-pointer calls (pinned host
+    assignment), exactly what the hooked prover issues. Returns ms per proof and a digest of the five points
+    (identical at every N: same seeded statement)."""
+    import hashlib
+    import torch
+    import zecale_b200 as z
+    global LOG_M, N_VARS, N_INPUTS, N_A, N_B, N_H, N_L, N_CONSTRAINTS, NNZ
+    saved = (LOG_M, N_VARS, N_INPUTS, N_A, N_B, N_H, N_L, N_CONSTRAINTS, NNZ)
+    LOG_M, N_VARS, N_INPUTS, N_B, N_CONSTRAINTS, NNZ = (B32["log_m"], B32["n_vars"], B32["n_inputs"], B32["n_b"],
+                                                       B32["n_constraints"], B32["nnz"])
+    N_A, N_H, N_L = N_VARS + 1, (1 << LOG_M) - 1, N_VARS - N_INPUTS
+    try:
+        torch.cuda.set_device(devices[0])
+        st = Statement(32)
+        gen = z.Context(devices[0])                 # bases are generated once on one device ...
+        ctx = z.Context(devices if len(devices) > 1 else devices[0])   # ... and pinned through the (multi-device) context
+        pk = {}
+        t0 = time.perf_counter()
+        for name, n, grp, sd in (("A", N_A, z.G1, 311), ("B1", N_B, z.G1, 312), ("B2", N_B, z.G2, 313),
+                                 ("H", N_H, z.G1, 314), ("L", N_L, z.G1, 315)):
+            pts = gen.synth_bases(n, grp, seed=sd)
+            pk[name] = ctx.pin_bases(pts, grp)
+            del pts
+        gen.close()
+        t_pin = time.perf_counter() - t0
+        t_w = torch.from_numpy(st.w.view(np.int64)).pin_memory()
+        h_w = t_w.numpy().view(np.uint64)
+        r1cs = ctx.r1cs_load(N_CONSTRAINTS, N_INPUTS, N_VARS, st.csr)
+        assert ctx.r1cs_log_domain(r1cs) == LOG_M
+
+        def prove():
+            out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
+            ctx.qap_h_from_witness_async(0, r1cs, h_w, st.g)
+            ctx.msm_pinned_async(1, pk["A"], h_w, out[0], n=N_A)
+            ctx.msm_pinned_async(2, pk["L"], h_w[N_INPUTS + 1:], out[4], n=N_L)
+            ctx.msm_pinned_async(3, pk["B2"], h_w, out[1], n=N_B, index=st.b_index)
+            ctx.msm_pinned_async(4, pk["B1"], h_w, out[2], n=N_B, index=st.b_index)
+            ctx.msm_pinned_async(0, pk["H"], None, out[3], n=N_H, from_qap=True)
+            ctx.sync()
+            return out
+
+        for _ in range(3):
+            out = prove()
+        for d in devices:
+            torch.cuda.synchronize(d)
+        steps = max(3, min(args.steps, 8))
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            out = prove()
+        for d in devices:
+            torch.cuda.synchronize(d)
+        ms = (time.perf_counter() - t0) * 1e3 / steps
+        digest = hashlib.sha256(b"".join(o.tobytes() for o in out)).hexdigest()[:16]
+        for p_ in pk.values():
+            p_.release()
+        ctx.r1cs_free(r1cs)
+        ctx.close()
+        return {"workload": "ONE batch-32-shaped aggregator proof (m=2^20; MSM A %d / B %d x2 / H %d / L %d), MSM points sharded over the "
+                            "GPUs of a multi-device context, partial sums combined by peer copies; host-pointer C ABI, one proof in flight"
+                            % (N_A, N_B, N_H, N_L),
+                "n_gpus": len(devices), "ms_per_proof": ms, "proofs_per_s": 1e3 / ms, "scaling": "strong", "steps": steps,
+                "key_pin_s": t_pin, "digest": digest}
+    finally:
+        LOG_M, N_VARS, N_INPUTS, N_A, N_B, N_H, N_L, N_CONSTRAINTS, NNZ = saved
 
 
 class ReferenceWorkload:
@@ -640,6 +730,7 @@ def main():
     ap.add_argument("--depth", type=int, default=3, help="proofs kept in flight per GPU (1 = strictly one at a time)")
     ap.add_argument("--skip-msm20", action="store_true")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-sharded", action="store_true", help="skip the config-5 block (one batch-32-shaped proof sharded over the GPUs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -64,9 +64,19 @@ enum { ZECALE_GPU_G1 = 1, ZECALE_GPU_G2 = 2 };
 
 /* ---- lifetime ------------------------------------------------------------------ */
 
-/* Create a context bound to devices[0] (multi-device contexts shard MSMs over all
- * listed devices). devices == NULL means {current device}. */
+/* Create a context. devices == NULL means {current device}.
+ * n_devices == 1: everything runs on that device.
+ * n_devices > 1 (distinct devices of one node, at most 16): a multi-device context. Pinned base
+ * vectors are sharded by points over the listed devices - the chunks of libff::multi_exp
+ * (multiexp.tcc:663-676), the first device taking a slightly smaller one because it also runs the
+ * witness map - and every zecale_gpu_msm_pinned / _pinned_async call runs one Pippenger per shard,
+ * concurrently, the 384-byte partial sums travelling to devices[0] by peer copies (NVLink) where they
+ * are summed and normalised; coefficients_for_H go the other way, one slice per device. The transforms,
+ * the sparse mat-vecs and the un-pinned entry points run on devices[0]. The host API is unchanged, so
+ * the hooked reference prover gains the extra devices by listing them ($ZECALE_GPU_DEVICES). */
 int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **ctx);
+/* Number of devices the context spans. */
+int zecale_gpu_device_count(zecale_gpu_ctx *ctx);
 void zecale_gpu_shutdown(zecale_gpu_ctx *ctx);
 const char *zecale_gpu_last_error(zecale_gpu_ctx *ctx);
 

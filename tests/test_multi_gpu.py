@@ -1,0 +1,85 @@
+"""Multi-device contexts (zecale_gpu_init with n_devices > 1): pinned MSMs sharded by points over the
+devices - libff::multi_exp's chunks (multiexp.tcc:663-685) - must give the reference's normalised point,
+through the blocking entry point and through the prover-shaped asynchronous lanes (witness map on
+devices[0], H coefficients sliced out to the other devices). Needs >= 2 GPUs: skipped on a one-GPU box,
+run with `gpurun --gpus 2`."""
+import numpy as np
+import pytest
+
+import bw6_constants as C
+
+pytestmark = pytest.mark.gpu
+
+
+def _device_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.fixture(scope="module")
+def multi():
+    import zecale_b200 as z
+    n = _device_count()
+    if n < 2:
+        pytest.skip("needs at least two GPUs")
+    ctx = z.Context(list(range(min(n, 8))))
+    assert ctx.device_count() == min(n, 8)
+    yield ctx
+    ctx.close()
+
+
+@pytest.mark.parametrize("group", [1, 2])
+def test_sharded_msm_vs_libff(multi, ref, group):
+    n = 1 << 14
+    bases = ref.bases_seq(n, group)
+    scalars = ref.fr_rng(77 + group, n)
+    scalars[5] = 0
+    scalars[6] = ref.fr_from_ints([1])[0]
+    exp, _ = ref.msm(bases, scalars, group)
+    pin = multi.pin_bases(bases, group)
+    try:
+        assert np.array_equal(multi.msm_pinned(pin, scalars), exp)
+        for k in (1, 3, 1000, n - 1):   # prefixes: shards beyond the prefix contribute nothing
+            e2, _ = ref.msm(bases[:k], scalars[:k], group)
+            assert np.array_equal(multi.msm_pinned(pin, scalars, n=k), e2), k
+        idx = np.sort(np.random.default_rng(3).choice(n, 5000, replace=False)).astype(np.uint64)
+        e3, _ = ref.msm(bases[:5000], np.ascontiguousarray(scalars[idx]), group)
+        assert np.array_equal(multi.msm_pinned(pin, scalars, index=idx, n=5000), e3)
+    finally:
+        pin.release()
+
+
+def test_sharded_prover_lanes(multi, ref):
+    """The fused prover's calls on a multi-device context: identical to libff / libfqfft."""
+    m, n = 1 << 12, 3000
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    assert ref.session_synthetic(3000, 10, 400, 5) == 0
+    ref.session_setup(4)
+    zs = ref.session_export()
+    nv, ni, mm = zs["num_variables"], zs["num_inputs"], zs["m"]
+    w = zs["assignment"]
+    r1cs = multi.r1cs_load(zs["num_constraints"], ni, nv, [zs["csr_a"], zs["csr_b"], zs["csr_c"]])
+    pa, ph, pl = multi.pin_bases(zs["A_query"]), multi.pin_bases(zs["H_query"]), multi.pin_bases(zs["L_query"])
+    pb2 = multi.pin_bases(zs["B_values"], 2)
+    pb1 = multi.pin_bases(zs["B_values"], 1, base_offset_bytes=288)
+    try:
+        r, s = ref.fr_rng(1, 1)[0], ref.fr_rng(2, 1)[0]
+        exp = ref.session_prove(r, s)
+        for _ in range(2):
+            out = [np.zeros(36, dtype=np.uint64) for _ in range(5)]
+            h_out = np.zeros((mm + 1, 6), dtype=np.uint64)
+            multi.qap_h_from_witness_async(0, r1cs, w, g, out=h_out)
+            multi.msm_pinned_async(1, pa, w, out[0])
+            multi.msm_pinned_async(2, pl, w[ni + 1:], out[4])
+            multi.msm_pinned_async(3, pb2, w, out[1], index=zs["B_indices"])
+            multi.msm_pinned_async(4, pb1, w, out[2], index=zs["B_indices"])
+            multi.msm_pinned_async(0, ph, None, out[3], n=mm - 1, from_qap=True)
+            multi.flush()
+            multi.sync()
+            assert np.array_equal(h_out, exp["h"])
+            for k in range(5):
+                assert np.array_equal(out[k], exp["msm5"][k]), k
+    finally:
+        for p in (pa, ph, pl, pb2, pb1):
+            p.release()
+        multi.r1cs_free(r1cs)

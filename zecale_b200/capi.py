@@ -36,6 +36,7 @@ G2 = 2
 
 EXPORTS = {
     "zecale_gpu_init": (_i, [ctypes.POINTER(_i), _i, ctypes.POINTER(_vp)]),
+    "zecale_gpu_device_count": (_i, [_vp]),
     "zecale_gpu_shutdown": (None, [_vp]),
     "zecale_gpu_last_error": (ctypes.c_char_p, [_vp]),
     "zecale_gpu_msm_g1": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp]),
@@ -113,15 +114,20 @@ class Context:
     """One zecale_gpu_ctx (one device, one stream)."""
 
     def __init__(self, device=None):
+        """device: None (current), an int, or a list of ints (multi-device context: pinned MSMs are sharded)."""
         h = ctypes.c_void_p()
         if device is None:
             rc = _lib.zecale_gpu_init(None, 0, ctypes.byref(h))
         else:
-            arr = (ctypes.c_int * 1)(device)
-            rc = _lib.zecale_gpu_init(arr, 1, ctypes.byref(h))
+            devs = list(device) if isinstance(device, (list, tuple)) else [device]
+            arr = (ctypes.c_int * len(devs))(*devs)
+            rc = _lib.zecale_gpu_init(arr, len(devs), ctypes.byref(h))
         if rc != 0:
             raise ZecaleGpuError(rc, "zecale_gpu_init failed (no usable sm_100 device?)")
         self._h = h
+
+    def device_count(self):
+        return int(_lib.zecale_gpu_device_count(self._h))
 
     def close(self):
         if self._h is not None:

@@ -859,10 +859,11 @@ struct TailJob {
     const uint32_t *heavy_count; // ... and how many
     XYZZ *partial;
     XYZZ *lvl[2];                // level-k buffer = lvl[k & 1]: [X_k | Y_0 | ... | Y_{k-1}]
-    XYZZ *fin;                   // V * c scaled terms
-    Proj *result;
+    XYZZ *fin;                   // n_fin terms to sum (V * c scaled terms of one MSM, or the per-device partial sums of a sharded one)
+    Proj *result;                // nullptr: leave the un-normalised sum in fin[0] (a shard of a multi-device MSM)
     uint32_t cm1;                // c - 1 = log2(NB)
     uint32_t V;
+    uint32_t n_fin;
 };
 
 struct TailBatch {
@@ -1000,7 +1001,7 @@ __global__ void __launch_bounds__(128, 3) k_tail_scale(TailBatch tb)
 __global__ void __launch_bounds__(128, 1) k_tail_sum(TailBatch tb)
 {
     const TailJob &J = tb.job[blockIdx.x];
-    const uint32_t n = J.V * (J.cm1 + 1);
+    const uint32_t n = J.n_fin;
     for (uint32_t step = 1; step < n; step <<= 1) {
         const uint32_t n_pairs = (n - step + 2 * step - 1) / (2 * step);
         for (uint32_t q = threadIdx.x; q < n_pairs; q += blockDim.x) {
@@ -1023,9 +1024,10 @@ __global__ void __launch_bounds__(32, 1) k_tail_norm(TailBatch tb)
 {
     if (threadIdx.x >= tb.n_jobs) return;
     const TailJob &J = tb.job[threadIdx.x];
+    Proj *out = J.result;
+    if (!out) return;
     FqSlots S;
     vs_load_acc(S, J.fin);
-    Proj *out = J.result;
     fqvm_run(S, VPC_TOAFF, [&](uint32_t id, uint32_t &, FqSlots &S_) {
         vs_one(S_, VS_T0);
         if (id == 2) { // infinity: (0, one, 0)
@@ -1390,7 +1392,20 @@ inline TailJob msm_tail_job(const MsmPlan &p, const MsmBuffers &b)
     j.result = b.result;
     j.cm1 = p.c - 1;
     j.V = p.V;
+    j.n_fin = p.V * p.c;
     return j;
+}
+
+// Last two steps only (sum n_fin terms, normalise): combines the per-device partial sums of sharded MSMs.
+inline cudaError_t msm_launch_gather_batch(const TailJob *jobs, uint32_t n_jobs, cudaStream_t st)
+{
+    if (n_jobs == 0 || n_jobs > TAIL_MAX_JOBS) return cudaErrorInvalidValue;
+    TailBatch tb{};
+    tb.n_jobs = n_jobs;
+    for (uint32_t i = 0; i < n_jobs; i++) tb.job[i] = jobs[i];
+    k_tail_sum<<<n_jobs, 128, 0, st>>>(tb);
+    k_tail_norm<<<1, 32, 0, st>>>(tb);
+    return cudaGetLastError();
 }
 
 inline cudaError_t msm_launch_tail_batch(const TailJob *jobs, uint32_t n_jobs, cudaStream_t st, uint64_t *n_launches = nullptr)

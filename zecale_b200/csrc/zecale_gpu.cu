@@ -28,6 +28,10 @@ struct zecale_gpu_bases {
     size_t n = 0;
     int group = 0;
     uint32_t c = 0, V = 0;    // window bits / bucket sets the image was expanded for (V = 0: not expanded)
+    // multi-device context: the points are sharded by libff::multi_exp's chunk arithmetic
+    // (multiexp.tcc:663-676); shard g = bases [lo[g], lo[g+1]) pinned on worker g (nullptr if empty)
+    std::vector<zecale_gpu_bases *> shards;
+    std::vector<size_t> lo;
 };
 
 // Device image of an R1CS (three CSR matrices over Fr), loaded once per circuit.
@@ -70,6 +74,11 @@ struct Lane {
     MsmPlan tail_plan{};
     MsmBuffers tail_buf{};
     cudaEvent_t ev_acc = nullptr; // bucket accumulation of the pending MSM finished
+    // shard of a multi-device MSM: the un-normalised partial sum (XYZZ) is copied to this address on
+    // device partial_dev instead of being normalised and sent to the host
+    XYZZ *partial_dst = nullptr;
+    int partial_dev = 0;
+    bool busy = false;            // an asynchronous MSM of this lane has not been synchronised yet
 };
 
 struct zecale_gpu_ctx {
@@ -105,6 +114,21 @@ struct zecale_gpu_ctx {
     // accumulations for SM space they finish ten times later.
     cudaEvent_t ev_qap = nullptr;
     bool qap_in_epoch = false;
+    // Multi-device context (zecale_gpu_init with n_devices > 1): this object coordinates and owns the
+    // witness map on devices[0]; workers[g] is a complete single-device context on devices[g] (g = 0
+    // shares the first device) that runs shard g of every pinned MSM. The partial sums (384 B each) are
+    // peer-copied into d_gather on devices[0], summed and normalised there (msm_launch_gather_batch).
+    std::vector<zecale_gpu_ctx *> workers;
+    static constexpr int MAX_DEVICES = 16;
+    XYZZ *d_gather = nullptr;        // [lane][MAX_DEVICES]
+    Proj *d_gather_res = nullptr;    // [lane]
+    cudaStream_t gstream = nullptr;  // high priority, devices[0]
+    cudaEvent_t ev_gdone = nullptr;
+    cudaEvent_t ev_parts = nullptr;  // (worker) partial sums of the last flush have been sent
+    struct Gather {
+        bool pending = false, flushed = false;
+        uint32_t n_parts = 0;
+    } gather[ZECALE_GPU_LANES];
     // ZECALE_GPU_TRACE=1: phase timestamps of every lane, printed to stderr at each sync
     bool trace = false;
     struct TraceMark {
@@ -179,6 +203,7 @@ int flush_tails(zecale_gpu_ctx *ctx)
     for (Lane &L : ctx->lanes)
         if (L.tail_pending) {
             jobs[n] = msm_tail_job(L.tail_plan, L.tail_buf);
+            if (L.partial_dst) jobs[n].result = nullptr; // a shard: leave the XYZZ sum in fin[0]
             owner[n++] = &L;
         }
     if (n == 0) return 0;
@@ -190,8 +215,18 @@ int flush_tails(zecale_gpu_ctx *ctx)
     uint64_t nl = 0;
     CK(msm_launch_tail_batch(jobs, n, F.hi, &nl));
     ctx->launches += nl;
-    for (uint32_t i = 0; i < n; i++)
-        CK(cudaMemcpyAsync(&owner[i]->h->result, owner[i]->tail_buf.result, sizeof(Proj), cudaMemcpyDeviceToHost, F.hi));
+    bool sent = false;
+    for (uint32_t i = 0; i < n; i++) {
+        Lane &L = *owner[i];
+        if (L.partial_dst) {
+            CK(cudaMemcpyPeerAsync(L.partial_dst, L.partial_dev, L.tail_buf.fin, ctx->device, sizeof(XYZZ), F.hi));
+            L.partial_dst = nullptr;
+            sent = true;
+        } else {
+            CK(cudaMemcpyAsync(&L.h->result, L.tail_buf.result, sizeof(Proj), cudaMemcpyDeviceToHost, F.hi));
+        }
+    }
+    if (sent) CK(cudaEventRecord(ctx->ev_parts, F.hi));
     CK(cudaEventRecord(F.ev_back, F.hi));
     for (uint32_t i = 0; i < n; i++) CK(cudaStreamWaitEvent(owner[i]->stream, F.ev_back, 0));
     trace_mark(ctx, "tail1", F.stream, lane);
@@ -228,6 +263,7 @@ int sync_lanes(zecale_gpu_ctx *ctx)
         cudaError_t e = cudaStreamSynchronize(L.stream);
         if (e != cudaSuccess && rc == 0)
             rc = fail(ctx, ZECALE_GPU_E_CUDA, "stream synchronize: %s", cudaGetErrorString(e));
+        L.busy = false;
         if (L.user_out) {
             if (e == cudaSuccess) {
                 memcpy(L.user_out, &L.h->result, sizeof(Proj));
@@ -311,7 +347,7 @@ int import_bases_bytes(zecale_gpu_ctx *ctx, const void *bytes, size_t stride, si
 // d_bases: affine image on device; scalars: device pointer. Result -> host out (288 B).
 int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf, uint32_t c, uint32_t V,
                uint32_t copy_stride, const uint8_t *d_scalars, size_t sstride, const uint64_t *d_index, size_t n,
-               void *out_point, float *elapsed_ms, bool nosync = false)
+               void *out_point, float *elapsed_ms, bool nosync = false, XYZZ *partial_dst = nullptr, int partial_dev = 0)
 {
     if (n == 0) {
         // empty sum = zero point (0, one, 0), as libff::multi_exp returns GroupT::zero()
@@ -322,7 +358,7 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
         if (elapsed_ms) *elapsed_ms = 0.f;
         return 0;
     }
-    if (ctx->cur->user_out) { // an asynchronous result of this lane is still undelivered
+    if (ctx->cur->user_out || ctx->cur->busy) { // an asynchronous MSM of this lane is still in flight
         int rc0 = sync_lanes(ctx);
         if (rc0) return rc0;
     }
@@ -351,6 +387,8 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
         L.tail_pending = true;
         L.tail_plan = plan;
         L.tail_buf = b;
+        L.partial_dst = partial_dst;
+        L.partial_dev = partial_dev;
     } else {
         TailJob job = msm_tail_job(plan, b);
         uint64_t nl = 0;
@@ -361,6 +399,7 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
     }
     L.last_plan = plan;
     L.user_out = out_point;
+    L.busy = nosync;
     if (nosync) return 0;
     CK(cudaStreamSynchronize(L.stream));
     memcpy(out_point, &L.h->result, sizeof(Proj));
@@ -739,6 +778,216 @@ void launch_group(int op, const Proj *a, const Proj *b, Proj *o, size_t n, cudaS
     k_test_group<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(op, a, b, o, n);
 }
 
+// Device copy of the host byte range [host, host+bytes) for the current lane: reuses an upload
+// made earlier in this epoch (any lane) if it covers the range, else uploads on this lane.
+int epoch_upload(zecale_gpu_ctx *ctx, const void *host, size_t bytes, const uint8_t **d_out)
+{
+    const char *h = (const char *)host;
+    for (auto &u : ctx->uploads)
+        if (h >= u.host && h + bytes <= u.host + u.bytes) {
+            CK(cudaStreamWaitEvent(ctx->cur->stream, u.ev, 0));
+            *d_out = (const uint8_t *)ctx->up_pool[u.buf].p + (h - u.host);
+            return 0;
+        }
+    if (ctx->uploads.size() >= 8) return 1; // pool exhausted: caller falls back to a lane-private upload
+    int slot = (int)ctx->uploads.size();
+    int rc = reserve(ctx, ctx->up_pool[slot], bytes);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(ctx->up_pool[slot].p, host, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
+    cudaEvent_t ev = take_event(ctx);
+    CK(cudaEventRecord(ev, ctx->cur->stream));
+    ctx->uploads.push_back({h, bytes, slot, ev});
+    *d_out = (const uint8_t *)ctx->up_pool[slot].p;
+    return 0;
+}
+
+
+// ------------------------------------------------------------------ multi-device contexts
+struct DevGuard { // cudaSetDevice for the scope of a call into a worker
+    int prev = 0;
+    explicit DevGuard(int dev)
+    {
+        cudaGetDevice(&prev);
+        cudaSetDevice(dev);
+    }
+    ~DevGuard() { cudaSetDevice(prev); }
+};
+
+bool is_multi(const zecale_gpu_ctx *ctx) { return !ctx->workers.empty(); }
+
+// Shard g of n points over G workers: libff::multi_exp's equal chunks (multiexp.tcc:663-676), except
+// that the first worker - whose device also runs the witness map of every proof - takes `w0` of an
+// equal share ($ZECALE_GPU_SHARD0_WEIGHT, default 1 - 0.05 (G - 1)).
+void shard_bounds(size_t n, size_t G, std::vector<size_t> &lo)
+{
+    lo.assign(G + 1, n);
+    lo[0] = 0;
+    if (n < G || G == 1) return; // too few points: the first worker takes them all
+    const char *e = getenv("ZECALE_GPU_SHARD0_WEIGHT");
+    double w0 = e ? atof(e) : 1.0 - 0.05 * (double)(G - 1);
+    if (w0 < 0.05) w0 = 0.05;
+    if (w0 > 1.0) w0 = 1.0;
+    const double one = (double)n / (w0 + (double)(G - 1));
+    for (size_t g = 1; g < G; g++) lo[g] = (size_t)(one * (w0 + (double)(g - 1)));
+}
+
+// Second halves of the workers' pending shard MSMs, then (once per epoch) the gather on devices[0]:
+// sum of the partial sums of every sharded MSM, normalisation, results to the lanes' staging areas.
+int multi_flush(zecale_gpu_ctx *ctx)
+{
+    for (zecale_gpu_ctx *w : ctx->workers) {
+        DevGuard dg(w->device);
+        int rc = flush_tails(w);
+        if (rc) return fail(ctx, rc, "worker on device %d: %s", w->device, w->err.c_str());
+    }
+    TailJob jobs[ZECALE_GPU_LANES];
+    int lanes[ZECALE_GPU_LANES];
+    uint32_t n = 0;
+    for (int l = 0; l < ZECALE_GPU_LANES; l++) {
+        auto &g = ctx->gather[l];
+        if (!g.pending || g.flushed) continue;
+        g.flushed = true;
+        TailJob j{};
+        j.fin = ctx->d_gather + (size_t)l * zecale_gpu_ctx::MAX_DEVICES;
+        j.n_fin = g.n_parts;
+        j.result = ctx->d_gather_res + l;
+        jobs[n] = j;
+        lanes[n++] = l;
+    }
+    if (n == 0) return 0;
+    for (zecale_gpu_ctx *w : ctx->workers) CK(cudaStreamWaitEvent(ctx->gstream, w->ev_parts, 0));
+    CK(msm_launch_gather_batch(jobs, n, ctx->gstream));
+    ctx->launches += 2;
+    for (uint32_t i = 0; i < n; i++)
+        CK(cudaMemcpyAsync(&ctx->lanes[lanes[i]].h->result, ctx->d_gather_res + lanes[i], sizeof(Proj), cudaMemcpyDeviceToHost,
+                           ctx->gstream));
+    CK(cudaEventRecord(ctx->ev_gdone, ctx->gstream));
+    for (uint32_t i = 0; i < n; i++) CK(cudaStreamWaitEvent(ctx->lanes[lanes[i]].stream, ctx->ev_gdone, 0));
+    return 0;
+}
+
+int multi_sync(zecale_gpu_ctx *ctx)
+{
+    int rc = multi_flush(ctx);
+    int rc1 = sync_lanes(ctx); // delivers the gathered results (and the coordinator's own lanes)
+    if (rc == 0) rc = rc1;
+    for (zecale_gpu_ctx *w : ctx->workers) {
+        DevGuard dg(w->device);
+        int rcw = sync_lanes(w);
+        if (rcw && rc == 0) rc = fail(ctx, rcw, "worker on device %d: %s", w->device, w->err.c_str());
+    }
+    for (auto &g : ctx->gather) g = zecale_gpu_ctx::Gather();
+    return rc;
+}
+
+// The whole assignment on every worker (epoch upload table), so that the shard MSMs of A, B and L find
+// their scalar ranges without further copies.
+int multi_broadcast_host(zecale_gpu_ctx *ctx, int lane, const void *host, size_t bytes)
+{
+    for (zecale_gpu_ctx *w : ctx->workers) {
+        DevGuard dg(w->device);
+        w->cur = &w->lanes[lane];
+        const uint8_t *d = nullptr;
+        int rc = epoch_upload(w, host, bytes, &d);
+        if (rc > 1) return fail(ctx, rc, "worker on device %d: %s", w->device, w->err.c_str());
+    }
+    return 0;
+}
+
+// Shard g of an MSM over the first n bases of a sharded image on lane `lane` of worker g, partial sums
+// routed to the coordinator's gather buffer. Scalars: host pointers, or (from_qap) the coefficients of
+// the H polynomial in the coordinator's lane on devices[0], sent to the other devices over NVLink.
+int multi_msm_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_bases *h, const void *scalars, size_t sstride,
+                    const size_t *index, size_t n, void *out_point, bool from_qap)
+{
+    Lane &PL = ctx->lanes[lane];
+    if (PL.user_out || ctx->gather[lane].pending) {
+        int rc0 = multi_sync(ctx);
+        if (rc0) return rc0;
+    }
+    if (h->shards.size() != ctx->workers.size()) return fail(ctx, ZECALE_GPU_E_ARG, "pinned image was not made by this multi-device context");
+    uint32_t parts = 0;
+    for (size_t g = 0; g < ctx->workers.size(); g++) {
+        const size_t lo = h->lo[g], hi = h->lo[g + 1] < n ? h->lo[g + 1] : n;
+        const zecale_gpu_bases *hs = h->shards[g];
+        if (lo >= hi || !hs) continue;
+        const size_t ng = hi - lo;
+        zecale_gpu_ctx *w = ctx->workers[g];
+        DevGuard dg(w->device);
+        w->cur = &w->lanes[lane];
+        Lane &WL = *w->cur;
+        if (WL.busy) return fail(ctx, ZECALE_GPU_E_ARG, "lane %d already holds an MSM of this proof", lane);
+        const uint8_t *d_sc = nullptr;
+        const uint64_t *d_idx = nullptr;
+        size_t stride = sstride;
+        int rc = 0;
+        if (from_qap) {
+            const uint8_t *src = (const uint8_t *)PL.ws_qap.p + lo * sizeof(Fr);
+            stride = sizeof(Fr);
+            CK(cudaStreamWaitEvent(WL.stream, ctx->ev_qap, 0));
+            if (w->device == ctx->device) {
+                d_sc = src;
+            } else {
+                rc = reserve(w, WL.ws_sc, ng * sizeof(Fr));
+                if (rc) return fail(ctx, rc, "worker on device %d: %s", w->device, w->err.c_str());
+                CK(cudaMemcpyPeerAsync(WL.ws_sc.p, w->device, src, ctx->device, ng * sizeof(Fr), WL.stream));
+                d_sc = (const uint8_t *)WL.ws_sc.p;
+            }
+        } else {
+            const size_t *idx = index ? index + lo : nullptr;
+            const char *sc = (const char *)scalars;
+            size_t first = lo, count = ng; // scalar range touched
+            if (idx) {
+                size_t mx = 0;
+                for (size_t i = 0; i < ng; i++)
+                    if (idx[i] > mx) mx = idx[i];
+                first = 0;
+                count = mx + 1;
+            }
+            rc = epoch_upload(w, sc + first * sstride, (count - 1) * sstride + sizeof(Fr), &d_sc);
+            if (rc == 1) { // upload table full: lane-private copy
+                rc = reserve(w, WL.ws_sc, (count - 1) * sstride + sizeof(Fr));
+                if (rc == 0) {
+                    CK(cudaMemcpyAsync(WL.ws_sc.p, sc + first * sstride, (count - 1) * sstride + sizeof(Fr), cudaMemcpyHostToDevice, WL.stream));
+                    d_sc = (const uint8_t *)WL.ws_sc.p;
+                }
+            }
+            if (rc) return fail(ctx, rc, "worker on device %d: %s", w->device, w->err.c_str());
+            if (idx) {
+                const uint8_t *d_i = nullptr;
+                rc = epoch_upload(w, idx, ng * 8, &d_i);
+                if (rc == 1) {
+                    rc = reserve(w, WL.ws_idx, ng * 8);
+                    if (rc == 0) {
+                        CK(cudaMemcpyAsync(WL.ws_idx.p, idx, ng * 8, cudaMemcpyHostToDevice, WL.stream));
+                        d_i = (const uint8_t *)WL.ws_idx.p;
+                    }
+                }
+                if (rc) return fail(ctx, rc, "worker on device %d: %s", w->device, w->err.c_str());
+                d_idx = (const uint64_t *)d_i;
+            }
+            // on the witness-map device the accumulations start once the seven transforms are done
+            if (ctx->qap_in_epoch && w->device == ctx->device) CK(cudaStreamWaitEvent(WL.stream, ctx->ev_qap, 0));
+        }
+        rc = msm_device(w, hs->d, hs->is_inf, hs->c, hs->V, (uint32_t)hs->n, d_sc, stride, d_idx, ng, nullptr, nullptr, true,
+                        ctx->d_gather + (size_t)lane * zecale_gpu_ctx::MAX_DEVICES + parts, ctx->device);
+        if (rc) return fail(ctx, rc, "worker on device %d: %s", w->device, w->err.c_str());
+        parts++;
+    }
+    if (parts == 0) { // no point, or none below n: the zero point
+        Proj z;
+        memset(&z, 0, sizeof z);
+        memcpy(z.Y.l, FQ_ONE_HOST, sizeof z.Y.l);
+        memcpy(out_point, &z, sizeof z);
+        return 0;
+    }
+    PL.user_out = out_point;
+    ctx->gather[lane].pending = true;
+    ctx->gather[lane].flushed = false;
+    ctx->gather[lane].n_parts = parts;
+    return 0;
+}
+
 } // namespace
 
 // ====================================================================== C ABI
@@ -770,7 +1019,8 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
         return ZECALE_GPU_E_CUDA; // sm_100a only: no fallback path
     }
     bool ok = cudaMalloc((void **)&ctx->d_status, sizeof(int)) == cudaSuccess &&
-              cudaEventCreateWithFlags(&ctx->ev_qap, cudaEventDisableTiming) == cudaSuccess;
+              cudaEventCreateWithFlags(&ctx->ev_qap, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_parts, cudaEventDisableTiming) == cudaSuccess;
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi); // numerically lower = higher priority
     for (Lane &L : ctx->lanes)
@@ -784,6 +1034,37 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
     ctx->cur = &ctx->lanes[0];
     const char *tr = getenv("ZECALE_GPU_TRACE");
     ctx->trace = tr && tr[0] == '1';
+    if (ok && ctx->devices.size() > 1) {
+        // multi-device context: one worker per listed device (the first shares devices[0] with this
+        // coordinator), peer access between all pairs so that the partial sums and the H coefficients
+        // travel over NVLink, a gather buffer and a high-priority gather stream on devices[0]
+        ok = ctx->devices.size() <= (size_t)zecale_gpu_ctx::MAX_DEVICES;
+        for (size_t a = 0; ok && a < ctx->devices.size(); a++) {
+            for (size_t b = 0; b < a; b++) ok = ok && ctx->devices[a] != ctx->devices[b];
+            ok = ok && ctx->devices[a] >= 0 && ctx->devices[a] < count;
+        }
+        for (size_t a = 0; ok && a < ctx->devices.size(); a++) {
+            cudaSetDevice(ctx->devices[a]);
+            for (size_t b = 0; b < ctx->devices.size(); b++) {
+                if (a == b) continue;
+                cudaError_t pe = cudaDeviceEnablePeerAccess(ctx->devices[b], 0);
+                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) {
+                    // no direct path: cudaMemcpyPeerAsync still works (staged), keep going
+                }
+                cudaGetLastError();
+            }
+        }
+        for (size_t a = 0; ok && a < ctx->devices.size(); a++) {
+            zecale_gpu_ctx *w = nullptr;
+            ok = zecale_gpu_init(&ctx->devices[a], 1, &w) == 0;
+            if (ok) ctx->workers.push_back(w);
+        }
+        cudaSetDevice(ctx->device);
+        ok = ok && cudaMalloc((void **)&ctx->d_gather, sizeof(XYZZ) * ZECALE_GPU_LANES * zecale_gpu_ctx::MAX_DEVICES) == cudaSuccess &&
+             cudaMalloc((void **)&ctx->d_gather_res, sizeof(Proj) * ZECALE_GPU_LANES) == cudaSuccess &&
+             cudaStreamCreateWithPriority(&ctx->gstream, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->ev_gdone, cudaEventDisableTiming) == cudaSuccess;
+    }
     if (!ok) {
         zecale_gpu_shutdown(ctx);
         return ZECALE_GPU_E_CUDA;
@@ -795,9 +1076,16 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
 void zecale_gpu_shutdown(zecale_gpu_ctx *ctx)
 {
     if (!ctx) return;
+    for (zecale_gpu_ctx *w : ctx->workers) zecale_gpu_shutdown(w);
+    ctx->workers.clear();
     cudaSetDevice(ctx->device);
     ctx->cur = &ctx->lanes[0];
     drain_timers(ctx);
+    if (ctx->d_gather) cudaFree(ctx->d_gather);
+    if (ctx->d_gather_res) cudaFree(ctx->d_gather_res);
+    if (ctx->gstream) cudaStreamDestroy(ctx->gstream);
+    if (ctx->ev_gdone) cudaEventDestroy(ctx->ev_gdone);
+    if (ctx->ev_parts) cudaEventDestroy(ctx->ev_parts);
     for (Lane &L : ctx->lanes) {
         for (DevBuf *b : {&L.ws_msm, &L.ws_sc, &L.ws_idx, &L.ws_ntt, &L.ws_qap})
             if (b->p) cudaFree(b->p);
@@ -839,12 +1127,14 @@ int zecale_gpu_msm_g2(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride
 
 // Window size for a fully expanded image (one bucket set shared by all W = ceil(378/c) windows):
 // the c that minimises the Fq products of one MSM over n points,
-//     10 * (n W - non-empty buckets)   mixed additions (the first entry of a bucket is a copy)
+//     10 * (n W - non-empty buckets)   mixed additions (the first entry of a bucket is a copy), divided by the
+//                                      fraction of 1.3 waves of accumulate threads (148 SM x 384) the non-empty
+//                                      buckets (= tasks) fill: measured, 33 k tasks run at 0.46 of the pipe's peak
 //   + 14 * 2 * 2^(c-1) * 1.5           additions of the tail (main tree + bit trees; weighted 1.5 because the
 //                                      tail runs latency-bound, below the accumulation's pipe utilisation),
 // with a surcharge when the top window holds so few bits that its entries pile up in a handful of
 // buckets (those are cut into tasks and folded, which lengthens the latency-bound tail). For the
-// batch-8 queries (n = 88 k ... 262 k) this gives c = 18: 378 = 21 * 18, no ragged top window.
+// batch-8 queries (n = 88 k ... 262 k) this gives c = 18: 378 = 21 * 18, no ragged top window, 131 072 tasks.
 static uint32_t pinned_c(size_t n)
 {
     uint32_t best_c = 8;
@@ -853,7 +1143,8 @@ static uint32_t pinned_c(size_t n)
         const double W = (double)((FR_SCALAR_BITS + 1 + c - 1) / c), NB = (double)(1u << (c - 1));
         const double entries = (double)n * W;
         const double nonempty = NB * (1.0 - exp(-entries / NB));
-        double cost = 10.0 * (entries - nonempty) + 42.0 * NB;
+        const double fill = nonempty / (1.3 * 148.0 * 384.0);
+        double cost = 10.0 * (entries - nonempty) / (fill < 1.0 ? fill : 1.0) + 42.0 * NB;
         const uint32_t top_bits = FR_SCALAR_BITS + 1 - ((uint32_t)W - 1) * c; // data bits of the top window (incl. the carry bit)
         if (top_bits + 4 < c && (double)n / (double)(1u << top_bits) > 8.0 * (entries / NB + 8.0)) cost *= 1.03;
         if (cost < best) {
@@ -866,6 +1157,8 @@ static uint32_t pinned_c(size_t n)
 
 // format 0: libff in-memory special-form points (288 B); 1: libzeth key-file bytes (X || Y, 192 B big-endian plain)
 static int pin_bases_impl(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group, int expand,
+                          zecale_gpu_bases **handle, int format);
+static int pin_bases_impl(zecale_gpu_ctx *ctx, const void *bases, size_t base_stride, size_t n, int group, int expand,
                           zecale_gpu_bases **handle, int format)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
@@ -874,6 +1167,30 @@ static int pin_bases_impl(zecale_gpu_ctx *ctx, const void *bases, size_t base_st
     if (!bases || !handle || !n || base_stride < (format ? sizeof(Affine) : sizeof(Proj)) || (format && (base_stride & 3)) ||
         n >= (1ull << 26) || (group != ZECALE_GPU_G1 && group != ZECALE_GPU_G2))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_pin_bases: bad argument");
+    if (is_multi(ctx)) { // shard the points over the workers, each pins (and expands) its own range
+        zecale_gpu_bases *h = new zecale_gpu_bases();
+        h->n = n;
+        h->group = group;
+        shard_bounds(n, ctx->workers.size(), h->lo);
+        h->shards.assign(ctx->workers.size(), nullptr);
+        for (size_t g = 0; g < ctx->workers.size(); g++) {
+            const size_t ng = h->lo[g + 1] - h->lo[g];
+            if (!ng) continue;
+            int rc = pin_bases_impl(ctx->workers[g], (const char *)bases + h->lo[g] * base_stride, base_stride, ng, group, expand,
+                                    &h->shards[g], format);
+            if (rc) {
+                fail(ctx, rc, "worker on device %d: %s", ctx->workers[g]->device, ctx->workers[g]->err.c_str());
+                for (size_t k = 0; k < g; k++)
+                    if (h->shards[k]) zecale_gpu_unpin_bases(ctx->workers[k], h->shards[k]);
+                delete h;
+                cudaSetDevice(ctx->device);
+                return rc;
+            }
+        }
+        cudaSetDevice(ctx->device);
+        *handle = h;
+        return 0;
+    }
     CK(cudaSetDevice(ctx->device));
     zecale_gpu_bases *h = new zecale_gpu_bases();
     h->n = n;
@@ -952,6 +1269,18 @@ int zecale_gpu_pin_bases(zecale_gpu_ctx *ctx, const void *bases, size_t base_str
 int zecale_gpu_unpin_bases(zecale_gpu_ctx *ctx, zecale_gpu_bases *h)
 {
     if (!ctx || !h) return ZECALE_GPU_E_ARG;
+    if (!h->shards.empty()) {
+        if (h->shards.size() != ctx->workers.size()) return ZECALE_GPU_E_ARG;
+        {
+            std::lock_guard<std::mutex> lk(ctx->mu);
+            multi_sync(ctx);
+        }
+        for (size_t g = 0; g < h->shards.size(); g++)
+            if (h->shards[g]) zecale_gpu_unpin_bases(ctx->workers[g], h->shards[g]);
+        cudaSetDevice(ctx->device);
+        delete h;
+        return 0;
+    }
     std::lock_guard<std::mutex> lk(ctx->mu);
     ctx->cur = &ctx->lanes[0];
     cudaSetDevice(ctx->device);
@@ -971,6 +1300,11 @@ int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, const 
     if (!h || !out_point || n > h->n || (n && !scalars) || scalar_stride < sizeof(Fr))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned: bad argument");
     CK(cudaSetDevice(ctx->device));
+    if (is_multi(ctx)) {
+        int rc = multi_msm_async(ctx, 0, h, scalars, scalar_stride, scalar_index, n, out_point, false);
+        int rc1 = multi_sync(ctx);
+        return rc ? rc : rc1;
+    }
     if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, 0, 0, nullptr, 0, nullptr, 0, out_point, nullptr);
     const uint8_t *d_sc;
     const uint64_t *d_idx;
@@ -989,6 +1323,7 @@ int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, co
     ctx->cur = &ctx->lanes[0];
     if (!h || !out_point || n > h->n || (n && !d_scalars) || scalar_stride < sizeof(Fr))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: bad argument");
+    if (is_multi(ctx)) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: device-resident scalars belong to one device; use a single-device context");
     CK(cudaSetDevice(ctx->device));
     return msm_device(ctx, h->d, h->is_inf, h->c, h->V, (uint32_t)h->n, (const uint8_t *)d_scalars, scalar_stride,
                       d_scalar_index, n, out_point, elapsed_ms);
@@ -1147,29 +1482,6 @@ int zecale_gpu_qap_pointwise_dev(zecale_gpu_ctx *ctx, void *d_aA, const void *d_
 
 int zecale_gpu_lane_count(void) { return ZECALE_GPU_LANES; }
 
-// Device copy of the host byte range [host, host+bytes) for the current lane: reuses an upload
-// made earlier in this epoch (any lane) if it covers the range, else uploads on this lane.
-static int epoch_upload(zecale_gpu_ctx *ctx, const void *host, size_t bytes, const uint8_t **d_out)
-{
-    const char *h = (const char *)host;
-    for (auto &u : ctx->uploads)
-        if (h >= u.host && h + bytes <= u.host + u.bytes) {
-            CK(cudaStreamWaitEvent(ctx->cur->stream, u.ev, 0));
-            *d_out = (const uint8_t *)ctx->up_pool[u.buf].p + (h - u.host);
-            return 0;
-        }
-    if (ctx->uploads.size() >= 8) return 1; // pool exhausted: caller falls back to a lane-private upload
-    int slot = (int)ctx->uploads.size();
-    int rc = reserve(ctx, ctx->up_pool[slot], bytes);
-    if (rc) return rc;
-    CK(cudaMemcpyAsync(ctx->up_pool[slot].p, host, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
-    cudaEvent_t ev = take_event(ctx);
-    CK(cudaEventRecord(ev, ctx->cur->stream));
-    ctx->uploads.push_back({h, bytes, slot, ev});
-    *d_out = (const uint8_t *)ctx->up_pool[slot].p;
-    return 0;
-}
-
 int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_bases *h, const void *scalars,
                                 size_t scalar_stride, const void *scalar_index, size_t n, void *out_point, unsigned flags)
 {
@@ -1180,6 +1492,14 @@ int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_async: bad argument");
     CK(cudaSetDevice(ctx->device));
     ctx->cur = &ctx->lanes[lane];
+    if (is_multi(ctx)) {
+        if (flags & ZECALE_GPU_DEVICE_POINTERS)
+            return fail(ctx, ZECALE_GPU_E_ARG, "msm_pinned_async: device-resident scalars belong to one device; use a single-device context");
+        if ((flags & ZECALE_GPU_SCALARS_FROM_QAP) && !ctx->cur->ws_qap.p)
+            return fail(ctx, ZECALE_GPU_E_ARG, "msm_pinned_async: no H polynomial on this lane");
+        return multi_msm_async(ctx, lane, h, scalars, scalar_stride, (const size_t *)scalar_index, n, out_point,
+                               (flags & ZECALE_GPU_SCALARS_FROM_QAP) != 0);
+    }
     const uint8_t *d_sc = (const uint8_t *)scalars;
     const uint64_t *d_idx = (const uint64_t *)scalar_index;
     if (flags & ZECALE_GPU_SCALARS_FROM_QAP) {
@@ -1344,8 +1664,17 @@ int zecale_gpu_qap_h_from_witness_async(zecale_gpu_ctx *ctx, int lane, const zec
     // the assignment [1, primary, aux] crosses PCIe once per proof: the MSM calls that pass the
     // same host range (A, B, L) find it in the epoch's upload table
     const uint8_t *d_w = (const uint8_t *)assignment;
+    if (is_multi(ctx) && (ctx->gather[lane].pending || ctx->cur->user_out)) {
+        int rc0 = multi_sync(ctx);
+        if (rc0) return rc0;
+    }
     if (!(flags & ZECALE_GPU_DEVICE_POINTERS)) {
         const size_t wbytes = (r1cs->n_variables + 1) * sizeof(Fr);
+        if (is_multi(ctx)) { // every worker gets the assignment once; the shard MSMs of A, B and L find it there
+            rc = multi_broadcast_host(ctx, lane, assignment, wbytes);
+            if (rc) return rc;
+            CK(cudaSetDevice(ctx->device));
+        }
         rc = epoch_upload(ctx, assignment, wbytes, &d_w);
         if (rc == 1) { // upload table full: lane-private copy
             rc = reserve(ctx, ctx->cur->ws_sc, wbytes);
@@ -1380,7 +1709,7 @@ int zecale_gpu_sync(zecale_gpu_ctx *ctx)
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
     CK(cudaSetDevice(ctx->device));
-    return sync_lanes(ctx);
+    return is_multi(ctx) ? multi_sync(ctx) : sync_lanes(ctx);
 }
 
 int zecale_gpu_flush(zecale_gpu_ctx *ctx)
@@ -1388,7 +1717,7 @@ int zecale_gpu_flush(zecale_gpu_ctx *ctx)
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
     CK(cudaSetDevice(ctx->device));
-    return flush_tails(ctx);
+    return is_multi(ctx) ? multi_flush(ctx) : flush_tails(ctx);
 }
 
 void *zecale_gpu_host_alloc(size_t bytes)
@@ -1510,7 +1839,15 @@ int zecale_gpu_msm_last_stats(zecale_gpu_ctx *ctx, uint64_t *entries, uint64_t *
     return 0;
 }
 
-uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx)
+{
+    if (!ctx) return 0;
+    uint64_t n = ctx->launches;
+    for (zecale_gpu_ctx *w : ctx->workers) n += w->launches;
+    return n;
+}
+
+int zecale_gpu_device_count(zecale_gpu_ctx *ctx) { return ctx ? (int)ctx->devices.size() : 0; }
 
 unsigned zecale_gpu_msm_window_bits(size_t n) { return n ? msm_default_c((uint32_t)n) : 0; }
 

@@ -91,15 +91,34 @@ inline state_t &state()
     return s;
 }
 
-/// The process-wide context, created on first use on device $ZECALE_GPU_DEVICE (default: current).
+/// Devices of every context the hooks create: $ZECALE_GPU_DEVICES = "0,1,2,3" (a multi-device context:
+/// the MSMs of a resident key are sharded over them), else $ZECALE_GPU_DEVICE, else the current device.
+inline std::vector<int> device_list()
+{
+    std::vector<int> out;
+    if (const char *l = std::getenv("ZECALE_GPU_DEVICES")) {
+        const char *p = l;
+        while (*p) {
+            char *end = nullptr;
+            const long v = std::strtol(p, &end, 10);
+            if (end == p) break;
+            out.push_back((int)v);
+            p = *end == ',' ? end + 1 : end;
+        }
+    } else if (const char *d = std::getenv("ZECALE_GPU_DEVICE")) {
+        out.push_back(std::atoi(d));
+    }
+    return out;
+}
+
+/// The process-wide context, created on first use (see device_list).
 inline zecale_gpu_ctx *context()
 {
     state_t &s = state();
     std::lock_guard<std::mutex> lk(s.mu);
     if (!s.ctx) {
-        const char *dev = std::getenv("ZECALE_GPU_DEVICE");
-        int d = dev ? std::atoi(dev) : 0;
-        const int rc = zecale_gpu_init(dev ? &d : nullptr, dev ? 1 : 0, &s.ctx);
+        const std::vector<int> devs = device_list();
+        const int rc = zecale_gpu_init(devs.empty() ? nullptr : devs.data(), (int)devs.size(), &s.ctx);
         if (rc != ZECALE_GPU_OK) {
             s.ctx = nullptr;
             throw std::runtime_error("zecale_gpu_init failed (code " + std::to_string(rc) + "): no usable sm_100 device");
@@ -229,9 +248,8 @@ inline size_t acquire_slot(size_t staging_bytes)
     });
     state_t::slot_t &sl = s.slots[k];
     if (!sl.ctx) {
-        const char *dev = std::getenv("ZECALE_GPU_DEVICE");
-        int d = dev ? std::atoi(dev) : 0;
-        if (zecale_gpu_init(dev ? &d : nullptr, dev ? 1 : 0, &sl.ctx) != ZECALE_GPU_OK) {
+        const std::vector<int> devs = device_list();
+        if (zecale_gpu_init(devs.empty() ? nullptr : devs.data(), (int)devs.size(), &sl.ctx) != ZECALE_GPU_OK) {
             sl.ctx = nullptr;
             throw std::runtime_error("zecale_gpu_init failed for a proof slot");
         }
