@@ -226,10 +226,19 @@ int zecale_gpu_point_sum(zecale_gpu_ctx *ctx, const void *points, size_t n, void
 int zecale_gpu_ntt_dist_phase(zecale_gpu_ctx *ctx, const void *d_in, void *d_out, unsigned log_m, unsigned flags,
                               const void *coset_g, int world, int rank, int phase, int sync);
 
+/* The same phase enqueued on the CALLER's stream (a cudaStream_t, e.g. the stream the caller's NCCL
+ * collectives are ordered on) and not synchronised: phase 0, the all-to-all and phase 1 then chain on the
+ * device with no host round trip in between. Tables are built on first use (that call synchronises). */
+int zecale_gpu_ntt_dist_phase_on(zecale_gpu_ctx *ctx, void *stream, const void *d_in, void *d_out, unsigned log_m,
+                                 unsigned flags, const void *coset_g, int world, int rank, int phase);
+
 /* The pointwise step of r1cs_to_qap_witness_map on `count` locally held elements of a domain of
  * size 2^log_m (r1cs_to_qap.tcc:283-315): aA[i] = (aA[i]*aB[i] - aC[i]) / (g^m - 1). DEVICE pointers. */
 int zecale_gpu_qap_pointwise_dev(zecale_gpu_ctx *ctx, void *d_aA, const void *d_aB, const void *d_aC, unsigned log_m,
                                  const void *coset_g, size_t count);
+/* ... on the caller's stream, not synchronised. */
+int zecale_gpu_qap_pointwise_dev_on(zecale_gpu_ctx *ctx, void *stream, void *d_aA, const void *d_aB, const void *d_aC,
+                                    unsigned log_m, const void *coset_g, size_t count);
 
 /* ---- synthetic inputs (bench / tests): out_points[i] = k_i * generator of the group, in
  * libff special form (288 B each), k_i a non-zero 32-bit hash of (seed, i). HOST pointer. */

@@ -35,6 +35,10 @@ def barrier():
 
 
 drv = D.DistNtt(D.gpu_phase_fn(ctx), D.nccl_exchange_fn() if world > 1 else None, world, rank)
+from oracle import ref as R   # checker only (scripts/ is measurement + verification, not the product path)
+REF = R.Ref() if R.available() else None
+if REF is not None:
+    REF.set_threads(max(1, (os.cpu_count() or 1) // max(world, 1)))
 for log_m in sizes:
     m = 1 << log_m
     x = bench.random_fr(np.random.default_rng(log_m), m)            # same on every rank (seeded)
@@ -47,12 +51,13 @@ for log_m in sizes:
         keep = buf.clone()
         drv.transform(buf, scratch, log_m, flags, g if flags & 2 else None)        # warm-up (tables)
         ts = []
+        out = None
         for _ in range(3):
             buf.copy_(keep)
             barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            drv.transform(buf, scratch, log_m, flags, g if flags & 2 else None)
+            out, _ = drv.transform(buf, scratch, log_m, flags, g if flags & 2 else None)   # phases + all-to-all chained on one stream
             e1.record()
             torch.cuda.synchronize()
             t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
@@ -60,15 +65,21 @@ for log_m in sizes:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ts.append(float(t.item()))
         res[name + "_ms"] = min(ts)
-        # correctness: rank 0 computes the single-GPU transform and every rank checks its shard
-        full = torch.from_numpy(x.view(np.int64).copy()).cuda()
-        ctx.ntt_dev(full.data_ptr(), log_m, flags, g if flags & 2 else None)
-        exp = full.cpu().numpy().view(np.uint64)[dst_idx]
-        ok = torch.tensor([int(np.array_equal(buf.cpu().numpy().view(np.uint64), exp))], device="cuda")
+        # correctness: every rank checks its shard against libfqfft (oracle/_ref) when it is on the box,
+        # else against the single-GPU transform (itself pinned to libfqfft by tests/test_ntt_gpu.py)
+        if REF is not None:
+            exp = REF.ntt(x, flags, g)[0][dst_idx]
+            res[name + "_checked_against"] = "libfqfft basic_radix2_domain (oracle/_ref)"
+        else:
+            full = torch.from_numpy(x.view(np.int64).copy()).cuda()
+            ctx.ntt_dev(full.data_ptr(), log_m, flags, g if flags & 2 else None)
+            exp = full.cpu().numpy().view(np.uint64)[dst_idx]
+            del full
+            res[name + "_checked_against"] = "single-GPU transform"
+        ok = torch.tensor([int(np.array_equal(out.cpu().numpy().view(np.uint64), exp))], device="cuda")
         if world > 1:
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         res[name + "_ok"] = bool(ok.item())
-        del full
     if rank == 0:
         print(json.dumps(res), flush=True)
 
@@ -97,7 +108,11 @@ for log_n in (20, 22):
     pin.release()
     res = {"op": "msm_sharded_g1", "log_n": log_n, "world": world, "ms": min(ts)}
     if rank == 0:
-        res["result_limb0"] = hex(int(total[0]))
+        # the whole MSM on this GPU alone: the sharded sum must be the same 288 bytes
+        allp = ctx.pin_bases(ctx.synth_bases(n, z.G1, seed=77))
+        whole = ctx.msm_pinned(allp, sc_all)
+        allp.release()
+        res["equals_single_gpu_point"] = bool(np.array_equal(whole, total))
         print(json.dumps(res), flush=True)
 ctx.close()
 if world > 1:

@@ -72,8 +72,8 @@ def _dist_ntt(rank, world):
         src_idx, dst_idx = (ib, ia) if flags & 1 else (ia, ib)
         buf = _t(x[src_idx])
         scratch = torch.empty_like(buf)
-        drv.transform(buf, scratch, log_m, flags, g["coset_g"] if flags & 2 else None)
-        got = _gather_layout(buf, torch.from_numpy(dst_idx), m, world)
+        res, _ = drv.transform(buf, scratch, log_m, flags, g["coset_g"] if flags & 2 else None)
+        got = _gather_layout(res, torch.from_numpy(dst_idx), m, world)
         assert np.array_equal(got, g["out_8_%d" % flags]), flags
 
 

@@ -55,6 +55,8 @@ EXPORTS = {
     "zecale_gpu_point_sum": (_i, [_vp, _vp, _sz, _vp]),
     "zecale_gpu_ntt_dist_phase": (_i, [_vp, _vp, _vp, _u, _u, _vp, _i, _i, _i, _i]),
     "zecale_gpu_qap_pointwise_dev": (_i, [_vp, _vp, _vp, _vp, _u, _vp, _sz]),
+    "zecale_gpu_ntt_dist_phase_on": (_i, [_vp, _vp, _vp, _vp, _u, _u, _vp, _i, _i, _i]),
+    "zecale_gpu_qap_pointwise_dev_on": (_i, [_vp, _vp, _vp, _vp, _vp, _u, _vp, _sz]),
     "zecale_gpu_r1cs_load": (_i, [_vp, _sz, _sz, _sz, ctypes.POINTER(_vp), ctypes.POINTER(_vp), ctypes.POINTER(_vp),
                                   ctypes.POINTER(_vp)]),
     "zecale_gpu_r1cs_free": (_i, [_vp, _vp]),
@@ -257,6 +259,15 @@ class Context:
     def ntt_dist_phase(self, d_in, d_out, log_m, flags, coset_g, world, rank, phase, sync=True):
         self._ck(_lib.zecale_gpu_ntt_dist_phase(self._h, ctypes.c_void_p(d_in), ctypes.c_void_p(d_out), log_m, flags,
                                                 _ptr(coset_g), world, rank, phase, 1 if sync else 0))
+
+    def ntt_dist_phase_on(self, stream, d_in, d_out, log_m, flags, coset_g, world, rank, phase):
+        """The phase on the caller's CUDA stream (raw handle), not synchronised."""
+        self._ck(_lib.zecale_gpu_ntt_dist_phase_on(self._h, ctypes.c_void_p(stream), ctypes.c_void_p(d_in), ctypes.c_void_p(d_out),
+                                                   log_m, flags, _ptr(coset_g), world, rank, phase))
+
+    def qap_pointwise_dev_on(self, stream, d_aA, d_aB, d_aC, log_m, coset_g, count):
+        self._ck(_lib.zecale_gpu_qap_pointwise_dev_on(self._h, ctypes.c_void_p(stream), ctypes.c_void_p(d_aA), ctypes.c_void_p(d_aB),
+                                                      ctypes.c_void_p(d_aC), log_m, _ptr(coset_g), count))
 
     def qap_pointwise_dev(self, d_aA, d_aB, d_aC, log_m, coset_g, count):
         self._ck(_lib.zecale_gpu_qap_pointwise_dev(self._h, ctypes.c_void_p(d_aA), ctypes.c_void_p(d_aB), ctypes.c_void_p(d_aC),

@@ -51,6 +51,7 @@ struct MsmPlan {
     uint64_t max_tasks;
     uint32_t acc_mode;     // MSM_ACC_XYZZ | MSM_ACC_TREE
     uint32_t tree_rounds;  // pair-tree rounds launched = ceil(log2(n * G)) (a bucket holds <= n*G entries)
+    uint32_t tree_min;     // rounds every bucket goes through before the XYZZ chains take over (k_tree_chain)
 };
 
 // Bucket accumulation mode: ZECALE_GPU_ACC = "tree" (batched affine pair tree, k_tree_round) or
@@ -63,6 +64,18 @@ inline uint32_t msm_acc_mode()
     if (v && v[0] == 'x') return MSM_ACC_XYZZ;
     if (v && v[0] == 't') return MSM_ACC_TREE;
     return MSM_ACC_DEFAULT;
+}
+// Hybrid accumulation: the first rounds of the pair tree hold almost all additions (1/2, 1/4, 1/8 ...
+// of them) in big, perfectly balanced batches of affine additions (6 products each + a shared
+// inversion); what is left after MSM_TREE_MIN_ROUNDS rounds - <= ceil(n_b / 2^R) points per bucket -
+// is summed by one XYZZ chain per bucket (10 products per addition, no batch to fill). Buckets much
+// heavier than the rest keep halving until no chain is longer than MSM_TREE_CHAIN_MAX points.
+static constexpr uint32_t MSM_TREE_MIN_ROUNDS = 3;
+static constexpr uint32_t MSM_TREE_CHAIN_MAX = 16;
+inline uint32_t msm_tree_min_rounds()
+{
+    const char *v = getenv("ZECALE_GPU_TREE_ROUNDS");
+    return v ? (uint32_t)atoi(v) : MSM_TREE_MIN_ROUNDS;
 }
 
 struct TreeMeta {
@@ -106,6 +119,7 @@ inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_s
     p.acc_mode = msm_acc_mode();
     p.tree_rounds = 0;
     while ((1ull << p.tree_rounds) < (uint64_t)n * p.G) p.tree_rounds++;
+    p.tree_min = msm_tree_min_rounds();
     p.n_buckets = (uint64_t)p.V * p.NB;
     p.max_tasks = ((uint64_t)n * p.W) / p.S + p.n_buckets + 1;
     return p;
@@ -602,6 +616,16 @@ __device__ __forceinline__ uint32_t tree_rounds_needed(uint32_t max_count)
     return r;
 }
 
+// Rounds the tree runs for the largest bucket `max_count` when every bucket does at least `rmin` rounds
+// and the chains that follow take at most MSM_TREE_CHAIN_MAX points: the level k_tree_chain reads.
+__device__ __forceinline__ uint32_t tree_last_level(uint32_t max_count, uint32_t rmin)
+{
+    const uint32_t need = tree_rounds_needed(max_count);
+    uint32_t r = rmin < need ? rmin : need;
+    while (r < need && ((max_count + (1u << r) - 1) >> r) > MSM_TREE_CHAIN_MAX) r++;
+    return r;
+}
+
 // level-r slot index of bucket b's first point (r >= 1)
 __device__ __forceinline__ uint32_t tree_base(const uint32_t *off, uint32_t b, uint32_t r) { return (off[b] >> r) + b; }
 
@@ -632,11 +656,11 @@ __device__ __forceinline__ void affine_store_inf(Affine *dst)
 
 template <int K>
 __global__ void __launch_bounds__(128, 3)
-k_tree_round(uint32_t r, uint32_t n_buckets, const uint32_t *off, const TreeMeta *meta, const Affine *bases,
+k_tree_round(uint32_t r, uint32_t rmin, uint32_t n_buckets, const uint32_t *off, const TreeMeta *meta, const Affine *bases,
              const uint32_t *entries, const Affine *in, Affine *out)
 {
     using SF = FqSlotFile<VS_COUNT + K>;
-    if (r >= tree_rounds_needed(meta->max_count)) return; // every bucket is already down to one point
+    if (r >= tree_last_level(meta->max_count, rmin)) return; // the chains take over from here
     const uint32_t slots = (off[n_buckets] >> (r + 1)) + n_buckets; // level r+1
     const uint32_t s0 = (blockIdx.x * blockDim.x + threadIdx.x) * K;
     // bucket of slot s0: the largest b with base_{r+1}(b) <= s0
@@ -799,35 +823,44 @@ k_tree_round(uint32_t r, uint32_t n_buckets, const uint32_t *off, const TreeMeta
         rel);
 }
 
-// Bucket values (level R = rounds needed, one point per non-empty bucket) -> partial[task_off[b]] as
-// XYZZ with zz = zzz = 1, the form the running-sum levels read.
-__global__ void k_tree_finish(uint32_t n_buckets, const uint32_t *off, const uint32_t *task_off, const TreeMeta *meta,
-                              const Affine *bases, const uint32_t *entries, const Affine *lvl_odd, const Affine *lvl_even,
-                              XYZZ *partial)
+// What the tree rounds left of bucket b - cr = ceil(n_b / 2^R) affine points at level R = tree_last_level
+// (the entries themselves when R = 0) - is summed by one XYZZ chain: partial[task_off[b]] = their sum.
+__global__ void __launch_bounds__(128, 3)
+k_tree_chain(uint32_t rmin, uint32_t n_buckets, const uint32_t *off, const uint32_t *task_off, const TreeMeta *meta,
+             const Affine *bases, const uint32_t *entries, const Affine *lvl_odd, const Affine *lvl_even, XYZZ *partial)
 {
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_buckets) return;
-    const uint32_t o = off[b];
-    if (off[b + 1] == o) return;
-    const uint32_t R = tree_rounds_needed(meta->max_count);
-    FqSlots S;
-    if (R == 0) {
-        tree_load_entry(S, VS_X, VS_Y, bases, entries[o]);
-    } else {
-        const Affine *src = ((R & 1u) ? lvl_odd : lvl_even) + tree_base(off, b, R);
-        vs_set(S, VS_X, &src->x);
-        vs_set(S, VS_Y, &src->y);
-    }
+    const uint32_t o = off[b], nb = off[b + 1] - o;
+    if (nb == 0) return;
+    const uint32_t R = tree_last_level(meta->max_count, rmin);
+    const uint32_t cr = (nb + (1u << R) - 1) >> R;
+    const Affine *lvl = R == 0 ? nullptr : ((R & 1u) ? lvl_odd : lvl_even) + tree_base(off, b, R);
     XYZZ *dst = partial + task_off[b];
-    if (vs_is_zero(S, VS_X) && vs_is_zero(S, VS_Y)) {
-        xyzz_store_inf(dst);
-        return;
-    }
-    vs_get(&dst->x, S, VS_X);
-    vs_get(&dst->y, S, VS_Y);
-    vs_one(S, VS_T0);
-    vs_get(&dst->zz, S, VS_T0);
-    vs_get(&dst->zzz, S, VS_T0);
+    uint32_t i = 0;
+    FqSlots S;
+    vs_acc_inf(S);
+    auto fetch = [&](uint32_t &pc, FqSlots &S_) -> bool {
+        for (;;) {
+            if (i >= cr) {
+                vs_store_acc(dst, S_);
+                return false;
+            }
+            if (R == 0) {
+                tree_load_entry(S_, VS_QX, VS_QY, bases, entries[o + i]);
+            } else {
+                vs_set(S_, VS_QX, &lvl[i].x);
+                vs_set(S_, VS_QY, &lvl[i].y);
+            }
+            i++;
+            if (!(vs_is_zero(S_, VS_QX) && vs_is_zero(S_, VS_QY))) break; // (0,0) = infinity
+        }
+        pc = VPC_MADD;
+        return true;
+    };
+    uint32_t pc = 0;
+    if (!fetch(pc, S)) return;
+    fqvm_run_noinv(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); });
 }
 
 // ------------------------------------------------------------------ tail: sum_b (b+1) B_b, batched over MSMs
@@ -1319,7 +1352,7 @@ inline void tree_round_launch(const MsmPlan &p, const MsmBuffers &b, uint32_t r,
 {
     const uint64_t slots = (((uint64_t)p.n * p.W) >> (r + 1)) + p.n_buckets;
     const unsigned blocks = (unsigned)(((slots + K - 1) / K + 127) / 128);
-    k_tree_round<K><<<blocks, 128, 0, st>>>(r, (uint32_t)p.n_buckets, b.offsets, b.tree_meta, d_bases, b.entries,
+    k_tree_round<K><<<blocks, 128, 0, st>>>(r, p.tree_min, (uint32_t)p.n_buckets, b.offsets, b.tree_meta, d_bases, b.entries,
                                             r ? b.tree_lvl[(r - 1) & 1] : nullptr, b.tree_lvl[r & 1]);
 }
 
@@ -1356,8 +1389,9 @@ inline cudaError_t msm_launch_front(const MsmPlan &p, const MsmBuffers &b, const
             else
                 tree_round_launch<8>(p, b, r, d_bases, st);
         }
-        k_tree_finish<<<gb, 256, 0, st>>>((uint32_t)p.n_buckets, b.offsets, b.task_off, b.tree_meta, d_bases, b.entries,
-                                          b.tree_lvl[0], b.tree_lvl[1], b.partial);
+        k_tree_chain<<<(unsigned)((p.n_buckets + 127) / 128), 128, 0, st>>>(p.tree_min, (uint32_t)p.n_buckets, b.offsets, b.task_off,
+                                                                           b.tree_meta, d_bases, b.entries, b.tree_lvl[0],
+                                                                           b.tree_lvl[1], b.partial);
         if (acc_ev1) cudaEventRecord(acc_ev1, st);
         return cudaGetLastError();
     }

@@ -1431,8 +1431,8 @@ int zecale_gpu_point_sum(zecale_gpu_ctx *ctx, const void *points, size_t n, void
     return 0;
 }
 
-int zecale_gpu_ntt_dist_phase(zecale_gpu_ctx *ctx, const void *d_in, void *d_out, unsigned log_m, unsigned flags,
-                              const void *coset_g, int world, int rank, int phase, int sync)
+static int ntt_dist_phase_impl(zecale_gpu_ctx *ctx, cudaStream_t user_stream, bool on_user_stream, const void *d_in, void *d_out,
+                               unsigned log_m, unsigned flags, const void *coset_g, int world, int rank, int phase, int sync)
 {
     if (!ctx) return ZECALE_GPU_E_ARG;
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -1444,19 +1444,58 @@ int zecale_gpu_ntt_dist_phase(zecale_gpu_ctx *ctx, const void *d_in, void *d_out
     CK(cudaSetDevice(ctx->device));
     unsigned nl = 0;
     const Fr *tw = nullptr;
-    CK(ntt_get_twiddles(ctx->ntt, log_m, ctx->cur->stream, &tw, &nl)); // tables outside the timed region
+    CK(ntt_get_twiddles(ctx->ntt, log_m, ctx->cur->stream, &tw, &nl)); // tables outside the timed region (built once, synchronised)
+    if ((flags & ZECALE_GPU_NTT_COSET) || (flags & ZECALE_GPU_NTT_INVERSE)) {
+        Fr one_g;
+        memcpy(one_g.l, FR_ONE_HOST, sizeof(Fr));
+        const Fr *ctab = nullptr;
+        CK(ntt_get_coset(ctx->ntt, log_m, (flags & ZECALE_GPU_NTT_COSET) ? *(const Fr *)coset_g : one_g, flags & 1u, ctx->cur->stream,
+                         &ctab, &nl));
+    }
+    cudaStream_t st = on_user_stream ? user_stream : ctx->cur->stream;
     cudaEvent_t e0 = take_event(ctx), e1 = take_event(ctx);
-    CK(cudaEventRecord(e0, ctx->cur->stream));
+    CK(cudaEventRecord(e0, st));
     cudaError_t e = ntt_dist_phase(ctx->ntt, (const Fr *)d_in, (Fr *)d_out, log_m, flags, (const Fr *)coset_g, (uint32_t)world,
-                                   (uint32_t)rank, (uint32_t)phase, ctx->cur->stream, &nl);
+                                   (uint32_t)rank, (uint32_t)phase, st, &nl);
     if (e == cudaErrorInvalidValue)
         return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_ntt_dist_phase: world %d does not divide the 4-step factors of 2^%u", world, log_m);
     CK(e);
-    CK(cudaEventRecord(e1, ctx->cur->stream));
+    CK(cudaEventRecord(e1, st));
     ctx->ev_pending[1].emplace_back(e0, e1);
     if (ctx->ev_pending[1].size() > 256) drain_timers(ctx, false);
     ctx->launches += nl;
-    if (sync) CK(cudaStreamSynchronize(ctx->cur->stream));
+    if (sync) CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int zecale_gpu_ntt_dist_phase(zecale_gpu_ctx *ctx, const void *d_in, void *d_out, unsigned log_m, unsigned flags,
+                              const void *coset_g, int world, int rank, int phase, int sync)
+{
+    return ntt_dist_phase_impl(ctx, nullptr, false, d_in, d_out, log_m, flags, coset_g, world, rank, phase, sync);
+}
+
+int zecale_gpu_ntt_dist_phase_on(zecale_gpu_ctx *ctx, void *stream, const void *d_in, void *d_out, unsigned log_m, unsigned flags,
+                                 const void *coset_g, int world, int rank, int phase)
+{
+    return ntt_dist_phase_impl(ctx, (cudaStream_t)stream, true, d_in, d_out, log_m, flags, coset_g, world, rank, phase, 0);
+}
+
+int zecale_gpu_qap_pointwise_dev_on(zecale_gpu_ctx *ctx, void *stream, void *d_aA, const void *d_aB, const void *d_aC, unsigned log_m,
+                                    const void *coset_g, size_t count)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!d_aA || !d_aB || !d_aC || !coset_g || !count) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_qap_pointwise_dev_on: bad argument");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_qap_pointwise_dev_on: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    const Fr *zinv = nullptr;
+    int rc = get_zinv(ctx, log_m, (const Fr *)coset_g, &zinv); // cached per (log_m, g); built (and synchronised) on first use
+    if (rc) return rc;
+    k_qap_pointwise<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>((Fr *)d_aA, (const Fr *)d_aB, (const Fr *)d_aC,
+                                                                                    zinv, count);
+    ctx->launches++;
+    CK(cudaGetLastError());
     return 0;
 }
 

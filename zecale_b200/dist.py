@@ -81,47 +81,64 @@ def layout_b_indices(log_m, world, rank):
 
 class DistNtt:
     """Driver of the distributed transforms. buf / scratch: torch tensors of shape (m/world, 6),
-    int64 (the 48-byte Fr rows), on the device the phase function works on."""
+    int64 (the 48-byte Fr rows), on the device the phase function works on. The two buffers ping-pong:
+    every method returns (result, other) - which of the two tensors holds the result depends on the
+    world size - and nothing is copied back. With the GPU backends below every phase, the all-to-all
+    and the pointwise step are enqueued on torch's current stream, so a whole H-polynomial pipeline
+    runs without a host synchronisation."""
 
     def __init__(self, phase_fn, exchange_fn, world, rank):
         self.phase_fn, self.exchange_fn, self.world, self.rank = phase_fn, exchange_fn, world, rank
 
     def transform(self, buf, scratch, log_m, flags, coset_g=None):
-        """In place on buf. flags bit0 inverse, bit1 coset. Forward: layout A in, B out; inverse: B in, A out."""
+        """flags bit0 inverse, bit1 coset. Forward: layout A in, B out; inverse: B in, A out.
+        Input in `buf`; returns (tensor holding the result, the other tensor)."""
         self.phase_fn(buf, scratch, log_m, flags, coset_g, self.world, self.rank, 0)
         if self.world > 1:
-            self.exchange_fn(buf, scratch)
-            src = buf
-            dst = scratch
-        else:
-            src, dst = scratch, buf
-        self.phase_fn(src, dst, log_m, flags, coset_g, self.world, self.rank, 1)
-        if self.world > 1:
-            buf.copy_(scratch)
-        return buf
+            self.exchange_fn(buf, scratch)        # buf <- all-to-all(scratch)
+            self.phase_fn(buf, scratch, log_m, flags, coset_g, self.world, self.rank, 1)
+            return scratch, buf
+        self.phase_fn(scratch, buf, log_m, flags, coset_g, self.world, self.rank, 1)
+        return buf, scratch
 
     def qap_h(self, aA, aB, aC, scratch, log_m, coset_g, pointwise_fn):
-        """H polynomial from the three evaluation vectors held in layout B; the coefficients come
-        back in aA in layout A. pointwise_fn(aA, aB, aC) computes (aA*aB - aC) / Z on the coset, in aA."""
+        """H polynomial from the three evaluation vectors held in layout B; returns the tensor that holds
+        the coefficients (layout A). pointwise_fn(aA, aB, aC) computes (aA*aB - aC) / Z on the coset, in aA.
+        All four tensors are clobbered."""
+        vec = []
         for v in (aA, aB, aC):
-            self.transform(v, scratch, log_m, 1)             # iFFT       B -> A
-            self.transform(v, scratch, log_m, 2, coset_g)    # cosetFFT   A -> B
-        pointwise_fn(aA, aB, aC)
-        return self.transform(aA, scratch, log_m, 3, coset_g)  # icosetFFT  B -> A
+            v, scratch = self.transform(v, scratch, log_m, 1)             # iFFT       B -> A
+            v, scratch = self.transform(v, scratch, log_m, 2, coset_g)    # cosetFFT   A -> B
+            vec.append(v)
+        pointwise_fn(vec[0], vec[1], vec[2])
+        h, _ = self.transform(vec[0], scratch, log_m, 3, coset_g)         # icosetFFT  B -> A
+        return h
 
 
 # ------------------------------------------------------------------ GPU backends (C ABI + NCCL)
 def gpu_phase_fn(ctx):
+    """Phases on torch's current stream (zecale_gpu_ntt_dist_phase_on): ordered with the NCCL collective
+    that torch.distributed enqueues behind the same stream, no host synchronisation."""
+    import torch
+
     def phase(src, dst, log_m, flags, coset_g, world, rank, ph):
-        ctx.ntt_dist_phase(src.data_ptr(), dst.data_ptr(), log_m, flags, coset_g, world, rank, ph, sync=True)
+        ctx.ntt_dist_phase_on(torch.cuda.current_stream().cuda_stream, src.data_ptr(), dst.data_ptr(), log_m, flags, coset_g,
+                              world, rank, ph)
     return phase
 
 
-def nccl_exchange_fn(group=None):
+def gpu_pointwise_fn(ctx, log_m, coset_g):
     import torch
+
+    def pointwise(aA, aB, aC):
+        ctx.qap_pointwise_dev_on(torch.cuda.current_stream().cuda_stream, aA.data_ptr(), aB.data_ptr(), aC.data_ptr(), log_m,
+                                 coset_g, aA.shape[0])
+    return pointwise
+
+
+def nccl_exchange_fn(group=None):
     import torch.distributed as dist
 
     def exchange(dst, src):
-        dist.all_to_all_single(dst.view(-1), src.view(-1), group=group)
-        torch.cuda.current_stream().synchronize()   # the library runs on its own streams
+        dist.all_to_all_single(dst.view(-1), src.view(-1), group=group)   # ordered on the current stream by ProcessGroupNCCL
     return exchange
