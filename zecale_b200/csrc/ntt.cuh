@@ -179,6 +179,7 @@ struct NttPass {
     const Fr *in_scale_tab;   // != null: input element is first multiplied by in_scale_tab[u*isc_sv + r*isc_sr + isc_off]
     uint64_t isc_sv, isc_sr, isc_off;
     uint32_t stw_global;      // 1: sub-transform twiddles are read from the global table (R too large to stage)
+    uint64_t batch_stride;    // blockIdx.y selects one of several same-sized vectors, batch_stride elements apart
 };
 
 __device__ __forceinline__ uint32_t bitrev(uint32_t x, uint32_t bits) { return __brev(x) >> (32 - bits); }
@@ -209,6 +210,8 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
     Fr *data = reinterpret_cast<Fr *>(ntt_smem);
     Fr *stw = data + (size_t)T * vstride; // R/2 sub-transform twiddles
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    in += (size_t)blockIdx.y * p.batch_stride;
+    out += (size_t)blockIdx.y * p.batch_stride;
 
     // tile -> (beta0, u0)
     uint32_t beta0, u0;
@@ -436,21 +439,23 @@ inline uint32_t ntt_pick_T(uint32_t logR, uint32_t n_avail)
     return T ? T : 1;
 }
 
-inline cudaError_t ntt_run_pass(const Fr *in, Fr *out, const Fr *tw, NttPass p, cudaStream_t st)
+inline cudaError_t ntt_run_pass(const Fr *in, Fr *out, const Fr *tw, NttPass p, cudaStream_t st, uint32_t batch = 1)
 {
     size_t smem = ntt_pass_smem(p.logR, p.T);
     p.stw_global = p.logR >= 12;
     cudaError_t e = cudaFuncSetAttribute(k_ntt_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
     uint64_t tiles = (uint64_t)p.n_batch * p.n_inner / p.T;
-    k_ntt_pass<<<(unsigned)tiles, 256, smem, st>>>(in, out, tw, p);
+    k_ntt_pass<<<dim3((unsigned)tiles, batch), 256, smem, st>>>(in, out, tw, p);
     return cudaGetLastError();
 }
 
 // In-place (result back in `a`) transform of 2^log_m elements; `tmp` is a same-sized
 // scratch vector. flags: bit0 inverse, bit1 coset (host pointer coset_g, Montgomery).
+// batch > 1: the same transform of `batch` vectors stored back to back in a (and tmp), one launch per pass
+// (the three independent A / B / C chains of r1cs_to_qap_witness_map).
 inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, uint32_t flags, const Fr *coset_g,
-                              cudaStream_t st, unsigned *launches)
+                              cudaStream_t st, unsigned *launches, uint32_t batch = 1)
 {
     const uint32_t inverse = flags & 1u, coset = (flags >> 1) & 1u;
     const size_t m = (size_t)1 << log_m;
@@ -472,6 +477,7 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
     NttPass p{};
     p.log_m = log_m;
     p.inverse = inverse;
+    p.batch_stride = m;
     if (log_m <= 11) {
         p.logR = log_m;
         p.T = 1;
@@ -485,10 +491,10 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.sub_tw_stride = 1;
         p.in_scale_tab = in_tab; p.isc_sr = 1;
         p.scale_tab = out_tab; p.sc_sr = 1;
-        e = ntt_run_pass(a, tmp, tw, p, st);
+        e = ntt_run_pass(a, tmp, tw, p, st, batch);
         if (e != cudaSuccess) return e;
         (*launches)++;
-        e = cudaMemcpyAsync(a, tmp, m * sizeof(Fr), cudaMemcpyDeviceToDevice, st);
+        e = cudaMemcpyAsync(a, tmp, (size_t)batch * m * sizeof(Fr), cudaMemcpyDeviceToDevice, st);
         if (e != cudaSuccess) return e;
     } else if (log_m <= 22) {
         const uint32_t l1 = (log_m + 1) / 2, l2 = log_m - l1;
@@ -506,7 +512,7 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.tw_mul = 1;
         p.sub_tw_stride = m2; // w_m1 = w_m^m2
         p.in_scale_tab = in_tab; p.isc_sv = 1; p.isc_sr = m2;
-        e = ntt_run_pass(a, tmp, tw, p, st);
+        e = ntt_run_pass(a, tmp, tw, p, st, batch);
         if (e != cudaSuccess) return e;
         p.in_scale_tab = nullptr;
         // pass 2: rows. vector beta = k1 < m1, element r = j2: in = beta*m2 + r ; out = beta + k*m1
@@ -521,7 +527,7 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.tw_post = 0;
         p.sub_tw_stride = m1; // w_m2 = w_m^m1
         p.scale_tab = out_tab; p.sc_bs = 1; p.sc_sr = m1;
-        e = ntt_run_pass(tmp, a, tw, p, st);
+        e = ntt_run_pass(tmp, a, tw, p, st, batch);
         if (e != cudaSuccess) return e;
         *launches += 2;
     } else {
@@ -541,7 +547,7 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.tw_mul = 1;
         p.sub_tw_stride = m2 * m3;
         p.in_scale_tab = in_tab; p.isc_sv = 1; p.isc_sr = m2 * m3;
-        e = ntt_run_pass(a, tmp, tw, p, st);
+        e = ntt_run_pass(a, tmp, tw, p, st, batch);
         if (e != cudaSuccess) return e;
         p.in_scale_tab = nullptr;
         // pass 2: inside each row beta = k1, length-m2 transforms down columns of m2 x m3
@@ -556,7 +562,7 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.tw_post = 1;
         p.tw_mul = m1; // w_(m2 m3) = w_m^m1
         p.sub_tw_stride = m1 * m3;
-        e = ntt_run_pass(tmp, tmp, tw, p, st);
+        e = ntt_run_pass(tmp, tmp, tw, p, st, batch);
         if (e != cudaSuccess) return e;
         // pass 3: rows (k1, k2) of length m3: in = k1*m2*m3 + k2*m3 + r ; out = k1 + k2*m1 + k*m1*m2
         p.logR = l3;
@@ -570,7 +576,7 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
         p.tw_post = 0;
         p.sub_tw_stride = m1 * m2;
         p.scale_tab = out_tab; p.sc_bs = 1; p.sc_sv = m1; p.sc_sr = m1 * m2;
-        e = ntt_run_pass(tmp, a, tw, p, st);
+        e = ntt_run_pass(tmp, a, tw, p, st, batch);
         if (e != cudaSuccess) return e;
         *launches += 3;
     }

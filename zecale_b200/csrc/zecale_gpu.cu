@@ -460,11 +460,11 @@ int msm_host(zecale_gpu_ctx *ctx, const void *bases, size_t bstride, const void 
     return msm_device(ctx, d_aff, d_inf, 0, 0, (uint32_t)n, d_sc, sstride, d_idx, n, out, nullptr);
 }
 
-// NTT on a device vector, no locking, no sync; timed as kernel class 1.
-int ntt_device(zecale_gpu_ctx *ctx, Fr *d_a, unsigned log_m, unsigned flags, const Fr *coset_g)
+// NTT on a device vector (or `batch` vectors back to back), no locking, no sync; timed as kernel class 1.
+int ntt_device(zecale_gpu_ctx *ctx, Fr *d_a, unsigned log_m, unsigned flags, const Fr *coset_g, uint32_t batch = 1)
 {
     size_t m = (size_t)1 << log_m;
-    int rc = reserve(ctx, ctx->cur->ws_ntt, m * sizeof(Fr));
+    int rc = reserve(ctx, ctx->cur->ws_ntt, (size_t)batch * m * sizeof(Fr));
     if (rc) return rc;
     unsigned nl = 0;
     // tables are built (and synchronised) before the timed region
@@ -472,7 +472,7 @@ int ntt_device(zecale_gpu_ctx *ctx, Fr *d_a, unsigned log_m, unsigned flags, con
     CK(ntt_get_twiddles(ctx->ntt, log_m, ctx->cur->stream, &tw, &nl));
     cudaEvent_t e0 = take_event(ctx), e1 = take_event(ctx);
     CK(cudaEventRecord(e0, ctx->cur->stream));
-    CK(ntt_launch(ctx->ntt, d_a, (Fr *)ctx->cur->ws_ntt.p, log_m, flags, coset_g, ctx->cur->stream, &nl));
+    CK(ntt_launch(ctx->ntt, d_a, (Fr *)ctx->cur->ws_ntt.p, log_m, flags, coset_g, ctx->cur->stream, &nl, batch));
     CK(cudaEventRecord(e1, ctx->cur->stream));
     ctx->ev_pending[1].emplace_back(e0, e1);
     if (ctx->ev_pending[1].size() > 256) drain_timers(ctx, false);
@@ -516,10 +516,16 @@ int qap_h_device(zecale_gpu_ctx *ctx, Fr *aA, Fr *aB, Fr *aC, unsigned log_m, co
     CK(cudaEventRecord(L.ev_hand, L.stream));
     CK(cudaStreamWaitEvent(L.hi, L.ev_hand, 0));
     std::swap(L.stream, L.hi);
-    Fr *v[3] = {aA, aB, aC};
-    for (int k = 0; k < 3 && rc == 0; k++) {
-        rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_INVERSE, nullptr);
-        if (rc == 0) rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_COSET, g);
+    if (aB == aA + m && aC == aB + m) {
+        // the three chains are independent and sit back to back: one launch per pass for all of them
+        rc = ntt_device(ctx, aA, log_m, ZECALE_GPU_NTT_INVERSE, nullptr, 3);
+        if (rc == 0) rc = ntt_device(ctx, aA, log_m, ZECALE_GPU_NTT_COSET, g, 3);
+    } else {
+        Fr *v[3] = {aA, aB, aC};
+        for (int k = 0; k < 3 && rc == 0; k++) {
+            rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_INVERSE, nullptr);
+            if (rc == 0) rc = ntt_device(ctx, v[k], log_m, ZECALE_GPU_NTT_COSET, g);
+        }
     }
     if (rc == 0) {
         k_qap_pointwise<<<(unsigned)((m + 255) / 256), 256, 0, L.stream>>>(aA, aB, aC, zinv, m);
