@@ -254,6 +254,15 @@ int zecale_gpu_synth_bases(zecale_gpu_ctx *ctx, int group, uint64_t seed, size_t
 int zecale_gpu_batch_exp(zecale_gpu_ctx *ctx, int group, const void *base_point, const void *scalars, size_t scalar_stride,
                          size_t n, const void *coeff, void *out_points);
 
+/* ---- Lagrange basis at a point (the QAP instance evaluation of the trusted setup) ----
+ * out[i] = L_i(t), i < m = 2^log_m, for the domain of m-th roots of unity: replaces
+ * libfqfft::basic_radix2_domain<Fr>::evaluate_all_lagrange_polynomials (basic_radix2_domain.tcc:91-94 ->
+ * _basic_radix2_evaluate_all_lagrange_polynomials, basic_radix2_domain_aux.tcc:186-239: m serial field
+ * inversions), called by r1cs_to_qap_instance_map_with_evaluation (r1cs_to_qap.tcc:102-108) once per
+ * setup. t: one Fr (Montgomery); out: m Fr. HOST pointers. Returns ZECALE_GPU_E_DOMAIN when t is itself a
+ * point of the domain (the unit-vector case, :203-217) - the caller keeps the reference's code for that. */
+int zecale_gpu_lagrange(zecale_gpu_ctx *ctx, unsigned log_m, const void *t, void *out);
+
 /* ---- introspection ----------------------------------------------------------------*/
 /* Number of kernel launches issued by this context so far (bench.py gpu_launches). */
 uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx);

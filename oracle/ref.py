@@ -37,7 +37,7 @@ class Ref:
         for f in ("zref_msm_g1", "zref_msm_g2", "zref_msm_g1_naive", "zref_msm_kc", "zref_ntt", "zref_qap_h",
                   "zref_session_setup", "zref_session_prove_stock", "zref_session_witness_map",
                   "zref_session_witness_gen_seconds", "zref_session_prove_pipeline", "zref_session_prove_threads",
-                  "zref_session_keypair_write", "zref_session_keypair_read"):
+                  "zref_session_keypair_write", "zref_session_keypair_read", "zref_lagrange"):
             getattr(L, f).restype = _d
         L.zref_fr_signed_digit.restype = ctypes.c_long
         L.zref_session_abc.restype = ctypes.c_long
@@ -153,6 +153,12 @@ class Ref:
         if t < 0:
             raise RuntimeError("reference NTT threw")
         return out, t
+
+    def lagrange(self, log_m, t):
+        """libfqfft evaluate_all_lagrange_polynomials(t) on the size-2^log_m domain; (u (m, 6), seconds)."""
+        out = np.zeros((1 << log_m, 6), dtype=np.uint64)
+        secs = self.L.zref_lagrange(ctypes.c_uint(log_m), _p(np.ascontiguousarray(t)), _p(out))
+        return out, secs
 
     def qap_h(self, aA, aB, aC):
         """coefficients_for_H (m+1, 6) by the reference's own transform sequence; returns (h, seconds)."""

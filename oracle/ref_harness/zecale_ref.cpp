@@ -546,6 +546,21 @@ extern "C" double zref_qap_h(const void *aA_, const void *aB_, const void *aC_, 
     return t1 - t0;
 }
 
+// evaluate_all_lagrange_polynomials(t) of the size-2^log_m domain through get_evaluation_domain (so the
+// hooked build exercises the device version); out receives m elements. Returns seconds.
+extern "C" double zref_lagrange(unsigned log_m, const void *t48, void *out)
+{
+    const size_t m = (size_t)1 << log_m;
+    Fr t;
+    std::memcpy((void *)&t, t48, 48);
+    const std::shared_ptr<libfqfft::evaluation_domain<Fr>> domain = libfqfft::get_evaluation_domain<Fr>(m);
+    const double t0 = now_s();
+    const std::vector<Fr> u = domain->evaluate_all_lagrange_polynomials(t);
+    const double t1 = now_s();
+    copy_out(out, u);
+    return t1 - t0;
+}
+
 // omega for the size-2^log_m domain (field_utils.tcc:190-206); (g^m - 1)^-1 helper.
 extern "C" void zref_domain_params(unsigned log_m, void *omega, void *z_inv_on_coset)
 {

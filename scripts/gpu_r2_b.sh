@@ -1,7 +1,7 @@
 #!/bin/bash
 # Single-GPU evidence pass: parity of the batched transforms, bench, sanitizer logs, ncu captures.
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_ntt_gpu.py tests/test_prove_gpu.py tests/test_golden_gpu.py tests/test_hooks_gpu.py -m gpu -x -q -k "not batch32 and not large" > gpurun_out/pytest_b.log 2>&1; rc=$?; echo "pytest rc=$rc" >> gpurun_out/pytest_b.log
+timeout 900 python -m pytest tests/test_ntt_gpu.py tests/test_batch_exp_gpu.py tests/test_prove_gpu.py tests/test_golden_gpu.py tests/test_hooks_gpu.py -m gpu -x -q -k "not batch32 and not large" > gpurun_out/pytest_b.log 2>&1; rc=$?; echo "pytest rc=$rc" >> gpurun_out/pytest_b.log
 tail -6 gpurun_out/pytest_b.log
 [ $rc -ne 0 ] && exit 1
 timeout 600 python bench.py --steps 10 --warmup 3 --skip-cpu-baseline > gpurun_out/bench_b.json 2> gpurun_out/bench_b.err; echo "bench rc=$?"

@@ -50,3 +50,20 @@ def test_batch_exp_zero_base_and_generator(gpu, ref):
     assert np.array_equal(gpu.batch_exp(zero, scalars, 1), ref.batch_exp(zero, scalars, 1))
     # s * G for the generator equals the harness's own scalar multiplications
     assert np.array_equal(gpu.batch_exp(gen, scalars, 1), ref.bases_mul(scalars, 1))
+
+
+@pytest.mark.parametrize("log_m", [1, 5, 12, 16, 18])
+def test_lagrange_vs_libfqfft(gpu, ref, log_m):
+    """zecale_gpu_lagrange == basic_radix2_domain::evaluate_all_lagrange_polynomials
+    (basic_radix2_domain_aux.tcc:186-239), the m inversions of the setup's QAP instance evaluation."""
+    import zecale_b200 as z
+    t = ref.fr_rng(0x7A6 + log_m, 1)[0]
+    exp, _ = ref.lagrange(log_m, t)
+    assert np.array_equal(gpu.lagrange(log_m, t), exp)
+    # t on the domain: the unit-vector case stays with the reference's code
+    e1 = np.zeros((1 << log_m, 6), dtype=np.uint64)
+    e1[1] = ref.fr_from_ints([1])[0]
+    w = ref.ntt(e1, 0)[0][1]          # FFT(e_1) = (1, w, w^2, ...): w is a point of the domain
+    with pytest.raises(z.ZecaleGpuError) as e:
+        gpu.lagrange(log_m, w)
+    assert e.value.code == 4

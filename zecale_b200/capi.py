@@ -72,6 +72,7 @@ EXPORTS = {
     "zecale_gpu_synth_bases": (_i, [_vp, _i, ctypes.c_uint64, _sz, _vp]),
     "zecale_gpu_pin_bases_bytes": (_i, [_vp, _vp, _sz, _sz, _i, _i, ctypes.POINTER(_vp)]),
     "zecale_gpu_batch_exp": (_i, [_vp, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
+    "zecale_gpu_lagrange": (_i, [_vp, _u, _vp, _vp]),
     "zecale_gpu_kernel_ms": (_i, [_vp, _i, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]),
     "zecale_gpu_launch_count": (ctypes.c_uint64, [_vp]),
     "zecale_gpu_msm_window_bits": (_u, [_sz]),
@@ -321,6 +322,12 @@ class Context:
         cf = np.ascontiguousarray(coeff) if coeff is not None else None
         self._ck(_lib.zecale_gpu_batch_exp(self._h, group, _ptr(base), _ptr(scalars) if n else None, 48, n,
                                            _ptr(cf) if cf is not None else None, _ptr(out)))
+        return out
+
+    def lagrange(self, log_m, t):
+        """All Lagrange basis polynomials of the size-2^log_m domain evaluated at t: (m, 6) uint64."""
+        out = np.zeros((1 << log_m, 6), dtype=np.uint64)
+        self._ck(_lib.zecale_gpu_lagrange(self._h, log_m, _ptr(np.ascontiguousarray(t)), _ptr(out)))
         return out
 
     def kernel_ms(self, kernel_class, reset=True):

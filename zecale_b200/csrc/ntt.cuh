@@ -583,6 +583,67 @@ inline cudaError_t ntt_launch(NttTables &tabs, Fr *a, Fr *tmp, uint32_t log_m, u
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ Lagrange basis at a point (setup generator)
+// u[i] = L_i(t) for the domain of m = 2^log_m roots of unity: libfqfft's
+// _basic_radix2_evaluate_all_lagrange_polynomials (basic_radix2_domain_aux.tcc:186-239),
+//     u[i] = Z(t) / m * w^i / (t - w^i),   Z(t) = t^m - 1,
+// which the reference computes with m serial field inversions (r1cs_to_qap_instance_map_with_evaluation,
+// called once per trusted setup, r1cs_gg_ppzksnark.tcc:243-247). Here: one thread per LAGRANGE_CHUNK
+// consecutive i, the chunk's denominators inverted together (Montgomery's trick, one Fermat inversion).
+// seed[0] = Z(t)/m, seed[1] = t, flag = 1 if t^m == 1 (t is a domain point: the caller falls back).
+static constexpr uint32_t LAGRANGE_CHUNK = 32;
+
+__global__ void k_lagrange_seed(Fr t, uint32_t log_m, Fr *seed, int *flag)
+{
+    uint32_t x[12], one[12], mm[12], two[12];
+    fr_load(x, &t);
+    fr_set_const(one, FR_ONE);
+    for (uint32_t i = 0; i < log_m; i++) fr_sqr_regs(x, x); // t^m
+    fr_sub_regs(x, x, one);
+    uint32_t nz = 0;
+#pragma unroll
+    for (int k = 0; k < 12; k++) nz |= x[k];
+    *flag = nz == 0;
+    fr_add_regs(two, one, one);
+    fr_set_const(mm, FR_ONE);
+    for (uint32_t i = 0; i < log_m; i++) fr_mul_regs(mm, mm, two);
+    fr_inv(mm, mm);
+    fr_mul_regs(x, x, mm);
+    fr_store(seed, x);
+    fr_store(seed + 1, t.l);
+}
+
+__global__ void __launch_bounds__(128) k_lagrange(const Fr *__restrict__ tw, uint32_t log_m, const Fr *seed, Fr *out)
+{
+    const size_t m = (size_t)1 << log_m;
+    const size_t i0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * LAGRANGE_CHUNK;
+    if (i0 >= m) return;
+    const uint32_t cnt = (uint32_t)(m - i0 < LAGRANGE_CHUNK ? m - i0 : LAGRANGE_CHUNK);
+    uint32_t t[12], acc[12], w[12], d[12];
+    fr_load(t, seed + 1);
+    fr_set_const(acc, FR_ONE);
+    for (uint32_t j = 0; j < cnt; j++) { // forward: out[i] = product of the denominators before i
+        fr_store(out + i0 + j, acc);
+        ntt_twiddle(w, tw, i0 + j, log_m, 0);
+        fr_sub_regs(d, t, w);
+        fr_mul_regs(acc, acc, d);
+    }
+    fr_inv(acc, acc); // != 0: t is not a domain point
+    uint32_t l0[12];
+    fr_load(l0, seed);
+    for (uint32_t j = cnt; j-- > 0;) { // backward
+        uint32_t pre[12], u[12];
+        fr_load(pre, out + i0 + j);
+        fr_mul_regs(u, acc, pre); // 1 / (t - w^i)
+        ntt_twiddle(w, tw, i0 + j, log_m, 0);
+        fr_sub_regs(d, t, w);
+        fr_mul_regs(acc, acc, d);
+        fr_mul_regs(u, u, w);
+        fr_mul_regs(u, u, l0);
+        fr_store(out + i0 + j, u);
+    }
+}
+
 // ------------------------------------------------------------------ distributed 4-step
 // One transform of m = m1*m2 elements over `world` ranks (a power of two dividing m1 and m2) with
 // ONE exchange. Layouts of the distributed vector (c1 = m1/world, c2 = m2/world):

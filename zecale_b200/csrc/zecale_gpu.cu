@@ -1525,6 +1525,37 @@ int zecale_gpu_qap_pointwise_dev(zecale_gpu_ctx *ctx, void *d_aA, const void *d_
     return 0;
 }
 
+int zecale_gpu_lagrange(zecale_gpu_ctx *ctx, unsigned log_m, const void *t, void *out)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!t || !out) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_lagrange: bad argument");
+    if (log_m < 1 || log_m > 28) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_lagrange: log_m %u out of range", log_m);
+    CK(cudaSetDevice(ctx->device));
+    const size_t m = (size_t)1 << log_m;
+    cudaStream_t st = ctx->cur->stream;
+    unsigned nl = 0;
+    const Fr *tw = nullptr;
+    CK(ntt_get_twiddles(ctx->ntt, log_m, st, &tw, &nl));
+    int rc = reserve(ctx, ctx->ws_in, m * sizeof(Fr) + 2 * sizeof(Fr));
+    if (rc) return rc;
+    Fr *d_out = (Fr *)ctx->ws_in.p, *d_seed = d_out + m;
+    Fr tv;
+    memcpy(tv.l, t, sizeof(Fr));
+    k_lagrange_seed<<<1, 1, 0, st>>>(tv, log_m, d_seed, ctx->d_status);
+    int flag = 0;
+    CK(cudaMemcpyAsync(&flag, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, st));
+    const size_t threads = (m + LAGRANGE_CHUNK - 1) / LAGRANGE_CHUNK;
+    k_lagrange<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(tw, log_m, d_seed, d_out);
+    ctx->launches += nl + 2;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+    if (flag) return fail(ctx, ZECALE_GPU_E_DOMAIN, "zecale_gpu_lagrange: t is a point of the domain");
+    CK(cudaMemcpy(out, d_out, m * sizeof(Fr), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 int zecale_gpu_lane_count(void) { return ZECALE_GPU_LANES; }
 
 int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_bases *h, const void *scalars,

@@ -333,9 +333,15 @@ public:
     {
         run(a, ZECALE_GPU_NTT_INVERSE | ZECALE_GPU_NTT_COSET, &g);
     }
+    /// The m Lagrange coefficients at t (the QAP instance evaluation of the setup): batched inversions on
+    /// the device instead of m serial ones; t on the domain itself keeps the reference's code.
     std::vector<Fr> evaluate_all_lagrange_polynomials(const Fr &t) override
     {
-        return cpu_.evaluate_all_lagrange_polynomials(t);
+        std::vector<Fr> u(this->m, Fr::zero());
+        const int rc = zecale_gpu_lagrange(context(), (unsigned)log_m_, &t, u.data());
+        if (rc == ZECALE_GPU_E_DOMAIN) return cpu_.evaluate_all_lagrange_polynomials(t);
+        check(rc, "zecale_gpu_lagrange");
+        return u;
     }
     Fr get_domain_element(const size_t idx) override { return cpu_.get_domain_element(idx); }
     Fr compute_vanishing_polynomial(const Fr &t) override { return cpu_.compute_vanishing_polynomial(t); }
@@ -442,9 +448,27 @@ ZECALE_GPU_MSM_SPECIALISE(multi_exp_filter_one_zero, bw6_761_G2, ZECALE_GPU_G2)
 
 // Fixed-base exponentiations of the trusted setup (r1cs_gg_ppzksnark_generator, r1cs_gg_ppzksnark.tcc:
 // 349-398: A, H, L queries and gamma_ABC): batch_exp (multiexp.tcc:887-916) and batch_exp_with_coeff
-// (:918-947). The CPU window table is only read for the base point (table[0][1] = 1 * g); the device
-// builds its own table. Points come back in special form, which the generator's following
-// batch_to_special leaves unchanged. (kc_batch_exp for the B query keeps its CPU loop.)
+// (:918-947). The device builds its own window table, so the CPU one (get_window_table,
+// multiexp.tcc:809-845: millions of serial point additions per setup) shrinks to {0, g}: every reader
+// of a window_table in the reference - batch_exp, batch_exp_with_coeff, kc_batch_exp and windowed_exp -
+// is specialised here and only needs the base point table[0][1]. Points come back in special form,
+// which the generator's following batch_to_special leaves unchanged.
+#define ZECALE_GPU_WINDOW_TABLE_SPECIALISE(GROUP)                                                       \
+    template<>                                                                                         \
+    inline window_table<GROUP> get_window_table<GROUP>(const size_t, const size_t, const GROUP &g)     \
+    {                                                                                                  \
+        return window_table<GROUP>(1, std::vector<GROUP>{GROUP::zero(), g});                           \
+    }                                                                                                  \
+    template<>                                                                                         \
+    inline GROUP windowed_exp<GROUP, bw6_761_Fr>(                                                      \
+        const size_t, const size_t, const window_table<GROUP> &table, const bw6_761_Fr &pow)           \
+    {                                                                                                  \
+        return pow * table[0][1];                                                                      \
+    }
+ZECALE_GPU_WINDOW_TABLE_SPECIALISE(bw6_761_G1)
+ZECALE_GPU_WINDOW_TABLE_SPECIALISE(bw6_761_G2)
+#undef ZECALE_GPU_WINDOW_TABLE_SPECIALISE
+
 #define ZECALE_GPU_BATCH_EXP_SPECIALISE(GROUP, GID)                                                    \
     template<>                                                                                         \
     inline std::vector<GROUP> batch_exp<GROUP, bw6_761_Fr>(                                            \
