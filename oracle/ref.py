@@ -37,7 +37,8 @@ class Ref:
         for f in ("zref_msm_g1", "zref_msm_g2", "zref_msm_g1_naive", "zref_msm_kc", "zref_ntt", "zref_qap_h",
                   "zref_session_setup", "zref_session_prove_stock", "zref_session_witness_map",
                   "zref_session_witness_gen_seconds", "zref_session_prove_pipeline", "zref_session_prove_threads",
-                  "zref_session_keypair_write", "zref_session_keypair_read", "zref_lagrange"):
+                  "zref_session_keypair_write", "zref_session_keypair_read", "zref_lagrange",
+                  "zref_session_witness_gen_parallel_seconds"):
             getattr(L, f).restype = _d
         L.zref_fr_signed_digit.restype = ctypes.c_long
         L.zref_session_abc.restype = ctypes.c_long
@@ -210,6 +211,13 @@ class Ref:
 
     def session_witness_gen_seconds(self):
         return float(self.L.zref_session_witness_gen_seconds())
+
+    def session_witness_gen_parallel(self):
+        """(seconds, threads) of the per-nested-proof parallel witness generation prototype of the last
+        aggregator session; seconds < 0 means it did not reproduce the serial assignment."""
+        n = ctypes.c_int()
+        t = self.L.zref_session_witness_gen_parallel_seconds(ctypes.byref(n))
+        return float(t), int(n.value)
 
     def session_sizes(self):
         sz = np.zeros(16, dtype=np.uint64)

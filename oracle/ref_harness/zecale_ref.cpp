@@ -87,8 +87,11 @@ struct session_t {
     double t_witness_map = 0, t_msm_a = 0, t_msm_b = 0, t_msm_h = 0,
            t_msm_l = 0, t_total = 0;
     // aggregator sessions: seconds spent in the generate_r1cs_witness statements of
-    // aggregator_circuit::prove (aggregator_circuit.tcc:136-157), i.e. SURVEY 8(f2)
-    double t_witness_gen = 0;
+    // aggregator_circuit::prove (aggregator_circuit.tcc:136-157), i.e. SURVEY 8(f2); and the same
+    // statements with the two per-nested-proof loops spread over host threads (prototype; -1 = the
+    // parallel run did not reproduce the serial assignment)
+    double t_witness_gen = 0, t_witness_gen_parallel = 0;
+    int witness_gen_threads = 0;
 };
 
 std::unique_ptr<session_t> S_ptr(new session_t());
@@ -657,6 +660,33 @@ template<size_t N> static int aggregator_session(uint64_t seed)
     const double tw1 = now_s();
 
     S.t_witness_gen = tw1 - tw0;
+    // SURVEY 8(f2) prototype: the N nested proofs are witnessed independently (aggregator_circuit.tcc:136-146,
+    // aggregator_gadget.tcc:94-111: disjoint protoboard variables, the shared processed verification key is
+    // only read), so both loops run one nested proof per host thread. Must reproduce the serial assignment.
+    {
+        const std::vector<Fr> serial = agg._pb.full_variable_assignment();
+        auto &gad = *agg._aggregator_gadget;
+        const int nt = std::min<int>((int)N, threads());
+        const double tp0 = now_s();
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+        for (size_t i = 0; i < N; ++i)
+            agg._nested_proofs[i]->generate_r1cs_witness(batch[i]->get_proof());
+        agg._nested_vk->generate_r1cs_witness(nkp.vk);
+        agg._nested_vk_hash_gadget->generate_r1cs_witness();
+        gad.vk_processor.generate_r1cs_witness();
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+        for (size_t i = 0; i < N; ++i) {
+            const libff::bit_vector input_bits =
+                libff::convert_field_element_vector_to_bit_vector<libff::Fr<npp>>(*(nested_inputs[i]));
+            gad.nested_primary_inputs_bits[i].fill_with_bits(agg._pb, input_bits);
+            gad.nested_primary_input_packers[i]->generate_r1cs_witness_from_bits();
+            gad.verifiers[i]->generate_r1cs_witness();
+        }
+        agg._nested_proof_results_packer->generate_r1cs_witness_from_bits();
+        const double tp1 = now_s();
+        S.witness_gen_threads = nt;
+        S.t_witness_gen_parallel = agg._pb.full_variable_assignment() == serial ? tp1 - tp0 : -1.0;
+    }
     S.cs = agg.get_constraint_system();
     S.primary = agg._pb.primary_input();
     S.aux = agg._pb.auxiliary_input();
@@ -685,6 +715,12 @@ extern "C" int zref_session_aggregator(size_t batch, uint64_t seed)
 }
 
 extern "C" double zref_session_witness_gen_seconds(void) { return S.t_witness_gen; }
+extern "C" double zref_session_witness_gen_parallel_seconds(int *threads_used)
+{
+    if (threads_used)
+        *threads_used = S.witness_gen_threads;
+    return S.t_witness_gen_parallel;
+}
 
 // A session whose constraint system is given as three CSR matrices (row i of matrix k =
 // constraints[i].{a,b,c}.terms; col 0 = the constant one) and whose assignment is `full` =

@@ -133,7 +133,12 @@ def test_hooked_reference_prover_aggregator_batch8(pair, capsys):
                   "host assembly + serialisation included); 2 threads x 3 proofs concurrently: %.3f s = %.1f proofs/s; witness generation "
                   "(aggregator_circuit::prove's generate_r1cs_witness calls, reference CPU code, 1 thread): %.3f s"
                   % (k, secs, k / secs, tsecs, 6 / tsecs, cpu.session_witness_gen_seconds()))
+            tpar, nthr = cpu.session_witness_gen_parallel()
+            print("[batch-8 aggregator, SURVEY 8(f2)] witness generation, one nested proof per host thread (%d threads): %.3f s, same "
+                  "assignment; so a whole aggregator_circuit::prove = witness generation %.3f s (serial) / %.3f s (parallel) + hooked prover %.3f s"
+                  % (nthr, tpar, cpu.session_witness_gen_seconds(), tpar, t_fused))
         assert k / secs > 15.0
+        assert cpu.session_witness_gen_parallel()[0] > 0, "parallel witness generation did not reproduce the serial assignment"
     finally:
         hooked.hooks_unpin()
 
