@@ -274,8 +274,11 @@ int zecale_gpu_kernel_ms(zecale_gpu_ctx *ctx, int kernel_class, int reset, doubl
  * window bits, bucket sets V and base copies G. Mixed additions executed = entries - tasks. */
 int zecale_gpu_msm_last_stats(zecale_gpu_ctx *ctx, uint64_t *entries, uint64_t *tasks, unsigned *c,
                               unsigned *bucket_sets, unsigned *base_copies);
-/* Window size c the MSM uses for n points (for the roofline op count). */
+/* Window size c an MSM over n points uses: the un-pinned calls (zecale_gpu_msm_g1/g2: bases uploaded per call,
+ * one shared set of doublings at the end) and the pinned ones (zecale_gpu_pin_bases with expand = 1: pre-shifted
+ * copies, cost-model choice; what zecale_gpu_msm_last_stats reports after such a call). */
 unsigned zecale_gpu_msm_window_bits(size_t n);
+unsigned zecale_gpu_msm_window_bits_pinned(size_t n);
 
 /* ---- unit-test / microbenchmark hooks (not used by the prover) --------------------
  * Element-wise field and group operations on host arrays, executed by the same

@@ -19,4 +19,9 @@ cap() { # name regex count
 cap accumulate k_accumulate 2
 cap tail k_tail_level 3
 cap ntt k_ntt_pass 2
-echo done
+echo done1
+# --- BASELINE configs 2 and 3 as tables, and the CPU-baseline variants
+timeout 1500 python scripts/sweep.py --cpu 2> gpurun_out/sweep.err | grep '^{' > gpurun_out/msm_ntt_sweep.jsonl; echo "sweep rc=${PIPESTATUS[0]}"; tail -3 gpurun_out/sweep.err
+timeout 900 python scripts/cpu_variants.py 2> gpurun_out/cpu_variants.err | grep '^{' > gpurun_out/cpu_baseline_variants.jsonl; echo "variants rc=${PIPESTATUS[0]}"
+cat gpurun_out/cpu_baseline_variants.jsonl | cut -c1-200
+echo done2

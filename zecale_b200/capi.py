@@ -76,6 +76,7 @@ EXPORTS = {
     "zecale_gpu_kernel_ms": (_i, [_vp, _i, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]),
     "zecale_gpu_launch_count": (ctypes.c_uint64, [_vp]),
     "zecale_gpu_msm_window_bits": (_u, [_sz]),
+    "zecale_gpu_msm_window_bits_pinned": (_u, [_sz]),
     "zecale_gpu_test_fq": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
     "zecale_gpu_test_fr": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
     "zecale_gpu_test_group": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
@@ -361,5 +362,5 @@ class Context:
         return ms.value
 
 
-def msm_window_bits(n):
-    return int(_lib.zecale_gpu_msm_window_bits(n))
+def msm_window_bits(n, pinned=False):
+    return int((_lib.zecale_gpu_msm_window_bits_pinned if pinned else _lib.zecale_gpu_msm_window_bits)(n))

@@ -1926,6 +1926,7 @@ uint64_t zecale_gpu_launch_count(zecale_gpu_ctx *ctx)
 int zecale_gpu_device_count(zecale_gpu_ctx *ctx) { return ctx ? (int)ctx->devices.size() : 0; }
 
 unsigned zecale_gpu_msm_window_bits(size_t n) { return n ? msm_default_c((uint32_t)n) : 0; }
+unsigned zecale_gpu_msm_window_bits_pinned(size_t n) { return n ? pinned_c(n) : 0; }
 
 int zecale_gpu_test_fq(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n)
 {
