@@ -1,7 +1,7 @@
 """Summarise ncu outputs under gpurun_out/ into small text files under profiles/ (tracked).
 
   python tools/ncu_summary.py launches gpurun_out/launches.csv profiles/r01_launches.md "title"
-  python tools/ncu_summary.py raw gpurun_out/prof_x.ncu-rep profiles/r01_x_raw.md "title"
+  python tools/ncu_summary.py raw gpurun_out/prof_x.ncu-rep|prof_x_raw.csv profiles/r01_x_raw.md "title"
 """
 import collections
 import csv
@@ -60,7 +60,10 @@ def launches(src, dst, title):
 
 
 def raw(src, dst, title):
-    out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if src.endswith(".csv"):   # exported on the GPU box: ncu -i x.ncu-rep --page raw --csv > x_raw.csv
+        out = open(src).read()
+    else:
+        out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
     ki = hdr.index("Kernel Name")

@@ -27,8 +27,22 @@ def is_stale():
     return any(os.path.getmtime(s) > t for s in sources())
 
 
-def build(force=False, verbose=False):
-    """Compile the CUDA library if it is missing or older than its sources."""
+LIB_CHECKED = os.path.join(HERE, "libzecale_gpu_checked.so")
+
+
+def build(force=False, verbose=False, checked=False):
+    """Compile the CUDA library if it is missing or older than its sources. checked=True builds
+    libzecale_gpu_checked.so with -DZECALE_GPU_CHECKED (device-side range checks on every index, fqvm.cuh ZG_CHECK);
+    load it with ZECALE_GPU_LIB=<path> (zecale_b200/capi.py)."""
+    if checked:
+        cmd = [NVCC] + FLAGS + ["-DZECALE_GPU_CHECKED", "-o", LIB_CHECKED, SRC]
+        env = dict(os.environ)
+        env.pop("CXX", None)
+        env.pop("CC", None)
+        r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+        return LIB_CHECKED
     if not force and not is_stale():
         return LIB
     cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, SRC]
@@ -45,4 +59,4 @@ def build(force=False, verbose=False):
 
 if __name__ == "__main__":
     import sys
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv))

@@ -15,7 +15,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libzecale_gpu.so")
+# ZECALE_GPU_LIB selects another build of the SAME library (the range-checked one, libzecale_gpu_checked.so)
+LIB_PATH = os.environ.get("ZECALE_GPU_LIB") or os.path.join(_HERE, "libzecale_gpu.so")
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

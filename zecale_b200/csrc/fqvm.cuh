@@ -31,6 +31,21 @@
 #include "fqvm_prog.cuh"
 #include "fq_inv.cuh"
 
+// Checked build (-DZECALE_GPU_CHECKED, `python -m zecale_b200.build --checked`): every index the sort, accumulate and
+// tail kernels form and every slot number the field VM decodes is range-checked on the device; a violation prints the site and traps the kernel. Stands in for
+// compute-sanitizer, which the B200 pool does not allow (profiles/r02_sanitizer.md). Compiles to nothing otherwise.
+#ifdef ZECALE_GPU_CHECKED
+#define ZG_CHECK(cond)                                                                                          \
+    do {                                                                                                        \
+        if (!(cond)) {                                                                                          \
+            printf("ZG_CHECK failed: %s (%s:%d, block %u thread %u)\n", #cond, __FILE__, __LINE__, blockIdx.x, threadIdx.x); \
+            __trap();                                                                                           \
+        }                                                                                                       \
+    } while (0)
+#else
+#define ZG_CHECK(cond) ((void)0)
+#endif
+
 namespace zecale {
 
 struct alignas(16) Fq {
@@ -63,6 +78,7 @@ using FqSlots = FqSlotFile<VS_COUNT>;
 template <class SF>
 __device__ __forceinline__ void vs_load(uint32_t (&x)[24], const SF &S, uint32_t slot)
 {
+    ZG_CHECK(slot * 6 + 6 <= sizeof(S.w) / sizeof(uint4));
     const uint4 *p = S.w + slot * 6;
 #pragma unroll
     for (int k = 0; k < 6; k++) {
@@ -77,6 +93,7 @@ __device__ __forceinline__ void vs_load(uint32_t (&x)[24], const SF &S, uint32_t
 template <class SF>
 __device__ __forceinline__ void vs_store(SF &S, uint32_t slot, const uint32_t (&x)[24])
 {
+    ZG_CHECK(slot * 6 + 6 <= sizeof(S.w) / sizeof(uint4));
     uint4 *p = S.w + slot * 6;
 #pragma unroll
     for (int k = 0; k < 6; k++) p[k] = make_uint4(x[4 * k], x[4 * k + 1], x[4 * k + 2], x[4 * k + 3]);

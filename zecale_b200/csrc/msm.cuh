@@ -52,6 +52,8 @@ struct MsmPlan {
     uint32_t acc_mode;     // MSM_ACC_XYZZ | MSM_ACC_TREE
     uint32_t tree_rounds;  // pair-tree rounds launched = ceil(log2(n * G)) (a bucket holds <= n*G entries)
     uint32_t tree_min;     // rounds every bucket goes through before the XYZZ chains take over (k_tree_chain)
+    uint64_t n_entries;    // n * W: capacity of digits / entries
+    uint64_t n_bases;      // G * copy_stride: points of the (expanded) base image
 };
 
 // Bucket accumulation mode: ZECALE_GPU_ACC = "tree" (batched affine pair tree, k_tree_round) or
@@ -122,6 +124,8 @@ inline MsmPlan msm_make_plan(uint32_t n, uint32_t c, uint32_t V, uint32_t copy_s
     p.tree_min = msm_tree_min_rounds();
     p.n_buckets = (uint64_t)p.V * p.NB;
     p.max_tasks = ((uint64_t)n * p.W) / p.S + p.n_buckets + 1;
+    p.n_entries = (uint64_t)n * p.W;
+    p.n_bases = (uint64_t)p.G * copy_stride;
     return p;
 }
 
@@ -376,6 +380,7 @@ __global__ void k_digits(const uint8_t *scalars, size_t sstride, const uint64_t 
     for (uint32_t w = 0; w < p.W; w++) {
         uint32_t bit = w * c;
         uint32_t lo = bit >> 5, sh = bit & 31;
+        ZG_CHECK(lo + 1 < 14);
         uint64_t two = (uint64_t)v[lo] | ((uint64_t)v[lo + 1] << 32);
         uint32_t d = (uint32_t)(two >> sh) & mask;
         d += carry;
@@ -391,6 +396,7 @@ __global__ void k_digits(const uint8_t *scalars, size_t sstride, const uint64_t 
         digits[(size_t)w * p.n + i] = sd;
         if (sd != 0) {
             uint32_t b = (sd < 0 ? (uint32_t)(-sd) : (uint32_t)sd) - 1;
+            ZG_CHECK(b < p.NB);
             atomicAdd(&counts[(size_t)(w % p.V) * p.NB + b], 1u);
         }
     }
@@ -407,7 +413,9 @@ __global__ void k_scatter(MsmPlan p, const int32_t *digits, uint32_t *cursor, ui
     if (sd == 0) return;
     uint32_t neg = sd < 0;
     uint32_t b = (neg ? (uint32_t)(-sd) : (uint32_t)sd) - 1;
+    ZG_CHECK(b < p.NB);
     uint32_t pos = atomicAdd(&cursor[(size_t)(w % p.V) * p.NB + b], 1u);
+    ZG_CHECK(pos < p.n_entries && (uint64_t)(w / p.V) * p.copy_stride + i < p.n_bases);
     entries[pos] = ((w / p.V) * p.copy_stride + i) | (neg << 31);
 }
 
@@ -533,6 +541,7 @@ __global__ void k_task_fill(MsmPlan p, const uint32_t *counts, const uint32_t *o
     if (nt > 1) heavy_list[atomicAdd(heavy_count, 1u)] = (uint32_t)b; // folded by k_tail_fold
     uint64_t cnt = counts[b];
     uint32_t off = offsets[b];
+    ZG_CHECK((uint64_t)t0 + nt <= p.max_tasks && off + cnt <= p.n_entries && (nt > 0) == (cnt > 0));
     for (uint32_t k = 0; k < nt; k++) {
         uint32_t lo = (uint32_t)((cnt * k) / nt), hi = (uint32_t)((cnt * (k + 1)) / nt);
         task_start[t0 + k] = off + lo;
@@ -548,6 +557,7 @@ __global__ void k_task_order(const uint32_t *task_off_total, const uint32_t *tas
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= *task_off_total) return;
     uint32_t pos = atomicAdd(&len_cursor[msm_len_bin(task_len[t])], 1u);
+    ZG_CHECK(pos < *task_off_total);
     order[pos] = t;
 }
 
@@ -562,6 +572,7 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
     const uint32_t t = order[pos];
     uint32_t e = task_start[t];
     const uint32_t end = e + task_len[t];
+    ZG_CHECK(t < *n_tasks && end <= p.n_entries);
     FqSlots S;
     vs_acc_inf(S);
     auto fetch = [&](uint32_t &pc, FqSlots &S_) -> bool {
@@ -571,6 +582,7 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
         }
         for (;;) {
             uint32_t ent = entries[e++];
+            ZG_CHECK((ent & 0x7fffffffu) < p.n_bases);
             const Affine *pt = bases + (ent & 0x7fffffffu);
             vs_set(S_, VS_QX, &pt->x);
             if (ent >> 31)
@@ -897,6 +909,7 @@ struct TailJob {
     uint32_t cm1;                // c - 1 = log2(NB)
     uint32_t V;
     uint32_t n_fin;
+    uint32_t lvl_cap, partial_cap, fin_cap, n_buckets; // capacities in items (checked build)
 };
 
 struct TailBatch {
@@ -927,7 +940,9 @@ __global__ void __launch_bounds__(32, 1) k_tail_fold(TailBatch tb)
     const uint32_t n_heavy = *J.heavy_count, nblk = tb.first_block[j + 1] - tb.first_block[j];
     for (uint32_t h = blockIdx.x - tb.first_block[j]; h < n_heavy; h += nblk) {
         const uint32_t b = J.heavy_list[h];
+        ZG_CHECK(b < J.n_buckets);
         const uint32_t t0 = J.task_off[b], nt = J.task_off[b + 1] - t0;
+        ZG_CHECK(nt > 1 && t0 + nt <= J.partial_cap);
         for (uint32_t step = 1; step < nt; step <<= 1) {
             // pairs (i, i + step), i = 2*step*q, q < ceil((nt - step) / (2 step))
             const uint32_t n_pairs = (nt - step + 2 * step - 1) / (2 * step);
@@ -960,7 +975,11 @@ __global__ void __launch_bounds__(128, 3) k_tail_level(TailBatch tb, uint32_t k)
     const XYZZ *a, *b;
     XYZZ *dst;
     auto x_prev = [&](uint32_t i) -> const XYZZ * { // item i of X_{k-1}
-        if (k > 1) return in + i;
+        if (k > 1) {
+            ZG_CHECK(i < J.lvl_cap);
+            return in + i;
+        }
+        ZG_CHECK(i < J.n_buckets);
         const uint32_t t0 = J.task_off[i];
         return t0 == J.task_off[i + 1] ? nullptr : J.partial + t0;
     };
@@ -975,11 +994,13 @@ __global__ void __launch_bounds__(128, 3) k_tail_level(TailBatch tb, uint32_t k)
             b = x_prev(4 * u + 3);
         } else {           // Y_tj of the previous launch: 2 n_tree items behind the 2 n_main of X_{k-1}
             const XYZZ *y = in + 2 * n_main + (size_t)tj * (2 * n_tree);
+            ZG_CHECK(2 * n_main + (size_t)tj * (2 * n_tree) + 2 * u + 1 < J.lvl_cap);
             a = y + 2 * u;
             b = y + 2 * u + 1;
         }
         dst = out + n_main + (size_t)tj * n_tree + u;
     }
+    ZG_CHECK((size_t)(dst - out) < J.lvl_cap);
     FqSlots S;
     if (a)
         vs_load_acc(S, a);
@@ -1013,6 +1034,8 @@ __global__ void __launch_bounds__(128, 3) k_tail_scale(TailBatch tb)
         src = j + 1 == J.cm1 ? s2 + 2 * v + 1 : s2 + 2 * V + (size_t)j * V + v;
         ndbl += j;
     }
+    ZG_CHECK((size_t)(src - J.lvl[0]) < J.lvl_cap || (size_t)(src - J.lvl[1]) < J.lvl_cap);
+    ZG_CHECK(tid < J.fin_cap);
     FqSlots S;
     vs_load_acc(S, src);
     XYZZ *dst = J.fin + tid;
@@ -1427,6 +1450,10 @@ inline TailJob msm_tail_job(const MsmPlan &p, const MsmBuffers &b)
     j.cm1 = p.c - 1;
     j.V = p.V;
     j.n_fin = p.V * p.c;
+    j.n_buckets = (uint32_t)p.n_buckets;
+    j.lvl_cap = (uint32_t)(p.n_buckets - p.n_buckets / 4);
+    j.partial_cap = (uint32_t)p.max_tasks;
+    j.fin_cap = p.V * p.c;
     return j;
 }
 
