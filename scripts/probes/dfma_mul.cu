@@ -13,6 +13,11 @@
 #include <cuda_runtime.h>
 
 #include "dfma_consts.h"
+#define DFMA_N 15
+#define DFMA_Q DFMA52_Q
+#define DFMA_Q_HOST DFMA52_Q_HOST
+#define DFMA_ONE_HOST DFMA52_ONE_HOST
+#define DFMA_QINV DFMA52_QINV
 
 typedef unsigned long long u64;
 constexpr int N = DFMA_N;
@@ -177,8 +182,8 @@ int main(int argc, char **argv)
         CK(cudaMemcpy(d_in, in.data(), in.size() * 8, cudaMemcpyHostToDevice));
         k_check<<<(n + 127) / 128, 128>>>(d_in, d_out, n, iters);
         CK(cudaMemcpy(out.data(), d_out, out.size() * 8, cudaMemcpyDeviceToHost));
-        const u64 hdr[2] = {(u64)n, (u64)iters};
-        fwrite(hdr, 8, 2, f);
+        const u64 hdr[4] = {(u64)n, (u64)iters, 52, (u64)N};
+        fwrite(hdr, 8, 4, f);
         for (int t = 0; t < n; t++) {
             fwrite(&in[(size_t)t * 2 * N], 8, 2 * N, f);
             fwrite(&out[(size_t)t * N], 8, N, f);
