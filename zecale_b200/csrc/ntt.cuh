@@ -202,13 +202,33 @@ __device__ __forceinline__ void ntt_twiddle(uint32_t (&w)[12], const Fr *tw, uin
 
 extern __shared__ __align__(16) uint8_t ntt_smem[];
 
+// Shared-memory layout of a tile. An Fr is 48 B = three 16-byte chunks, LDS.128 / STS.128 serve a quarter
+// warp per wavefront, so 8 consecutive lanes are conflict-free iff their element positions are distinct
+// mod 8 (3 is odd). Element i of a vector sits at position ntt_swz(i): the low three bits are XORed with
+// GF(2)-linear images of bit 3 (-> 111) and of the top three bits (-> 001, 010, 100), which makes every
+// access pattern of the kernel a bijection on the low three bits: butterflies of stage 0 / 1 / 2 (lanes vary
+// bits {1,2,3} / {0,2,3} / {0,1,3}; columns 001, 010, 100, 111 are independent in threes), later stages (bits
+// {0,1,2}), and the bit-reversed load (lanes vary the top bits). Vectors are padded so that the T vectors a
+// quarter warp touches in the load / store phases fall on different residues as well.
+__host__ __device__ __forceinline__ uint32_t ntt_vstride(uint32_t logR, uint32_t T)
+{
+    const uint32_t R = 1u << logR;
+    return R + (T >= 8 ? 1u : T > 1 ? 8u / T : 0u);
+}
+__device__ __forceinline__ uint32_t ntt_swz(uint32_t i, uint32_t logR)
+{
+    uint32_t x = i ^ (((i >> 3) & 1u) * 7u);
+    if (logR >= 7) x ^= __brev(i >> (logR - 3)) >> 29;
+    return x;
+}
+
 __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, const Fr *__restrict__ tw, NttPass p)
 {
     const uint32_t R = 1u << p.logR;
     const uint32_t T = p.T;
-    const uint32_t vstride = R + 1; // padded: adjacent vectors land 12 words apart -> conflict-free
+    const uint32_t vstride = ntt_vstride(p.logR, T);
     Fr *data = reinterpret_cast<Fr *>(ntt_smem);
-    Fr *stw = data + (size_t)T * vstride; // R/2 sub-transform twiddles
+    Fr *stw = data + (size_t)T * vstride; // sub-transform twiddles, one contiguous run per stage: stw[half + j] = w_(2 half)^j, j < half
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     in += (size_t)blockIdx.y * p.batch_stride;
     out += (size_t)blockIdx.y * p.batch_stride;
@@ -225,10 +245,11 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
         u0 = (blockIdx.x % tiles_per_b) * T;
     }
 
-    // sub-transform twiddles w_R^e, e < R/2
-    for (uint32_t e = tid; e < R / 2 && !p.stw_global; e += nthr) {
+    // sub-transform twiddles: entry e in [2, R) = (half = 2^floor(log2 e), j = e - half) holds w_(2 half)^j = w_R^(j R / (2 half))
+    for (uint32_t e = tid + 2; e < R && !p.stw_global; e += nthr) {
+        const uint32_t s_ = 31 - __clz(e), j = e - (1u << s_);
         uint32_t w[12];
-        ntt_twiddle(w, tw, (uint64_t)e * p.sub_tw_stride, p.log_m, p.inverse);
+        ntt_twiddle(w, tw, (uint64_t)j * ((R >> 1) >> s_) * p.sub_tw_stride, p.log_m, p.inverse);
         fr_store(stw + e, w);
     }
     // load, bit-reversing the position inside each vector
@@ -255,7 +276,7 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
             fr_load(w, p.in_scale_tab + ((uint64_t)u * p.isc_sv + (uint64_t)r * p.isc_sr + p.isc_off));
             fr_mul_regs(x, x, w);
         }
-        fr_store(data + (size_t)v * vstride + bitrev(r, p.logR), x);
+        fr_store(data + (size_t)v * vstride + ntt_swz(bitrev(r, p.logR), p.logR), x);
     }
     __syncthreads();
     // DIT stages
@@ -268,15 +289,15 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
             uint32_t b = l & (halfR - 1);
             uint32_t j = b & (half - 1);
             uint32_t i = ((b >> s) << (s + 1)) + j;
-            Fr *pa = data + (size_t)v * vstride + i;
-            Fr *pb = pa + half;
+            Fr *pa = data + (size_t)v * vstride + ntt_swz(i, p.logR);
+            Fr *pb = data + (size_t)v * vstride + ntt_swz(i + half, p.logR);
             uint32_t x[12], y[12], w[12];
             fr_load(y, pb);
             if (j != 0) {
                 if (p.stw_global)
                     ntt_twiddle(w, tw, (uint64_t)j * tw_step * p.sub_tw_stride, p.log_m, p.inverse);
                 else
-                    fr_load(w, stw + (size_t)j * tw_step);
+                    fr_load(w, stw + half + j);
                 fr_mul_regs(y, y, w);
             }
             fr_load(x, pa);
@@ -294,7 +315,7 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
         uint32_t beta = beta0 + (p.tile_over_batch ? v : 0);
         uint32_t u = u0 + (p.tile_over_batch ? 0 : v);
         uint32_t x[12];
-        fr_load(x, data + (size_t)v * vstride + k);
+        fr_load(x, data + (size_t)v * vstride + ntt_swz(k, p.logR));
         const uint64_t tv = (p.tw_use_beta ? beta : u) + p.tw_vec_off;
         if (p.tw_post && tv != 0 && k != 0) {
             uint32_t w[12];
@@ -426,8 +447,8 @@ inline cudaError_t ntt_get_coset(NttTables &t, uint32_t log_m, const Fr &g, uint
 inline size_t ntt_pass_smem(uint32_t logR, uint32_t T)
 {
     size_t R = (size_t)1 << logR;
-    if (logR >= 12) return (size_t)T * (R + 1) * sizeof(Fr); // twiddles stay in global memory (stw_global)
-    return ((size_t)T * (R + 1) + R / 2) * sizeof(Fr);
+    if (logR >= 12) return (size_t)T * ntt_vstride(logR, T) * sizeof(Fr); // twiddles stay in global memory (stw_global)
+    return ((size_t)T * ntt_vstride(logR, T) + R) * sizeof(Fr);
 }
 
 // Tile width: as many vectors as fit ~100 KB (2 CTAs / SM), at most 8.
