@@ -215,6 +215,16 @@ __host__ __device__ __forceinline__ uint32_t ntt_vstride(uint32_t logR, uint32_t
     const uint32_t R = 1u << logR;
     return R + (T >= 8 ? 1u : T > 1 ? 8u / T : 0u);
 }
+// Sub-transform twiddle e (w_R^e, e < R/2) sits at e with its low three bits XORed by every higher 3-bit group of e:
+// stage s reads e = j * 2^t for 8 consecutive j, i.e. varies bits t, t+1, t+2 of e, which the fold sends to three
+// different low bits whatever t is - 8 different residues mod 8 instead of 8 entries a power of two apart.
+__device__ __forceinline__ uint32_t ntt_swz_tw(uint32_t e)
+{
+    uint32_t f = e >> 3;
+    f ^= f >> 3;
+    f ^= f >> 6;   // R/2 <= 2^11: four groups
+    return e ^ (f & 7u);
+}
 __device__ __forceinline__ uint32_t ntt_swz(uint32_t i, uint32_t logR)
 {
     uint32_t x = i ^ (((i >> 3) & 1u) * 7u);
@@ -222,13 +232,13 @@ __device__ __forceinline__ uint32_t ntt_swz(uint32_t i, uint32_t logR)
     return x;
 }
 
-__global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, const Fr *__restrict__ tw, NttPass p)
+__global__ void __launch_bounds__(256, 3) k_ntt_pass(const Fr *in, Fr *out, const Fr *__restrict__ tw, NttPass p)
 {
     const uint32_t R = 1u << p.logR;
     const uint32_t T = p.T;
     const uint32_t vstride = ntt_vstride(p.logR, T);
     Fr *data = reinterpret_cast<Fr *>(ntt_smem);
-    Fr *stw = data + (size_t)T * vstride; // sub-transform twiddles, one contiguous run per stage: stw[half + j] = w_(2 half)^j, j < half
+    Fr *stw = data + (size_t)T * vstride; // sub-transform twiddles w_R^e, e < R/2, at position ntt_swz_tw(e)
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     in += (size_t)blockIdx.y * p.batch_stride;
     out += (size_t)blockIdx.y * p.batch_stride;
@@ -245,12 +255,11 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
         u0 = (blockIdx.x % tiles_per_b) * T;
     }
 
-    // sub-transform twiddles: entry e in [2, R) = (half = 2^floor(log2 e), j = e - half) holds w_(2 half)^j = w_R^(j R / (2 half))
-    for (uint32_t e = tid + 2; e < R && !p.stw_global; e += nthr) {
-        const uint32_t s_ = 31 - __clz(e), j = e - (1u << s_);
+    // sub-transform twiddles w_R^e, e < R/2
+    for (uint32_t e = tid; e < R / 2 && !p.stw_global; e += nthr) {
         uint32_t w[12];
-        ntt_twiddle(w, tw, (uint64_t)j * ((R >> 1) >> s_) * p.sub_tw_stride, p.log_m, p.inverse);
-        fr_store(stw + e, w);
+        ntt_twiddle(w, tw, (uint64_t)e * p.sub_tw_stride, p.log_m, p.inverse);
+        fr_store(stw + ntt_swz_tw(e), w);
     }
     // load, bit-reversing the position inside each vector
     for (uint32_t l = tid; l < T * R; l += nthr) {
@@ -297,7 +306,7 @@ __global__ void __launch_bounds__(256, 2) k_ntt_pass(const Fr *in, Fr *out, cons
                 if (p.stw_global)
                     ntt_twiddle(w, tw, (uint64_t)j * tw_step * p.sub_tw_stride, p.log_m, p.inverse);
                 else
-                    fr_load(w, stw + half + j);
+                    fr_load(w, stw + ntt_swz_tw(j * tw_step));
                 fr_mul_regs(y, y, w);
             }
             fr_load(x, pa);
@@ -448,7 +457,7 @@ inline size_t ntt_pass_smem(uint32_t logR, uint32_t T)
 {
     size_t R = (size_t)1 << logR;
     if (logR >= 12) return (size_t)T * ntt_vstride(logR, T) * sizeof(Fr); // twiddles stay in global memory (stw_global)
-    return ((size_t)T * ntt_vstride(logR, T) + R) * sizeof(Fr);
+    return ((size_t)T * ntt_vstride(logR, T) + R / 2) * sizeof(Fr);
 }
 
 // Tile width: as many vectors as fit ~100 KB (2 CTAs / SM), at most 8.
