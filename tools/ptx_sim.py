@@ -51,6 +51,8 @@ def run(lines, regs):
             regs[args[0]] = (val(args[1]) << (val(args[2]) & 31)) & M32
         elif base == "and":
             regs[args[0]] = val(args[1]) & val(args[2])
+        elif base == "xor":
+            regs[args[0]] = val(args[1]) ^ val(args[2])
         elif base == "setp":
             pred[args[0]] = val(args[1]) != val(args[2])
         elif base == "selp":
