@@ -197,20 +197,21 @@ def header():
         o.append("static const uint32_t %s_HOST[16][32][2] = {\n%s};" % (name, ",\n".join(rows)))
     o.append("static const uint32_t IMMA_Q_HOST[24] = {%s};" % ", ".join("0x%08xu" % v for v in C.limbs32(Q, N)))
     o.append("static const uint32_t IMMA_ONE_HOST[24] = {%s};" % ", ".join("0x%08xu" % v for v in C.limbs32(R % Q, N)))
-    lines, nreg = gen_product(lambda j: "%%%d" % (2 * N + j), lambda i: "%%%d" % (3 * N + i), lambda k: "%%%d" % k, "%%%d" % (4 * N))
-    o.append("// p[48] = a[24] * b[24]: 576 wide MADs, even / odd carry chains, no reduction")
-    o.append("// zero: 0 at run time, unknown to the compiler (serialises the rows, see gen_product)")
-    o.append("__device__ __forceinline__ void imma_full_product(uint32_t (&p)[48], const uint32_t (&a)[24], const uint32_t (&b)[24], uint32_t zero)")
-    o.append("{")
-    o.append("    asm volatile(")
-    o.append('        "{\\n\\t"')
-    o.append('        ".reg .u32 w<%d>;\\n\\t"' % nreg)
-    for ln in lines:
-        o.append('        "%s\\n\\t"' % ln)
-    o.append('        "}\\n\\t"')
-    o.append("        : " + ", ".join('"=&r"(p[%d])' % k for k in range(2 * N)))
-    o.append("        : " + ", ".join('"r"(%s[%d])' % (c, k) for c in "ab" for k in range(N)) + ', "r"(zero));')
-    o.append("}")
+    for depth in (1, 2, 3):
+        lines, nreg = gen_product(lambda j: "%%%d" % (2 * N + j), lambda i: "%%%d" % (3 * N + i), lambda k: "%%%d" % k, "%%%d" % (4 * N), depth)
+        o.append("// p[48] = a[24] * b[24]: 576 wide MADs, even / odd carry chains, no reduction; at most %d rows in flight" % depth)
+        o.append("// zero: 0 at run time, unknown to the compiler (serialises the rows, see gen_product)")
+        o.append("__device__ __forceinline__ void imma_full_product_d%d(uint32_t (&p)[48], const uint32_t (&a)[24], const uint32_t (&b)[24], uint32_t zero)" % depth)
+        o.append("{")
+        o.append("    asm volatile(")
+        o.append('        "{\\n\\t"')
+        o.append('        ".reg .u32 w<%d>;\\n\\t"' % nreg)
+        for ln in lines:
+            o.append('        "%s\\n\\t"' % ln)
+        o.append('        "}\\n\\t"')
+        o.append("        : " + ", ".join('"=&r"(p[%d])' % k for k in range(2 * N)))
+        o.append("        : " + ", ".join('"r"(%s[%d])' % (c, k) for c in "ab" for k in range(N)) + ', "r"(zero));')
+        o.append("}")
     return "\n".join(o) + "\n"
 
 

@@ -17,7 +17,12 @@
 
 constexpr int N = 24;
 constexpr int A_STRIDE = 28;  // words per row of the operand staging (112 B: conflict-free STS.128 and fragment loads)
-constexpr int D_STRIDE = 100; // words per row of the digit staging (96 digits + pad)
+constexpr int D_STRIDE = 52;  // words per row of the digit staging (48 digits = 12 column tiles + pad; conflict-free both ways)
+#ifndef DEPTH
+#define DEPTH 2
+#endif
+#define IMMA_PRODUCT_(d) imma_full_product_d##d
+#define IMMA_PRODUCT(d) IMMA_PRODUCT_(d)
 constexpr int WARPS = 4;
 
 struct WarpStage {
@@ -32,8 +37,8 @@ __device__ __forceinline__ void mma_u8(int (&acc)[4], const uint32_t (&a)[4], ui
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
 
-// digits of the 32 rows' products with a constant: W.d[row][4 nt + q], n_tiles column tiles of 8
-template <int N_TILES>
+// digits of the 32 rows' products with a constant, column tiles [NT0, NT0 + 12): W.d[row][4 (nt - NT0) + q]
+template <int NT0>
 __device__ __forceinline__ void toeplitz_gemm(WarpStage &W, const uint2 *__restrict__ tiles, int lane)
 {
     const int g = lane >> 2, q = lane & 3;
@@ -49,7 +54,7 @@ __device__ __forceinline__ void toeplitz_gemm(WarpStage &W, const uint2 *__restr
             A[mt][ks][3] = r0[8 * A_STRIDE + 4];
         }
 #pragma unroll
-    for (int nt = 0; nt < N_TILES; nt++) {
+    for (int nt = NT0; nt < NT0 + 12; nt++) {
         int acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
 #pragma unroll
         for (int ks = 0; ks < 3; ks++) {
@@ -62,8 +67,8 @@ __device__ __forceinline__ void toeplitz_gemm(WarpStage &W, const uint2 *__restr
         }
 #pragma unroll
         for (int mt = 0; mt < 2; mt++) {
-            W.d[(16 * mt + g) * D_STRIDE + 4 * nt + q] = (uint32_t)acc[mt][0] + ((uint32_t)acc[mt][1] << 8);
-            W.d[(16 * mt + g + 8) * D_STRIDE + 4 * nt + q] = (uint32_t)acc[mt][2] + ((uint32_t)acc[mt][3] << 8);
+            W.d[(16 * mt + g) * D_STRIDE + 4 * (nt - NT0) + q] = (uint32_t)acc[mt][0] + ((uint32_t)acc[mt][1] << 8);
+            W.d[(16 * mt + g + 8) * D_STRIDE + 4 * (nt - NT0) + q] = (uint32_t)acc[mt][2] + ((uint32_t)acc[mt][3] << 8);
         }
     }
 }
@@ -98,23 +103,26 @@ __device__ __forceinline__ void fq_mul_imma(uint32_t (&r)[N], const uint32_t (&a
                                             const uint2 *tq, const uint2 *tn, const uint32_t *qmod, int lane, uint32_t zero)
 {
     uint32_t P[2 * N];
-    imma_full_product(P, a, b, zero);
+    IMMA_PRODUCT(DEPTH)(P, a, b, zero);
     uint32_t nz = 0;
 #pragma unroll
     for (int k = 0; k < N; k++) nz |= P[k];
     stage_operand(W, P, lane);
     __syncwarp();
-    toeplitz_gemm<12>(W, tq, lane);
+    toeplitz_gemm<0>(W, tq, lane);
     __syncwarp();
     uint32_t m[N];
     normalise<N>(m, W.d + lane * D_STRIDE);
     stage_operand(W, m, lane);
     __syncwarp();
-    toeplitz_gemm<24>(W, tn, lane);
+    toeplitz_gemm<0>(W, tn, lane);
     __syncwarp();
     uint32_t lo[N], hi[N];
-    const uint32_t c = normalise<N>(lo, W.d + lane * D_STRIDE);
-    normalise<N>(hi, W.d + lane * D_STRIDE + 48, c);
+    const uint32_t c = normalise<N>(lo, W.d + lane * D_STRIDE);   // low half of m q: only its carry is used
+    __syncwarp();
+    toeplitz_gemm<12>(W, tn, lane);
+    __syncwarp();
+    normalise<N>(hi, W.d + lane * D_STRIDE, c);
     __syncwarp();
     // T = P_hi + U_hi + (P_lo != 0)
     unsigned long long carry = nz ? 1u : 0u;
@@ -230,9 +238,9 @@ template <int MINB> static int time_chain(uint32_t *sink, const uint2 *tq, const
     float ms = 0;
     CK(cudaEventElapsedTime(&ms, e0, e1));
     const double prods = (double)blocks * 32 * WARPS * iters;
-    printf("{\"probe\": \"imma_mul chain\", \"min_blocks_per_sm\": %d, \"blocks\": %d, \"threads\": %d, \"iters\": %d, \"ms\": %.4f, "
+    printf("{\"probe\": \"imma_mul chain\", \"rows_in_flight\": %d, \"min_blocks_per_sm\": %d, \"blocks\": %d, \"threads\": %d, \"iters\": %d, \"ms\": %.4f, "
            "\"fq_products_per_s\": %.4e, \"equiv_32x32_products_per_s\": %.4e}\n",
-           MINB, blocks, 32 * WARPS, iters, ms, prods / (ms * 1e-3), prods * 1176.0 / (ms * 1e-3));
+           DEPTH, MINB, blocks, 32 * WARPS, iters, ms, prods / (ms * 1e-3), prods * 1176.0 / (ms * 1e-3));
     return 0;
 }
 
@@ -284,6 +292,7 @@ int main(int argc, char **argv)
     for (int mult : {1, 2, 4}) {
         if (time_chain<2>(sink, tq, tn, sms * mult * 2, iters)) return 2;
         if (time_chain<3>(sink, tq, tn, sms * mult * 3, iters)) return 2;
+        if (time_chain<4>(sink, tq, tn, sms * mult * 4, iters)) return 2;
     }
     return 0;
 }
