@@ -3,7 +3,7 @@
 # product in flight x CTAs per SM), one ncu capture of the best.
 mkdir -p gpurun_out
 : > gpurun_out/imma_mul.jsonl
-for d in 1 2 3; do
+for d in 2; do
   timeout 300 ./scripts/probes/imma_mul_d$d /tmp/imma_dump_$d.bin 1000 >> gpurun_out/imma_mul.jsonl 2>> gpurun_out/imma_mul.err; echo "imma d$d rc=$?"
   timeout 300 python scripts/probes/imma_model.py check /tmp/imma_dump_$d.bin >> gpurun_out/imma_mul.jsonl 2>> gpurun_out/imma_mul.err; echo "check rc=$?"
 done

@@ -100,6 +100,37 @@ def gen_product(a_op, b_op, p_op, zero_op=None, depth=1):
     return lines, cnt[0]
 
 
+def gen_normalise(L, limb_op, dig_op, cin_op, cout_op):
+    """limbs[L] = sum of 2 L radix-2^16 digits (each < 2^32) + cin, carry out in cout. The digit pairs are folded in
+    parallel (lo_k = d_2k + (d_2k+1 << 16), hi_k = (d_2k+1 >> 16) + carry); only one add-with-carry per limb is serial."""
+    lines = []
+    for k in range(L):
+        lines.append("shl.b32 t%d, %s, 16;" % (k, dig_op(2 * k + 1)))
+        lines.append("add.cc.u32 l%d, %s, t%d;" % (k, dig_op(2 * k), k))
+        lines.append("shr.b32 h%d, %s, 16;" % (k, dig_op(2 * k + 1)))
+        lines.append("addc.u32 h%d, h%d, 0;" % (k, k))
+    lines.append("add.cc.u32 %s, l0, %s;" % (limb_op(0), cin_op))
+    for k in range(1, L):
+        lines.append("addc.cc.u32 %s, l%d, h%d;" % (limb_op(k), k, k - 1))
+    lines.append("addc.u32 %s, h%d, 0;" % (cout_op, L - 1))
+    return lines
+
+
+def check_normalise_ptx():
+    import random
+    rng = random.Random(9)
+    L = 24
+    lines = gen_normalise(L, lambda k: "r%d" % k, lambda i: "d%d" % i, "cin", "cout")
+    for _ in range(50):
+        regs = {"d%d" % i: rng.choice((rng.randrange(1 << 32), 0xFFFFFFFF, 0)) for i in range(2 * L)}
+        regs["cin"] = rng.randrange(1 << 18)
+        want = sum(regs["d%d" % i] << (16 * i) for i in range(2 * L)) + regs["cin"]
+        ptx_sim.run(lines, regs)
+        got = sum(regs["r%d" % k] << (32 * k) for k in range(L)) + (regs["cout"] << (32 * L))
+        assert got == want
+    print("normalise PTX ok (%d lines)" % len(lines))
+
+
 def check_product_ptx():
     import random
     rng = random.Random(3)
@@ -178,6 +209,7 @@ def selftest():
     import random
     rng = random.Random(5)
     check_product_ptx()
+    check_normalise_ptx()
     xs = [rng.randrange(Q) for _ in range(32)]
     ys = [rng.randrange(Q) for _ in range(32)]
     xs[0], ys[1], xs[2], ys[2] = 0, 0, Q - 1, Q - 1
@@ -212,6 +244,22 @@ def header():
         o.append("        : " + ", ".join('"=&r"(p[%d])' % k for k in range(2 * N)))
         o.append("        : " + ", ".join('"r"(%s[%d])' % (c, k) for c in "ab" for k in range(N)) + ', "r"(zero));')
         o.append("}")
+    L = 24
+    lines = gen_normalise(L, lambda k: "%%%d" % k, lambda i: "%%%d" % (L + 1 + i), "%%%d" % (3 * L + 1), "%%%d" % L)
+    o.append("// limbs[24] = 48 radix-2^16 digits (each < 2^32) + cin; returns the carry out. One serial add-with-carry per limb.")
+    o.append("__device__ __forceinline__ uint32_t imma_normalise24(uint32_t (&limbs)[24], const uint32_t (&d)[48], uint32_t cin)")
+    o.append("{")
+    o.append("    uint32_t cout;")
+    o.append("    asm volatile(")
+    o.append('        "{\\n\\t"')
+    o.append('        ".reg .u32 t<%d>, l<%d>, h<%d>;\\n\\t"' % (L, L, L))
+    for ln in lines:
+        o.append('        "%s\\n\\t"' % ln)
+    o.append('        "}\\n\\t"')
+    o.append("        : " + ", ".join('"=&r"(limbs[%d])' % k for k in range(L)) + ', "=&r"(cout)')
+    o.append("        : " + ", ".join('"r"(d[%d])' % i for i in range(2 * L)) + ', "r"(cin));')
+    o.append("    return cout;")
+    o.append("}")
     return "\n".join(o) + "\n"
 
 

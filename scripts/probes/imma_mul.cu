@@ -73,22 +73,19 @@ __device__ __forceinline__ void toeplitz_gemm(WarpStage &W, const uint2 *__restr
     }
 }
 
-// limbs[k] = digits 2k, 2k+1 (radix 2^16, each < 2^32) + carry; returns the carry out
-template <int LIMBS>
-__device__ __forceinline__ uint32_t normalise(uint32_t (&limbs)[LIMBS], const uint32_t *digits, uint32_t carry_in = 0)
+// limbs = the lane's 48 staged digits (+ carry in); returns the carry out
+__device__ __forceinline__ uint32_t normalise(uint32_t (&limbs)[24], const uint32_t *digits, uint32_t carry_in = 0)
 {
-    unsigned long long carry = carry_in;
+    uint32_t d[48];
 #pragma unroll
-    for (int k4 = 0; k4 < LIMBS / 2; k4++) {
+    for (int k4 = 0; k4 < 12; k4++) {
         const uint4 v = reinterpret_cast<const uint4 *>(digits)[k4];
-        unsigned long long t = (unsigned long long)v.x + ((unsigned long long)v.y << 16) + carry;
-        limbs[2 * k4] = (uint32_t)t;
-        carry = t >> 32;
-        t = (unsigned long long)v.z + ((unsigned long long)v.w << 16) + carry;
-        limbs[2 * k4 + 1] = (uint32_t)t;
-        carry = t >> 32;
+        d[4 * k4] = v.x;
+        d[4 * k4 + 1] = v.y;
+        d[4 * k4 + 2] = v.z;
+        d[4 * k4 + 3] = v.w;
     }
-    return (uint32_t)carry;
+    return imma_normalise24(limbs, d, carry_in);
 }
 
 __device__ __forceinline__ void stage_operand(WarpStage &W, const uint32_t *x, int lane)
@@ -112,17 +109,17 @@ __device__ __forceinline__ void fq_mul_imma(uint32_t (&r)[N], const uint32_t (&a
     toeplitz_gemm<0>(W, tq, lane);
     __syncwarp();
     uint32_t m[N];
-    normalise<N>(m, W.d + lane * D_STRIDE);
+    normalise(m, W.d + lane * D_STRIDE);
     stage_operand(W, m, lane);
     __syncwarp();
     toeplitz_gemm<0>(W, tn, lane);
     __syncwarp();
     uint32_t lo[N], hi[N];
-    const uint32_t c = normalise<N>(lo, W.d + lane * D_STRIDE);   // low half of m q: only its carry is used
+    const uint32_t c = normalise(lo, W.d + lane * D_STRIDE);   // low half of m q: only its carry is used
     __syncwarp();
     toeplitz_gemm<12>(W, tn, lane);
     __syncwarp();
-    normalise<N>(hi, W.d + lane * D_STRIDE, c);
+    normalise(hi, W.d + lane * D_STRIDE, c);
     __syncwarp();
     // T = P_hi + U_hi + (P_lo != 0)
     unsigned long long carry = nz ? 1u : 0u;

@@ -47,6 +47,8 @@ def run(lines, regs):
         elif base == "shf":   # shf.l.wrap.b32 d, lo, hi, c
             lo, hi, c = val(args[1]), val(args[2]), val(args[3]) & 31
             regs[args[0]] = (((hi << 32) | lo) << c >> 32) & M32
+        elif base == "shr":
+            regs[args[0]] = val(args[1]) >> (val(args[2]) & 31)
         elif base == "shl":
             regs[args[0]] = (val(args[1]) << (val(args[2]) & 31)) & M32
         elif base == "and":
