@@ -54,8 +54,15 @@ NNZ = (444246, 496421, 877410)   # non-zero terms of the A / B / C constraint ma
 METRIC = "bw6_761_groth16_batch8_proofs_per_s"
 UNIT = "proofs/s"
 FR_TOP = 0x01AE3A4617C510EA  # top 64-bit limb of r: a random value with a smaller top limb is < r
-PRODUCTS_PER_FQ_MUL = 1176   # 24*24 (a*b) + 24*24 (m*q) + 24 (m) 32x32 products, SURVEY.md §8(d)
+# 32x32 products the device executes: a*b by one Karatsuba level = 3 * 12*12, the word-serial reduction
+# 24*24 + 24. SURVEY.md 8(d)'s schoolbook figure (24*24 + 24*24 + 24 = 1176 per Fq product, 10 per mixed addition) is kept
+# as PRODUCTS_PER_MADD_SCHOOLBOOK for comparison with round 1.
+PRODUCTS_MULW = 432
+PRODUCTS_REDC = 600
 FQ_MUL_PER_MADD = 10         # madd-2008-s: 8M + 2S, every S done as M
+# a mixed addition = 10 products but 9 reductions: Y3 = R(Q - X3) - Y1 PPP is reduced once (MULW + MULFIN)
+PRODUCTS_PER_MADD = 10 * PRODUCTS_MULW + 9 * PRODUCTS_REDC
+PRODUCTS_PER_MADD_SCHOOLBOOK = 10 * 1176
 
 
 def random_fr(rng, n):
@@ -397,14 +404,20 @@ PAPER_PEAK_PRODUCTS = 148 * 32 * 1.965e9   # 148 SM x 32 IMAD.WIDE / clk x 1.965
 
 
 def imad_peak(ctx):
-    """Measured integer-multiply ceiling of this GPU: best Fq products/s of a dependent-chain
-    Montgomery-product kernel over a few occupancies, in 32x32 products per second."""
+    """Measured integer-multiply ceiling of this GPU in 32x32 products per second: independent chains of IMAD.WIDE.U32
+    (k_bench_imad, 8 chains per thread) over a few occupancies. Also returns the Fq Montgomery products/s of the
+    dependent-chain product kernel (k_bench_fq_mul), the figure rounds 1-2 used as the ceiling."""
     best = 0.0
-    for blocks_per_sm, tpb in ((2, 128), (3, 128), (4, 64)):
+    for blocks_per_sm, tpb in ((2, 256), (4, 256), (8, 256)):
+        blocks, iters = 148 * blocks_per_sm, 4096
+        ms = min(ctx.bench_imad(blocks, tpb, iters) for _ in range(3))
+        best = max(best, blocks * tpb * iters * 8 / (ms * 1e-3))
+    fq = 0.0
+    for blocks_per_sm, tpb in ((2, 128), (4, 64)):
         blocks, iters = 148 * blocks_per_sm, 1000
         ms = min(ctx.bench_fq_mul(blocks, tpb, iters) for _ in range(2))
-        best = max(best, blocks * tpb * iters / (ms * 1e-3))
-    return best * PRODUCTS_PER_FQ_MUL
+        fq = max(fq, blocks * tpb * iters / (ms * 1e-3))
+    return best, fq
 
 
 def run_b200(args, rank, world, local_rank):
@@ -482,10 +495,10 @@ def run_b200(args, rank, world, local_rank):
     out = None
     if rank == 0:
         peaks, peaks_src = measured_peaks()
-        peak_prod = imad_peak(ctx)
+        peak_prod, fq_mul_rate = imad_peak(ctx)
         madds, shapes, iso_acc_ms, iso_ntt_ms, iso_ntt_n = wl.isolated_kernels()
         acc_s = iso_acc_ms * 1e-3                            # the step's 5 accumulate launches, each timed alone
-        prod_step = madds * FQ_MUL_PER_MADD * PRODUCTS_PER_FQ_MUL
+        prod_step = madds * PRODUCTS_PER_MADD
         achieved = prod_step / acc_s if acc_s > 0 else 0.0
         step_s = t_res / args.steps
         m = 1 << LOG_M
@@ -510,7 +523,13 @@ def run_b200(args, rank, world, local_rank):
             "roofline": {"bound": "imad", "bound_note": "integer-multiply pipe (sm__pipe_fmaheavy): neither HBM- nor tensor-bound, SURVEY.md 8(d)",
                          "kernel": "k_accumulate (MSM bucket accumulation)", "achieved": achieved / 1e12,
                          "peak": peak_prod / 1e12, "unit": "T(32x32 products)/s", "frac": achieved / peak_prod if peak_prod else None,
-                         "peak_source": "measured in this run: dependent-chain Fq Montgomery products (k_bench_fq_mul)",
+                         "peak_source": "measured in this run: independent IMAD.WIDE.U32 chains (k_bench_imad, zecale_gpu_bench_imad)",
+                         "fq_products_per_s": fq_mul_rate,
+                         "products_per_madd": PRODUCTS_PER_MADD,
+                         "products_note": "32x32 products executed per mixed addition: 10 x 432 (one Karatsuba level on a*b) + 9 x 600 "
+                                          "(word-serial reductions; Y3 is reduced once). Round 1 executed 10 x 1176 = 11760 for the same "
+                                          "addition: madds_per_step x 11760 / step time is the figure comparable with r01's in_step_achieved",
+                         "in_step_achieved_schoolbook_equiv": madds * PRODUCTS_PER_MADD_SCHOOLBOOK / step_s / 1e12,
                          "peak_paper": PAPER_PEAK_PRODUCTS / 1e12, "frac_of_paper_peak": achieved / PAPER_PEAK_PRODUCTS,
                          "launches_per_step": 5, "launch_ms_avg": 1e3 * acc_s / 5,
                          "timing": "CUDA events on the launching stream, each of the step's five launches alone on the GPU",

@@ -293,6 +293,10 @@ int zecale_gpu_test_group(zecale_gpu_ctx *ctx, int op, const void *a, const void
  * `iters` products; returns the CUDA-event time in ms in *elapsed_ms. */
 int zecale_gpu_bench_fq_mul(zecale_gpu_ctx *ctx, unsigned blocks, unsigned threads_per_block, unsigned iters,
                             float *elapsed_ms);
+/* Integer-multiply pipe ceiling (the denominator of the MSM roofline): every thread runs 8 independent dependent chains
+ * of 32x32+64 -> 64 multiply-adds (IMAD.WIDE.U32), 8 * iters of them per thread; CUDA-event time in ms in *elapsed_ms. */
+int zecale_gpu_bench_imad(zecale_gpu_ctx *ctx, unsigned blocks, unsigned threads_per_block, unsigned iters,
+                          float *elapsed_ms);
 
 #ifdef __cplusplus
 }

@@ -8,8 +8,9 @@ import zecale_b200 as z
 
 ctx = z.Context(0)
 res = []
-for blocks_per_sm in (1, 2, 3, 4):
-    for tpb in (32, 64, 128):
+quick = "--quick" in sys.argv
+for blocks_per_sm in ((2, 3) if quick else (1, 2, 3, 4)):
+    for tpb in ((128,) if quick else (32, 64, 128)):
         blocks = 148 * blocks_per_sm
         iters = 2000
         ms = min(ctx.bench_fq_mul(blocks, tpb, iters) for _ in range(3))

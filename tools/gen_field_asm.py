@@ -190,6 +190,255 @@ def gen_sub(N, P, a_op, b_op, r_op):
     return em
 
 
+# ---------------------------------------------------------------------------------------------
+# Round 2: product and reduction separated, Karatsuba on the product.
+#
+# r = (P + M*q)/R = P_hi + (P_lo + M*q)/R,  P = a*b (2N limbs),  M = sum m_i 2^(32 i) chosen so that
+# P_lo + M*q = 0 mod R. The m_i depend on P_lo and q only, so the word-serial rounds run on an N-limb
+# window that starts as P_lo (T <- (T + m*q) >> 32, m = T_0 * inv: the m*q half of the CIOS round above,
+# N wide MADs instead of 2N) and P_hi is added once at the end: T_N <= q, P_hi < q^2/R < q, sum < 2q,
+# one conditional subtract -- the same canonical value. The product a*b no longer has to be interleaved
+# with the reduction, so it can be Karatsuba: a = a0 + a1 B, b = b0 + b1 B,
+#     a*b = z0 + (z0 + z2 - (a0 - a1)(b0 - b1)) B + z2 B^2,   z0 = a0 b0, z2 = a1 b1,
+# three half-size products instead of four; (a0 - a1)(b0 - b1) = +-|a0 - a1| |b0 - b1| with the sign
+# applied as a masked two's complement. Each level trades N^2/4 wide MADs (the saturated pipe,
+# DESIGN.md section 3.1) for ~8N adds/logic ops on the otherwise idle ALU pipe. Base case: schoolbook rows
+# in the even/odd carry-chain form of gen_mul.
+#   Fq: 1152 + 24 wide MADs  ->  levels=1: 432 + 576 + 24,  levels=2: 324 + 576 + 24.
+
+
+def school_product(em, A, B):
+    """A, B: n operand names (n even). Returns 2n names holding A*B. n*n wide MADs."""
+    n = len(A)
+    assert n == len(B) and n % 2 == 0
+    E = [em.fresh() for _ in range(n)]
+    O = [em.fresh() for _ in range(n)]
+    out = []
+    x = None
+    for i in range(n):
+        bi = B[i]
+        if i == 0:
+            for j in range(0, n, 2):
+                em.op("mul.lo.u32 %s, %s, %s;" % (E[j], A[j], bi))
+                em.op("mul.hi.u32 %s, %s, %s;" % (E[j + 1], A[j], bi))
+            for j in range(1, n, 2):
+                em.op("mul.lo.u32 %s, %s, %s;" % (O[j - 1], A[j], bi))
+                em.op("mul.hi.u32 %s, %s, %s;" % (O[j], A[j], bi))
+            top = None
+        else:
+            em.op("add.cc.u32 %s, %s, %s;" % (E[0], E[0], x))   # pending word; its carry enters the odd chain
+            for j in range(1, n, 2):
+                if O[j - 1] is None:                              # the carry word of row 0 (no even chain yet)
+                    lo = em.fresh()
+                    em.op("madc.lo.cc.u32 %s, %s, %s, 0;" % (lo, A[j], bi))
+                    O[j - 1] = lo
+                else:
+                    em.op("madc.lo.cc.u32 %s, %s, %s, %s;" % (O[j - 1], A[j], bi, O[j - 1]))
+                if j == n - 1:
+                    nw = em.fresh()
+                    em.op("madc.hi.u32 %s, %s, %s, 0;" % (nw, A[j], bi))
+                    O[j] = nw
+                else:
+                    em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (O[j], A[j], bi, O[j]))
+            for j in range(0, n, 2):
+                c0 = "mad.lo.cc.u32" if j == 0 else "madc.lo.cc.u32"
+                em.op("%s %s, %s, %s, %s;" % (c0, E[j], A[j], bi, E[j]))
+                em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], A[j], bi, E[j + 1]))
+            top = em.fresh()
+            em.op("addc.u32 %s, 0, 0;" % top)
+        out.append(E[0])                                          # limb i of the product is final
+        x = E[1]
+        E, O = O, E[2:] + [top, None]
+    # remaining n limbs: E + x + O*2^32 (O[n-1] is None; O[n-2] is None only for n == 2 rows... never: n >= 2)
+    hi = [em.fresh() for _ in range(n)]
+    em.op("add.cc.u32 %s, %s, %s;" % (hi[0], E[0], x))
+    for k in range(1, n):
+        cc = "addc.cc.u32" if k < n - 1 else "addc.u32"
+        o = O[k - 1]
+        em.op("%s %s, %s, %s;" % (cc, hi[k], E[k], o if o is not None else "0"))
+    return out + hi
+
+
+def abs_diff(em, X, Y):
+    """(|X - Y| as len(X) names, mask name: 0xffffffff if X < Y else 0)."""
+    h = len(X)
+    d = [em.fresh() for _ in range(h)]
+    e = [em.fresh() for _ in range(h)]
+    r = [em.fresh() for _ in range(h)]
+    bw = em.fresh()
+    for k in range(h):
+        em.op("%s %s, %s, %s;" % ("sub.cc.u32" if k == 0 else "subc.cc.u32", d[k], X[k], Y[k]))
+    em.op("subc.u32 %s, 0, 0;" % bw)
+    for k in range(h):
+        cc = "sub.cc.u32" if k == 0 else ("subc.cc.u32" if k < h - 1 else "subc.u32")
+        em.op("%s %s, %s, %s;" % (cc, e[k], Y[k], X[k]))
+    for k in range(h):
+        em.op("lop3.b32 %s, %s, %s, %s, 0xE4;" % (r[k], e[k], d[k], bw))   # bw ? e : d
+    return r, bw
+
+
+def kara_product(em, A, B, levels):
+    """A*B as 2n limb names; `levels` Karatsuba levels above schoolbook rows."""
+    n = len(A)
+    if levels == 0 or n % 4 != 0:
+        return school_product(em, A, B)
+    h = n // 2
+    a0, a1, b0, b1 = A[:h], A[h:], B[:h], B[h:]
+    da, sa = abs_diff(em, a0, a1)
+    db, sb = abs_diff(em, b0, b1)
+    z0 = kara_product(em, a0, b0, levels - 1)
+    z2 = kara_product(em, a1, b1, levels - 1)
+    mm = kara_product(em, da, db, levels - 1)
+    # t = z0 + z2 (n limbs + carry limb)
+    t = [em.fresh() for _ in range(n + 1)]
+    for k in range(n):
+        em.op("%s %s, %s, %s;" % ("add.cc.u32" if k == 0 else "addc.cc.u32", t[k], z0[k], z2[k]))
+    em.op("addc.u32 %s, 0, 0;" % t[n])
+    # z1 = t - mm when the two differences have the same sign, t + mm otherwise (always >= 0, n+1 limbs)
+    neg = em.fresh()
+    em.op("xor.b32 %s, %s, %s;" % (neg, sa, sb))
+    em.op("xor.b32 %s, %s, 0xffffffff;" % (neg, neg))
+    w = [em.fresh() for _ in range(n)]
+    for k in range(n):
+        em.op("xor.b32 %s, %s, %s;" % (w[k], mm[k], neg))
+    z1 = [em.fresh() for _ in range(n + 1)]
+    junk = em.fresh()
+    em.op("add.cc.u32 %s, %s, %s;" % (junk, neg, neg))            # carry = 1 iff subtracting (the +1 of -mm)
+    for k in range(n):
+        em.op("addc.cc.u32 %s, %s, %s;" % (z1[k], t[k], w[k]))
+    em.op("addc.u32 %s, %s, %s;" % (z1[n], t[n], neg))
+    # P = z0 + z1 B + z2 B^2
+    out = list(z0[:h])
+    for k in range(n + 1):
+        base = z0[h + k] if k < h else z2[k - h]
+        r = em.fresh()
+        em.op("%s %s, %s, %s;" % ("add.cc.u32" if k == 0 else "addc.cc.u32", r, base, z1[k]))
+        out.append(r)
+    for k in range(h + 1, n):
+        r = em.fresh()
+        cc = "addc.cc.u32" if k < n - 1 else "addc.u32"
+        em.op("%s %s, %s, 0;" % (cc, r, z2[k]))
+        out.append(r)
+    assert len(out) == 2 * n
+    return out
+
+
+def gen_redc(em, N, q, inv, Pw, r_op):
+    """r = Pw / R mod p for a 2N-limb Pw < p*R (names), canonical. N*N wide MADs + N MULs."""
+    E = list(Pw[:N])
+    O = [None] * N
+    x = None
+    for i in range(N):
+        m = em.fresh()
+        if i > 0:
+            nw = em.fresh()
+            em.op("add.cc.u32 %s, %s, %s;" % (nw, E[0], x))       # carry enters the odd chain
+            E[0] = nw
+        em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], imm(inv)))
+        for j in range(1, N, 2):
+            lo, hi = em.fresh(), em.fresh()
+            if O[j - 1] is None and i == 0:
+                em.op("mul.lo.u32 %s, %s, %s;" % (lo, m, imm(q[j])))
+                em.op("mul.hi.u32 %s, %s, %s;" % (hi, m, imm(q[j])))
+            else:
+                c0 = "madc.lo.cc.u32" if (i > 0 or j > 1) else "mad.lo.cc.u32"
+                em.op("%s %s, %s, %s, %s;" % (c0, lo, m, imm(q[j]), O[j - 1]))
+                c1 = "madc.hi.u32" if j == N - 1 else "madc.hi.cc.u32"
+                em.op("%s %s, %s, %s, %s;" % (c1, hi, m, imm(q[j]), O[j] if O[j] is not None else "0"))
+            O[j - 1], O[j] = lo, hi
+        nE = list(E)
+        for j in range(0, N, 2):
+            lo, hi = em.fresh(), em.fresh()
+            c0 = "mad.lo.cc.u32" if j == 0 else "madc.lo.cc.u32"
+            em.op("%s %s, %s, %s, %s;" % (c0, lo, m, imm(q[j]), E[j]))
+            em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (hi, m, imm(q[j]), E[j + 1]))
+            nE[j], nE[j + 1] = lo, hi
+        top = em.fresh()
+        em.op("addc.u32 %s, 0, 0;" % top)
+        x = nE[1]
+        E, O = O, nE[2:] + [top, None]
+    # T = E + x + O*2^32 <= q, then + P_hi (< q): < 2q
+    T = [em.fresh() for _ in range(N)]
+    em.op("add.cc.u32 %s, %s, %s;" % (T[0], E[0], x))
+    for k in range(1, N):
+        cc = "addc.cc.u32" if k < N - 1 else "addc.u32"
+        em.op("%s %s, %s, %s;" % (cc, T[k], E[k], O[k - 1]))
+    U = [em.fresh() for _ in range(N)]
+    for k in range(N):
+        cc = "add.cc.u32" if k == 0 else ("addc.cc.u32" if k < N - 1 else "addc.u32")
+        em.op("%s %s, %s, %s;" % (cc, U[k], T[k], Pw[N + k]))
+    gen_final_sub(em, N, q, U, r_op)
+
+
+def gen_mul_kara(N, P, inv, a_op, b_op, r_op, levels):
+    q = C.limbs32(P, N)
+    em = Emit()
+    Pw = kara_product(em, [a_op(j) for j in range(N)], [b_op(j) for j in range(N)], levels)
+    gen_redc(em, N, q, inv, Pw, r_op)
+    return em
+
+
+def gen_mulw(N, a_op, b_op, p_op, levels):
+    """p (2N limbs) = a*b, unreduced."""
+    em = Emit()
+    Pw = kara_product(em, [a_op(j) for j in range(N)], [b_op(j) for j in range(N)], levels)
+    for k in range(2 * N):
+        em.op("mov.u32 %s, %s;" % (p_op(k), Pw[k]))
+    return em
+
+
+def gen_wsubk(N, P, w_op, p_op):
+    """w (2N limbs, in/out) = w - p + q^2: the difference of two products of reduced operands, made non-negative by a
+    multiple of q; 0 < w < 2 q^2 < q R, so gen_redc's bound holds."""
+    K = C.limbs32(P * P, 2 * N)
+    em = Emit()
+    D = [em.fresh() for _ in range(2 * N)]
+    for k in range(2 * N):
+        cc = "sub.cc.u32" if k == 0 else ("subc.cc.u32" if k < 2 * N - 1 else "subc.u32")
+        em.op("%s %s, %s, %s;" % (cc, D[k], w_op(k), p_op(k)))
+    for k in range(2 * N):
+        cc = "add.cc.u32" if k == 0 else ("addc.cc.u32" if k < 2 * N - 1 else "addc.u32")
+        em.op("%s %s, %s, %s;" % (cc, w_op(k), D[k], imm(K[k])))
+    return em
+
+
+def gen_redc_only(N, P, inv, p_op, r_op):
+    q = C.limbs32(P, N)
+    em = Emit()
+    gen_redc(em, N, q, inv, [p_op(k) for k in range(2 * N)], r_op)
+    return em
+
+
+def wrap_io(name, em, outs, ins, inouts, doc):
+    """outs / ins / inouts: lists of (c_name, length); asm operands are numbered outs, inouts, ins in that order."""
+    o = ["// %s" % doc]
+    args = ["uint32_t (&%s)[%d]" % (c, n) for c, n in outs + inouts] + ["const uint32_t (&%s)[%d]" % (c, n) for c, n in ins]
+    o.append("__device__ __forceinline__ void %s(%s)" % (name, ", ".join(args)))
+    o.append("{")
+    o.append("    asm volatile(")
+    o.append('        "{\\n\\t"')
+    o.append('        ".reg .u32 v<%d>;\\n\\t"' % max(em.nreg, 1))
+    o.append('        ".reg .pred pb;\\n\\t"')
+    for ln in em.lines:
+        o.append('        "%s\\n\\t"' % ln)
+    o.append('        "}\\n\\t"')
+    cons = ['"=r"(%s[%d])' % (c, k) for c, n in outs for k in range(n)] + ['"+r"(%s[%d])' % (c, k) for c, n in inouts for k in range(n)]
+    o.append("        : %s" % ", ".join(cons))
+    o.append("        : %s);" % ", ".join('"r"(%s[%d])' % (c, k) for c, n in ins for k in range(n)))
+    o.append("}")
+    o.append("")
+    return "\n".join(o)
+
+
+# Karatsuba levels of <tag>_mul_regs (0 = the interleaved CIOS form). Override: ZECALE_FQ_KARA / ZECALE_FR_KARA.
+KARA_LEVELS = {"fq": int(os.environ.get("ZECALE_FQ_KARA", "1")), "fr": int(os.environ.get("ZECALE_FR_KARA", "0"))}
+
+
+def n_wide(em):
+    """wide MADs of a body (lo/hi pairs fuse into one IMAD.WIDE) + the single-word MULs by inv."""
+    return sum(1 for l in em.lines if l.startswith(("mul.lo", "mad.lo", "madc.lo")))
+
+
 def wrap(name, N, em, n_in, doc):
     """Emit a __forceinline__ device function around one asm block."""
     out = []
@@ -218,8 +467,24 @@ def gen_field(tag, N, P, inv):
     a_op = lambda k: "%%%d" % (N + k)
     b_op = lambda k: "%%%d" % (2 * N + k)
     s = []
-    s.append(wrap("%s_mul_regs" % tag, N, gen_mul(N, P, inv, a_op, b_op, r_op), 2,
-                  "r = a*b/R mod p  (Montgomery product, fully reduced). %d wide MADs." % (2 * N * N)))
+    lv = KARA_LEVELS.get(tag, 0)
+    if lv:
+        em = gen_mul_kara(N, P, inv, a_op, b_op, r_op, lv)
+        s.append(wrap("%s_mul_regs" % tag, N, em, 2,
+                      "r = a*b/R mod p  (Montgomery product, fully reduced): %d-level Karatsuba product + word-serial "
+                      "reduction, %d wide MADs." % (lv, n_wide(em) - N)))
+        pc = lambda base: (lambda k: "%%%d" % (base + k))
+        s.append(wrap_io("%s_mulw_regs" % tag, gen_mulw(N, pc(2 * N), pc(3 * N), pc(0), lv), [("p", 2 * N)], [("a", N), ("b", N)], [],
+                         "p = a*b, 2N limbs, unreduced (the product half of %s_mul_regs)." % tag))
+        s.append(wrap_io("%s_wsubk_regs" % tag, gen_wsubk(N, P, pc(0), pc(2 * N)), [], [("p", 2 * N)], [("w", 2 * N)],
+                         "w = w - p + q^2 (difference of two unreduced products, kept in [0, qR) for %s_redc_regs)." % tag))
+        s.append(wrap_io("%s_redc_regs" % tag, gen_redc_only(N, P, inv, pc(N), pc(0)), [("r", N)], [("p", 2 * N)], [],
+                         "r = p/R mod q for p < qR, canonical (the reduction half of %s_mul_regs)." % tag))
+        s.append(wrap("%s_mul_cios_regs" % tag, N, gen_mul(N, P, inv, a_op, b_op, r_op), 2,
+                      "the interleaved (CIOS) form of the same product, %d wide MADs; kept for the field tests." % (2 * N * N)))
+    else:
+        s.append(wrap("%s_mul_regs" % tag, N, gen_mul(N, P, inv, a_op, b_op, r_op), 2,
+                      "r = a*b/R mod p  (Montgomery product, fully reduced). %d wide MADs." % (2 * N * N)))
     s.append(wrap("%s_sqr_regs" % tag, N, gen_mul(N, P, inv, a_op, a_op, r_op, square=True), 1,
                   "r = a*a/R mod p. %d wide MADs (even columns below the diagonal dropped)." % (2 * N * N - N * N // 4)))
     s.append(wrap("%s_add_regs" % tag, N, gen_add(N, P, a_op, b_op, r_op), 2, "r = a+b mod p."))
@@ -275,13 +540,14 @@ def gen_consts():
 
 def main():
     dstc = os.path.join(os.path.dirname(__file__), "..", "zecale_b200", "csrc", "field_consts.cuh")
-    with open(dstc, "w") as f:
-        f.write(gen_consts())
+    if not os.environ.get("ZECALE_FIELD_ASM_OUT"):
+        with open(dstc, "w") as f:
+            f.write(gen_consts())
     out = HEADER
     out += gen_field("fq", C.FQ_LIMBS32, C.Q, C.FQ["inv32"])
     out += gen_field("fr", C.FR_LIMBS32, C.R, C.FR["inv32"])
     out += "\n} // namespace zecale\n"
-    dst = os.path.join(os.path.dirname(__file__), "..", "zecale_b200", "csrc", "field_asm.cuh")
+    dst = os.environ.get("ZECALE_FIELD_ASM_OUT") or os.path.join(os.path.dirname(__file__), "..", "zecale_b200", "csrc", "field_asm.cuh")
     with open(dst, "w") as f:
         f.write(out)
     print("wrote", os.path.abspath(dst), len(out.splitlines()), "lines")

@@ -18,11 +18,14 @@ import re
 
 SLOTS = {"X": 0, "Y": 1, "ZZ": 2, "ZZZ": 3, "QX": 4, "QY": 5, "QZZ": 6, "QZZZ": 7,
          "T0": 8, "T1": 9, "T2": 10, "T3": 11, "T4": 12, "RX": 13, "RY": 14, "RZZ": 15, "RZZZ": 16,
-         "K0": 17, "K1": 18}
-NSLOT = 19
+         "K0": 17, "K1": 18, "W0": 19, "W1": 20}
+NSLOT = 21
 
-OPS = {"MUL": 0, "ADD": 1, "SUB": 2, "MOV": 3, "ONE": 4, "ZERO": 5, "JZ": 6, "JMP": 7, "JBIT": 8,
-       "DECJNZ": 9, "SETCNT": 10, "CALL": 11, "RET": 12, "HOOK": 13, "HALT": 14, "INVP": 15, "LDR3": 16}
+# MULW c, e ; MULFIN d, a, b: d = a*b - c*e with ONE Montgomery reduction. MULW leaves the unreduced 1536-bit product
+# c*e in the wide slot pair (W0, W1); MULFIN subtracts it from a*b before reducing (fq_mulw_regs, fq_wsubk_regs,
+# fq_redc_regs in field_asm.cuh).
+OPS = {"MUL": 0, "ADD": 1, "SUB": 2, "MULW": 3, "MULFIN": 4, "MOV": 5, "ONE": 6, "ZERO": 7, "JZ": 8, "JMP": 9, "JBIT": 10,
+       "DECJNZ": 11, "SETCNT": 12, "CALL": 13, "RET": 14, "HOOK": 15, "HALT": 16, "INVP": 17, "LDR3": 18}
 
 PROGRAM = r"""
 ; ---------------------------------------------------------------- acc += (QX, QY) affine, not infinity
@@ -43,9 +46,8 @@ madd:
     SUB  T2, T2, T3
     SUB  X, T2, T3          ; X3 = R^2 - PPP - 2Q
     SUB  T3, T3, X
-    MUL  T3, T1, T3
-    MUL  T2, Y, T0
-    SUB  Y, T3, T2          ; Y3 = R(Q - X3) - Y1*PPP
+    MULW Y, T0
+    MULFIN Y, T1, T3        ; Y3 = R(Q - X3) - Y1*PPP
     HOOK 0
 madd_accinf:
     MOV  X, QX
@@ -68,9 +70,8 @@ mdbl:                       ; acc = 2*(QX, QY)
     SUB  T4, T4, T3
     SUB  X, T4, T3          ; X3 = M^2 - 2S
     SUB  T4, T3, X
-    MUL  T4, T0, T4
-    MUL  T0, T2, QY
-    SUB  Y, T4, T0          ; Y3 = M(S - X3) - W Y1
+    MULW T2, QY
+    MULFIN Y, T0, T4        ; Y3 = M(S - X3) - W Y1
     MOV  ZZ, T1
     MOV  ZZZ, T2
     HOOK 0
@@ -228,9 +229,8 @@ add{S}:
     SUB  T4, T4, T0
     SUB  {AX}, T4, T0         ; X3
     SUB  T0, T0, {AX}
-    MUL  T0, T3, T0
-    MUL  T2, T2, T1
-    SUB  {AY}, T0, T2         ; Y3
+    MULW T2, T1
+    MULFIN {AY}, T3, T0       ; Y3 = R(Q - X3) - S1 PPP
 add_done{S}:
     HOOK 0
 add_accinf{S}:
@@ -261,9 +261,8 @@ dbl{S}:
     SUB  T4, T4, T3
     SUB  {AX}, T4, T3         ; X3
     SUB  T4, T3, {AX}
-    MUL  T4, T0, T4
-    MUL  T0, T2, {AY}
-    SUB  {AY}, T4, T0         ; Y3
+    MULW T2, {AY}
+    MULFIN {AY}, T0, T4       ; Y3 = M(S - X3) - W Y1
     MUL  {AZZ}, T1, {AZZ}
     MUL  {AZZZ}, T2, {AZZZ}
 dbl_done{S}:
@@ -288,15 +287,17 @@ def slot(x):
 def assemble(text):
     lines = []
     labels = {}
+    addr = 0
     for raw in text.splitlines():
         ln = raw.split(";")[0].strip()
         if not ln:
             continue
         m = re.match(r"^([A-Za-z_][A-Za-z_0-9]*):$", ln)
         if m:
-            labels[m.group(1)] = len(lines)
+            labels[m.group(1)] = addr
             continue
         lines.append(ln)
+        addr += 1
     code = []
     for ln in lines:
         parts = ln.replace(",", " ").split()
@@ -304,7 +305,10 @@ def assemble(text):
         args = parts[1:]
         o = OPS[op]
         d = a = b = 0
-        if op in ("MUL", "ADD", "SUB"):
+        if op == "MULW":
+            a, b = (slot(x) for x in args)
+            imm = a | (b << 8)
+        elif op in ("MUL", "ADD", "SUB", "MULFIN"):
             d, a, b = (slot(x) for x in args)
             imm = a | (b << 8)
         elif op in ("MOV", "INVP"):

@@ -55,6 +55,20 @@ def run(lines, regs):
             regs[args[0]] = val(args[1]) & val(args[2])
         elif base == "xor":
             regs[args[0]] = val(args[1]) ^ val(args[2])
+        elif base == "lop3":  # lop3.b32 d, a, b, c, immLut
+            a, b, c, lut = val(args[1]), val(args[2]), val(args[3]), val(args[4])
+            r = 0
+            for bit in range(8):
+                if (lut >> bit) & 1:
+                    ta = a if bit & 4 else ~a
+                    tb = b if bit & 2 else ~b
+                    tc = c if bit & 1 else ~c
+                    r |= ta & tb & tc
+            regs[args[0]] = r & M32
+        elif base == "mov":
+            regs[args[0]] = val(args[1])
+        elif base == "not":
+            regs[args[0]] = ~val(args[1]) & M32
         elif base == "setp":
             pred[args[0]] = val(args[1]) != val(args[2])
         elif base == "selp":

@@ -82,6 +82,7 @@ EXPORTS = {
     "zecale_gpu_test_fr": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
     "zecale_gpu_test_group": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
     "zecale_gpu_bench_fq_mul": (_i, [_vp, _u, _u, _u, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_bench_imad": (_i, [_vp, _u, _u, _u, ctypes.POINTER(ctypes.c_float)]),
 }
 
 for _name, (_res, _args) in EXPORTS.items():
@@ -360,6 +361,12 @@ class Context:
     def bench_fq_mul(self, blocks, threads_per_block, iters):
         ms = ctypes.c_float()
         self._ck(_lib.zecale_gpu_bench_fq_mul(self._h, blocks, threads_per_block, iters, ctypes.byref(ms)))
+        return ms.value
+
+    def bench_imad(self, blocks, threads_per_block, iters):
+        """ms for blocks * threads_per_block threads x 8 * iters dependent IMAD.WIDE.U32 (8 independent chains per thread)."""
+        ms = ctypes.c_float()
+        self._ck(_lib.zecale_gpu_bench_imad(self._h, blocks, threads_per_block, iters, ctypes.byref(ms)))
         return ms.value
 
 

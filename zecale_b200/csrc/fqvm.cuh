@@ -311,16 +311,39 @@ __device__ __forceinline__ void fqvm_run_impl(SF &S, uint32_t pc, Hook &&hook, c
         const uint32_t u = FQVM_CODE[pc++];
         const uint32_t op = u & 0xffu, imm = u >> 16;
         const uint32_t d = op <= VOP_JZ ? rs((u >> 8) & 0xffu) : (u >> 8) & 0xffu;
-        if (op <= VOP_SUB) {
+        if (op <= VOP_MULFIN) {
             uint32_t x[24], y[24], z[24];
             vs_load(x, S, rs(imm & 0xffu));
             vs_load(y, S, rs(imm >> 8));
-            if (op == VOP_MUL)
-                fq_mul_regs(z, x, y);
-            else if (op == VOP_ADD)
+            if (op == VOP_ADD)
                 fq_add_regs(z, x, y);
-            else
+            else if (op == VOP_SUB)
                 fq_sub_regs(z, x, y);
+            else {
+                // product and reduction are separate bodies (field_asm.cuh), one copy of each per kernel: MUL = mulw + redc;
+                // MULW c, e stashes the unreduced c*e in the wide slot pair; MULFIN d, a, b reduces a*b - c*e + q^2 ONCE.
+                uint32_t w[48];
+                fq_mulw_regs(w, x, y);
+                uint4 *ws = S.w + VS_W0 * 6;
+                if (op == VOP_MULW) {
+#pragma unroll
+                    for (int k = 0; k < 12; k++) ws[k] = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+                    continue;
+                }
+                if (op == VOP_MULFIN) {
+                    uint32_t t[48];
+#pragma unroll
+                    for (int k = 0; k < 12; k++) {
+                        const uint4 v = ws[k];
+                        t[4 * k] = v.x;
+                        t[4 * k + 1] = v.y;
+                        t[4 * k + 2] = v.z;
+                        t[4 * k + 3] = v.w;
+                    }
+                    fq_wsubk_regs(w, t);
+                }
+                fq_redc_regs(z, w);
+            }
             vs_store(S, d, z);
             continue;
         }

@@ -34,6 +34,11 @@
 
 namespace zecale {
 
+// resident CTAs per SM of k_accumulate (register cap 65536 / (128 * ZG_ACC_CTAS))
+#ifndef ZG_ACC_CTAS
+#define ZG_ACC_CTAS 3
+#endif
+
 static constexpr int FR_SCALAR_BITS = 377;
 static constexpr uint32_t MSM_MAX_TASKS_PER_BUCKET = 256;
 static constexpr uint64_t MSM_TARGET_TASKS = 3ull * 148 * 3 * 128;
@@ -563,7 +568,7 @@ __global__ void k_task_order(const uint32_t *task_off_total, const uint32_t *tas
 
 // ------------------------------------------------------------------ accumulate
 // One thread per task: partial[t] = sum of its entries (mixed additions).
-__global__ void __launch_bounds__(128, 3)
+__global__ void __launch_bounds__(128, ZG_ACC_CTAS)
 k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint32_t *order, const uint32_t *task_start,
              const uint32_t *task_len, const uint32_t *entries, XYZZ *partial)
 {

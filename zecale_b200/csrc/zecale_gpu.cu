@@ -701,6 +701,22 @@ __global__ void __launch_bounds__(128, 2) k_bench_fq_mul(Fq *sink, unsigned iter
     if (x[0] == 0x12345678u && x[5] == 77u) vs_get(sink, S, VS_K1); // keep the chain alive
 }
 
+// Pipe-rate probe: 8 independent chains of IMAD.WIDE.U32 per thread (the operand is perturbed by a LOP3 so the
+// chain cannot be strength-reduced); 8 * iters wide multiply-adds per thread.
+__global__ void __launch_bounds__(256) k_bench_imad(uint64_t *sink, uint32_t a, uint32_t b, unsigned iters)
+{
+    uint64_t x[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) x[k] = threadIdx.x + k;
+    for (unsigned i = 0; i < iters; i++)
+#pragma unroll
+        for (int k = 0; k < 8; k++) x[k] = (uint64_t)((uint32_t)x[k] ^ a) * b + x[k];
+    uint64_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += x[k];
+    if (s == 0x123456789abcdefull) sink[0] = s; // keep the chains alive
+}
+
 // out = sum of n projective points (any Z), normalised to libff special form. One thread: n is
 // the number of ranks / chunks (multi_exp's serial "final = final + partial[i]", multiexp.tcc:680-685).
 __global__ void __launch_bounds__(32, 1) k_point_sum(const Proj *pts, uint32_t n, Proj *out)
@@ -1953,6 +1969,25 @@ int zecale_gpu_bench_fq_mul(zecale_gpu_ctx *ctx, unsigned blocks, unsigned tpb, 
     k_bench_fq_mul<<<blocks, tpb, 0, ctx->cur->stream>>>((Fq *)ctx->ws_tmp.p, 8); // warm-up
     CK(cudaEventRecord(ctx->cur->ev0, ctx->cur->stream));
     k_bench_fq_mul<<<blocks, tpb, 0, ctx->cur->stream>>>((Fq *)ctx->ws_tmp.p, iters);
+    CK(cudaEventRecord(ctx->cur->ev1, ctx->cur->stream));
+    ctx->launches += 2;
+    CK(cudaStreamSynchronize(ctx->cur->stream));
+    CK(cudaEventElapsedTime(elapsed_ms, ctx->cur->ev0, ctx->cur->ev1));
+    return 0;
+}
+
+int zecale_gpu_bench_imad(zecale_gpu_ctx *ctx, unsigned blocks, unsigned tpb, unsigned iters, float *elapsed_ms)
+{
+    if (!ctx) return ZECALE_GPU_E_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->cur = &ctx->lanes[0];
+    if (!blocks || !tpb || tpb > 256 || !elapsed_ms || !iters) return fail(ctx, ZECALE_GPU_E_ARG, "bench_imad: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    int rc = reserve(ctx, ctx->ws_tmp, sizeof(Fq));
+    if (rc) return rc;
+    k_bench_imad<<<blocks, tpb, 0, ctx->cur->stream>>>((uint64_t *)ctx->ws_tmp.p, 0x9e3779b9u, 0x85ebca6bu, 8); // warm-up
+    CK(cudaEventRecord(ctx->cur->ev0, ctx->cur->stream));
+    k_bench_imad<<<blocks, tpb, 0, ctx->cur->stream>>>((uint64_t *)ctx->ws_tmp.p, 0x9e3779b9u, 0x85ebca6bu, iters);
     CK(cudaEventRecord(ctx->cur->ev1, ctx->cur->stream));
     ctx->launches += 2;
     CK(cudaStreamSynchronize(ctx->cur->stream));
