@@ -215,6 +215,7 @@ def school_product(em, A, B):
     O = [em.fresh() for _ in range(n)]
     out = []
     x = None
+    tops = {}
     for i in range(n):
         bi = B[i]
         if i == 0:
@@ -224,39 +225,41 @@ def school_product(em, A, B):
             for j in range(1, n, 2):
                 em.op("mul.lo.u32 %s, %s, %s;" % (O[j - 1], A[j], bi))
                 em.op("mul.hi.u32 %s, %s, %s;" % (O[j], A[j], bi))
-            top = None
         else:
             em.op("add.cc.u32 %s, %s, %s;" % (E[0], E[0], x))   # pending word; its carry enters the odd chain
             for j in range(1, n, 2):
-                if O[j - 1] is None:                              # the carry word of row 0 (no even chain yet)
-                    lo = em.fresh()
+                if j == n - 1:
+                    # the top pair of the odd vector is always empty: the carry word of the even chain is NOT folded
+                    # back in (a (carry, 0) register pair as 64-bit addend costs ptxas a zeroing move per row and
+                    # often splits the wide MAD); it is added once, in the final merge.
+                    lo, nw = em.fresh(), em.fresh()
                     em.op("madc.lo.cc.u32 %s, %s, %s, 0;" % (lo, A[j], bi))
-                    O[j - 1] = lo
+                    em.op("madc.hi.u32 %s, %s, %s, 0;" % (nw, A[j], bi))
+                    O[j - 1], O[j] = lo, nw
                 else:
                     em.op("madc.lo.cc.u32 %s, %s, %s, %s;" % (O[j - 1], A[j], bi, O[j - 1]))
-                if j == n - 1:
-                    nw = em.fresh()
-                    em.op("madc.hi.u32 %s, %s, %s, 0;" % (nw, A[j], bi))
-                    O[j] = nw
-                else:
                     em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (O[j], A[j], bi, O[j]))
             for j in range(0, n, 2):
                 c0 = "mad.lo.cc.u32" if j == 0 else "madc.lo.cc.u32"
                 em.op("%s %s, %s, %s, %s;" % (c0, E[j], A[j], bi, E[j]))
                 em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], A[j], bi, E[j + 1]))
-            top = em.fresh()
-            em.op("addc.u32 %s, 0, 0;" % top)
+            tops[i] = em.fresh()                                  # weight 2^(32 (n + i)): limb i of the high half
+            em.op("addc.u32 %s, 0, 0;" % tops[i])
         out.append(E[0])                                          # limb i of the product is final
         x = E[1]
-        E, O = O, E[2:] + [top, None]
-    # remaining n limbs: E + x + O*2^32 (O[n-1] is None; O[n-2] is None only for n == 2 rows... never: n >= 2)
+        E, O = O, E[2:] + [None, None]
+    # remaining n limbs: E + x + O*2^32 + the deferred carry words
     hi = [em.fresh() for _ in range(n)]
     em.op("add.cc.u32 %s, %s, %s;" % (hi[0], E[0], x))
     for k in range(1, n):
         cc = "addc.cc.u32" if k < n - 1 else "addc.u32"
         o = O[k - 1]
         em.op("%s %s, %s, %s;" % (cc, hi[k], E[k], o if o is not None else "0"))
-    return out + hi
+    hi2 = [hi[0]] + [em.fresh() for _ in range(n - 1)]
+    for k in range(1, n):
+        cc = "add.cc.u32" if k == 1 else ("addc.cc.u32" if k < n - 1 else "addc.u32")
+        em.op("%s %s, %s, %s;" % (cc, hi2[k], hi[k], tops[k]))
+    return out + hi2
 
 
 def abs_diff(em, X, Y):
@@ -328,6 +331,7 @@ def gen_redc(em, N, q, inv, Pw, r_op):
     E = list(Pw[:N])
     O = [None] * N
     x = None
+    tops = []
     for i in range(N):
         m = em.fresh()
         if i > 0:
@@ -342,7 +346,7 @@ def gen_redc(em, N, q, inv, Pw, r_op):
                 em.op("mul.hi.u32 %s, %s, %s;" % (hi, m, imm(q[j])))
             else:
                 c0 = "madc.lo.cc.u32" if (i > 0 or j > 1) else "mad.lo.cc.u32"
-                em.op("%s %s, %s, %s, %s;" % (c0, lo, m, imm(q[j]), O[j - 1]))
+                em.op("%s %s, %s, %s, %s;" % (c0, lo, m, imm(q[j]), O[j - 1] if O[j - 1] is not None else "0"))
                 c1 = "madc.hi.u32" if j == N - 1 else "madc.hi.cc.u32"
                 em.op("%s %s, %s, %s, %s;" % (c1, hi, m, imm(q[j]), O[j] if O[j] is not None else "0"))
             O[j - 1], O[j] = lo, hi
@@ -353,20 +357,25 @@ def gen_redc(em, N, q, inv, Pw, r_op):
             em.op("%s %s, %s, %s, %s;" % (c0, lo, m, imm(q[j]), E[j]))
             em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (hi, m, imm(q[j]), E[j + 1]))
             nE[j], nE[j + 1] = lo, hi
-        top = em.fresh()
-        em.op("addc.u32 %s, 0, 0;" % top)
+        tops.append(em.fresh())                                   # weight 2^(32 (N + i)): limb i after the division by R
+        em.op("addc.u32 %s, 0, 0;" % tops[i])
         x = nE[1]
-        E, O = O, nE[2:] + [top, None]
-    # T = E + x + O*2^32 <= q, then + P_hi (< q): < 2q
+        E, O = O, nE[2:] + [None, None]
+    # T = E + x + O*2^32 + deferred carry words <= q, then + P_hi (< q): < 2q
     T = [em.fresh() for _ in range(N)]
     em.op("add.cc.u32 %s, %s, %s;" % (T[0], E[0], x))
     for k in range(1, N):
         cc = "addc.cc.u32" if k < N - 1 else "addc.u32"
-        em.op("%s %s, %s, %s;" % (cc, T[k], E[k], O[k - 1]))
+        o = O[k - 1]
+        em.op("%s %s, %s, %s;" % (cc, T[k], E[k], o if o is not None else "0"))
+    V = [em.fresh() for _ in range(N)]
+    for k in range(N):
+        cc = "add.cc.u32" if k == 0 else ("addc.cc.u32" if k < N - 1 else "addc.u32")
+        em.op("%s %s, %s, %s;" % (cc, V[k], Pw[N + k], tops[k]))
     U = [em.fresh() for _ in range(N)]
     for k in range(N):
         cc = "add.cc.u32" if k == 0 else ("addc.cc.u32" if k < N - 1 else "addc.u32")
-        em.op("%s %s, %s, %s;" % (cc, U[k], T[k], Pw[N + k]))
+        em.op("%s %s, %s, %s;" % (cc, U[k], T[k], V[k]))
     gen_final_sub(em, N, q, U, r_op)
 
 
