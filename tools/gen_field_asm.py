@@ -280,18 +280,93 @@ def abs_diff(em, X, Y):
     return r, bw
 
 
-def kara_product(em, A, B, levels):
-    """A*B as 2n limb names; `levels` Karatsuba levels above schoolbook rows."""
+def signed_cross(em, zi, zj, mm, sa, sb):
+    """zi + zj -+ mm (n limbs each) -> n + 1 limbs: a_i b_j + a_j b_i from the three products of a Karatsuba step;
+    mm = |a_i - a_j| |b_i - b_j| is subtracted when the two differences have the same sign (masks sa, sb)."""
+    n = len(zi)
+    t = [em.fresh() for _ in range(n + 1)]
+    for k in range(n):
+        em.op("%s %s, %s, %s;" % ("add.cc.u32" if k == 0 else "addc.cc.u32", t[k], zi[k], zj[k]))
+    em.op("addc.u32 %s, 0, 0;" % t[n])
+    neg = em.fresh()
+    em.op("xor.b32 %s, %s, %s;" % (neg, sa, sb))
+    em.op("xor.b32 %s, %s, 0xffffffff;" % (neg, neg))
+    w = [em.fresh() for _ in range(n)]
+    for k in range(n):
+        em.op("xor.b32 %s, %s, %s;" % (w[k], mm[k], neg))
+    z1 = [em.fresh() for _ in range(n + 1)]
+    junk = em.fresh()
+    em.op("add.cc.u32 %s, %s, %s;" % (junk, neg, neg))            # carry = 1 iff subtracting (the +1 of -mm)
+    for k in range(n):
+        em.op("addc.cc.u32 %s, %s, %s;" % (z1[k], t[k], w[k]))
+    em.op("addc.u32 %s, %s, %s;" % (z1[n], t[n], neg))
+    return z1
+
+
+def add_at(em, X, Y, off):
+    """X + Y * 2^(32 off) for limb-name lists (None = zero limb); the result has max(len) limbs, the final carry is
+    dropped (callers know the sum fits)."""
+    L = max(len(X), off + len(Y))
+    out = []
+    started = False
+    for k in range(L):
+        x = X[k] if k < len(X) else None
+        y = Y[k - off] if 0 <= k - off < len(Y) else None
+        if not started and y is None:
+            out.append(x)
+            continue
+        r = em.fresh()
+        last = k == L - 1
+        if not started:
+            op = "add.u32" if last else "add.cc.u32"
+            started = True
+        else:
+            op = "addc.u32" if last else "addc.cc.u32"
+        em.op("%s %s, %s, %s;" % (op, r, x if x is not None else "0", y if y is not None else "0"))
+        out.append(r)
+    return out
+
+
+def three_way_product(em, A, B, sub):
+    """Karatsuba with three parts: 6 products of n/3 limbs instead of 9."""
     n = len(A)
-    if levels == 0 or n % 4 != 0:
+    s = n // 3
+    a = [A[i * s:(i + 1) * s] for i in range(3)]
+    b = [B[i * s:(i + 1) * s] for i in range(3)]
+    z = [kara_product(em, a[i], b[i], sub) for i in range(3)]
+    cross = {}
+    for i, j in ((0, 1), (0, 2), (1, 2)):
+        da, sa = abs_diff(em, a[i], a[j])
+        db, sb = abs_diff(em, b[i], b[j])
+        mm = kara_product(em, da, db, sub)
+        cross[(i, j)] = signed_cross(em, z[i], z[j], mm, sa, sb)
+    # P = z0 | z1 | z2 (disjoint 2s-limb blocks) + (c01 + c02 B + c12 B^2) B,  B = 2^(32 s)
+    M = add_at(em, cross[(0, 1)] + [None] * (2 * s), cross[(0, 2)], s)
+    M = add_at(em, M, cross[(1, 2)], 2 * s)
+    out = add_at(em, z[0] + z[1] + z[2], M, s)
+    assert len(out) == 2 * n
+    return out
+
+
+def kara_product(em, A, B, levels):
+    """A*B as 2n limb names. `levels`: 0 = schoolbook rows; k > 0 = k two-way Karatsuba levels; a 3-tuple = one
+    two-way level whose three sub-products (low, high, middle) use the given specs; "t3" = one three-way level."""
+    n = len(A)
+    if levels == "t3" and n % 6 == 0:
+        return three_way_product(em, A, B, 0)
+    if isinstance(levels, tuple):
+        subs = levels
+    elif levels == 0 or n % 4 != 0:
         return school_product(em, A, B)
+    else:
+        subs = (levels - 1,) * 3
     h = n // 2
     a0, a1, b0, b1 = A[:h], A[h:], B[:h], B[h:]
     da, sa = abs_diff(em, a0, a1)
     db, sb = abs_diff(em, b0, b1)
-    z0 = kara_product(em, a0, b0, levels - 1)
-    z2 = kara_product(em, a1, b1, levels - 1)
-    mm = kara_product(em, da, db, levels - 1)
+    z0 = kara_product(em, a0, b0, subs[0])
+    z2 = kara_product(em, a1, b1, subs[1])
+    mm = kara_product(em, da, db, subs[2])
     # t = z0 + z2 (n limbs + carry limb)
     t = [em.fresh() for _ in range(n + 1)]
     for k in range(n):
@@ -440,7 +515,16 @@ def wrap_io(name, em, outs, ins, inouts, doc):
 
 
 # Karatsuba levels of <tag>_mul_regs (0 = the interleaved CIOS form). Override: ZECALE_FQ_KARA / ZECALE_FR_KARA.
-KARA_LEVELS = {"fq": int(os.environ.get("ZECALE_FQ_KARA", "1")), "fr": int(os.environ.get("ZECALE_FR_KARA", "0"))}
+def _kara_spec(v):
+    """"1" -> 1, "t3" -> "t3", "1,0,0" -> (1, 0, 0)."""
+    if v == "t3":
+        return v
+    if "," in v:
+        return tuple(int(x) for x in v.split(","))
+    return int(v)
+
+
+KARA_LEVELS = {"fq": _kara_spec(os.environ.get("ZECALE_FQ_KARA", "1")), "fr": _kara_spec(os.environ.get("ZECALE_FR_KARA", "0"))}
 
 
 def n_wide(em):
@@ -480,7 +564,7 @@ def gen_field(tag, N, P, inv):
     if lv:
         em = gen_mul_kara(N, P, inv, a_op, b_op, r_op, lv)
         s.append(wrap("%s_mul_regs" % tag, N, em, 2,
-                      "r = a*b/R mod p  (Montgomery product, fully reduced): %d-level Karatsuba product + word-serial "
+                      "r = a*b/R mod p  (Montgomery product, fully reduced): Karatsuba product (spec %s) + word-serial "
                       "reduction, %d wide MADs." % (lv, n_wide(em) - N)))
         pc = lambda base: (lambda k: "%%%d" % (base + k))
         s.append(wrap_io("%s_mulw_regs" % tag, gen_mulw(N, pc(2 * N), pc(3 * N), pc(0), lv), [("p", 2 * N)], [("a", N), ("b", N)], [],
