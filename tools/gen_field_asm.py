@@ -44,10 +44,13 @@ def imm(x):
     return "0x%08x" % x
 
 
-def gen_mul(N, P, inv, a_op, b_op, r_op, square=False):
-    """a_op(j), b_op(i), r_op(k) -> PTX operand strings (%k placeholders)."""
+def gen_mul(N, P, inv, a_op, b_op, r_op, square=False, q_op=None, inv_only=False):
+    """a_op(j), b_op(i), r_op(k) -> PTX operand strings (%k placeholders). q_op(j): operand holding limb j of the
+    modulus in the m*q chains (default: an immediate)."""
     q = C.limbs32(P, N)
     em = Emit()
+    qm = (lambda j: q_op(j)) if (q_op and not inv_only) else (lambda j: imm(q[j]))
+    invm = q_op(N) if q_op else imm(inv)          # with q_op, operand N of the modulus array holds inv
     E = [em.fresh() for _ in range(N)]
     O = [em.fresh() for _ in range(N)]
     top = em.fresh()
@@ -86,12 +89,12 @@ def gen_mul(N, P, inv, a_op, b_op, r_op, square=False):
             for j in range(1, N, 2):
                 em.op("mul.lo.u32 %s, %s, %s;" % (O[j - 1], col(j), bi))
                 em.op("mul.hi.u32 %s, %s, %s;" % (O[j], col(j), bi))
-            em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], imm(inv)))
+            em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], invm))
             # even q chain
             for j in range(0, N, 2):
                 c0 = "mad.lo.cc.u32" if j == 0 else "madc.lo.cc.u32"
-                em.op("%s %s, %s, %s, %s;" % (c0, E[j], m, imm(q[j]), E[j]))
-                em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], m, imm(q[j]), E[j + 1]))
+                em.op("%s %s, %s, %s, %s;" % (c0, E[j], m, qm(j), E[j]))
+                em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], m, qm(j), E[j + 1]))
             em.op("addc.u32 %s, 0, 0;" % top)
         else:
             # fold pending word; its carry (weight 2^32) enters the odd chain
@@ -121,18 +124,18 @@ def gen_mul(N, P, inv, a_op, b_op, r_op, square=False):
                 em.op("add.u32 %s, 0, 0;" % top)
             else:
                 em.op("addc.u32 %s, 0, 0;" % top)
-            em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], imm(inv)))
+            em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], invm))
             for j in range(0, N, 2):
                 c0 = "mad.lo.cc.u32" if j == 0 else "madc.lo.cc.u32"
-                em.op("%s %s, %s, %s, %s;" % (c0, E[j], m, imm(q[j]), E[j]))
-                em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], m, imm(q[j]), E[j + 1]))
+                em.op("%s %s, %s, %s, %s;" % (c0, E[j], m, qm(j), E[j]))
+                em.op("madc.hi.cc.u32 %s, %s, %s, %s;" % (E[j + 1], m, qm(j), E[j + 1]))
             em.op("addc.u32 %s, %s, 0;" % (top, top))
         # odd q chain (never carries out)
         for j in range(1, N, 2):
             c0 = "mad.lo.cc.u32" if j == 1 else "madc.lo.cc.u32"
-            em.op("%s %s, %s, %s, %s;" % (c0, O[j - 1], m, imm(q[j]), O[j - 1]))
+            em.op("%s %s, %s, %s, %s;" % (c0, O[j - 1], m, qm(j), O[j - 1]))
             c1 = "madc.hi.u32" if j == N - 1 else "madc.hi.cc.u32"
-            em.op("%s %s, %s, %s, %s;" % (c1, O[j], m, imm(q[j]), O[j]))
+            em.op("%s %s, %s, %s, %s;" % (c1, O[j], m, qm(j), O[j]))
         # divide by 2^32: rename
         x = E[1]
         newO = E[2:] + [top, None]
@@ -352,6 +355,8 @@ def kara_product(em, A, B, levels):
     """A*B as 2n limb names. `levels`: 0 = schoolbook rows; k > 0 = k two-way Karatsuba levels; a 3-tuple = one
     two-way level whose three sub-products (low, high, middle) use the given specs; "t3" = one three-way level."""
     n = len(A)
+    if levels == "s":
+        return school_product(em, A, B)
     if levels == "t3" and n % 6 == 0:
         return three_way_product(em, A, B, 0)
     if isinstance(levels, tuple):
@@ -516,8 +521,8 @@ def wrap_io(name, em, outs, ins, inouts, doc):
 
 # Karatsuba levels of <tag>_mul_regs (0 = the interleaved CIOS form). Override: ZECALE_FQ_KARA / ZECALE_FR_KARA.
 def _kara_spec(v):
-    """"1" -> 1, "t3" -> "t3", "1,0,0" -> (1, 0, 0)."""
-    if v == "t3":
+    """"1" -> 1, "t3" -> "t3", "1,0,0" -> (1, 0, 0), "s" -> separated schoolbook product + reduction (no Karatsuba)."""
+    if v in ("t3", "s"):
         return v
     if "," in v:
         return tuple(int(x) for x in v.split(","))
@@ -525,6 +530,9 @@ def _kara_spec(v):
 
 
 KARA_LEVELS = {"fq": _kara_spec(os.environ.get("ZECALE_FQ_KARA", "1")), "fr": _kara_spec(os.environ.get("ZECALE_FR_KARA", "0"))}
+
+
+Q_FROM_REGS = {"fr": int(os.environ.get("ZECALE_FR_QREGS", "2"))}      # 1: modulus limbs and inv from registers, 2: inv only
 
 
 def n_wide(em):
@@ -575,6 +583,21 @@ def gen_field(tag, N, P, inv):
                          "r = p/R mod q for p < qR, canonical (the reduction half of %s_mul_regs)." % tag))
         s.append(wrap("%s_mul_cios_regs" % tag, N, gen_mul(N, P, inv, a_op, b_op, r_op), 2,
                       "the interleaved (CIOS) form of the same product, %d wide MADs; kept for the field tests." % (2 * N * N)))
+    elif Q_FROM_REGS.get(tag):
+        # inv (mode 2), or inv and the modulus limbs (mode 1), reach the body through registers / the constant bank instead of
+        # as immediates. Fr has inv = 0xffffffff: told so, ptxas replaces m = T0 * inv by a negation and then splits every wide MAD
+        # of the m*q chains into IMAD.X + IMAD.HI.U32.X (6 pipe cycles for 4; k_ntt_pass: 1815 -> 1348 FMA-pipe instructions).
+        inv_only = Q_FROM_REGS[tag] == 2
+        nq = 1 if inv_only else N + 1
+        q_op = (lambda k: "%%%d" % (3 * N)) if inv_only else (lambda k: "%%%d" % (3 * N + k))
+        em = gen_mul(N, P, inv, a_op, b_op, r_op, q_op=q_op, inv_only=inv_only)
+        s.append(wrap_io("%s_mul_q_regs" % tag, em, [("r", N)], [("a", N), ("b", N), ("q", nq)], [],
+                         "r = a*b/R mod p (Montgomery product, fully reduced), %d wide MADs; q = {inv} or {modulus limbs, inv}, "
+                         "opaque to the compiler." % (2 * N * N)))
+        fill = "" if inv_only else "#pragma unroll\n    for (int k = 0; k < %d; k++) q[k] = %s_P[k];\n" % (N, tag.upper())
+        s.append("__device__ __forceinline__ void %s_mul_regs(uint32_t (&r)[%d], const uint32_t (&a)[%d], const uint32_t (&b)[%d])\n"
+                 "{\n    uint32_t q[%d];\n%s    q[%d] = %s_INV32_DEV;\n    %s_mul_q_regs(r, a, b, q);\n}\n"
+                 % (tag, N, N, N, nq, fill, nq - 1, tag.upper(), tag))
     else:
         s.append(wrap("%s_mul_regs" % tag, N, gen_mul(N, P, inv, a_op, b_op, r_op), 2,
                       "r = a*b/R mod p  (Montgomery product, fully reduced). %d wide MADs." % (2 * N * N)))
@@ -590,6 +613,8 @@ HEADER = """// GENERATED by tools/gen_field_asm.py — do not edit by hand.
 // See the generator's docstring and DESIGN.md §3.1 for the derivation and bounds.
 #pragma once
 #include <cstdint>
+
+#include "field_consts.cuh"
 
 namespace zecale {
 
@@ -615,6 +640,7 @@ def gen_consts():
         o += carr("%s_R2" % tag, C.limbs32(K["r2"], N))
         o += carr("%s_PM2" % tag, C.limbs32(P - 2, N))
         o += "static constexpr uint32_t %s_INV32 = 0x%08xu;\n" % (tag, K["inv32"])
+        o += "__device__ __constant__ uint32_t %s_INV32_DEV = 0x%08xu;\n" % (tag, K["inv32"])
         o += "static constexpr int %s_BITS = %d;\n" % (tag, P.bit_length())
     # 2-adic root of unity of order 2^46 and its inverse, Montgomery form
     Rm = (1 << C.FR_RBITS) % C.R

@@ -232,7 +232,11 @@ __device__ __forceinline__ uint32_t ntt_swz(uint32_t i, uint32_t logR)
     return x;
 }
 
-__global__ void __launch_bounds__(256, 3) k_ntt_pass(const Fr *in, Fr *out, const Fr *__restrict__ tw, NttPass p)
+// resident CTAs per SM of k_ntt_pass (register cap 65536 / (256 * ZG_NTT_CTAS))
+#ifndef ZG_NTT_CTAS
+#define ZG_NTT_CTAS 3
+#endif
+__global__ void __launch_bounds__(256, ZG_NTT_CTAS) k_ntt_pass(const Fr *in, Fr *out, const Fr *__restrict__ tw, NttPass p)
 {
     const uint32_t R = 1u << p.logR;
     const uint32_t T = p.T;
