@@ -55,6 +55,23 @@ madd_accinf:
     ONE  ZZ
     ONE  ZZZ
     HOOK 0
+; acc = (X, Y) with ZZ = ZZZ = 1 (what madd_accinf leaves: the first point of a chain) += (QX, QY): U2 = QX, S2 = QY,
+; ZZ3 = PP, ZZZ3 = PPP - 6 products and 5 reductions instead of 10 and 9
+madd_aff:
+    SUB  T0, QX, X          ; P
+    SUB  T1, QY, Y          ; R
+    JZ   T0, madd_samex
+    MUL  ZZ, T0, T0         ; PP = ZZ3
+    MUL  ZZZ, T0, ZZ        ; PPP = ZZZ3
+    MUL  T3, X, ZZ          ; Q = X1*PP
+    MUL  T2, T1, T1         ; R^2
+    SUB  T2, T2, ZZZ
+    SUB  T2, T2, T3
+    SUB  X, T2, T3          ; X3 = R^2 - PPP - 2Q
+    SUB  T3, T3, X
+    MULW Y, ZZZ
+    MULFIN Y, T1, T3        ; Y3 = R(Q - X3) - Y1*PPP
+    HOOK 0
 madd_samex:
     JZ   T1, mdbl
     JMP  set_inf
@@ -274,7 +291,7 @@ PROGRAM += ADD_TEMPLATE.format(S="", BX="QX", BY="QY", BZZ="QZZ", BZZZ="QZZZ", *
 # second accumulator R += acc (running-sum bucket reduction)
 PROGRAM += ADD_TEMPLATE.format(S="_r", AX="RX", AY="RY", AZZ="RZZ", AZZZ="RZZZ", BX="X", BY="Y", BZZ="ZZ", BZZZ="ZZZ")
 
-ENTRY_POINTS = ["tfwd", "tfwd_go", "tinv", "tbwd", "tbwd_dbl", "madd", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep", "inv_fermat"]
+ENTRY_POINTS = ["tfwd", "tfwd_go", "tinv", "tbwd", "tbwd_dbl", "madd", "madd_aff", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep", "inv_fermat"]
 
 
 def slot(x):

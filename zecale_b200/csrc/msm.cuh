@@ -580,6 +580,7 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
     ZG_CHECK(t < *n_tasks && end <= p.n_entries);
     FqSlots S;
     vs_acc_inf(S);
+    uint32_t absorbed = 0; // points added so far: the second one meets an affine accumulator (madd_aff: 6 products, not 10)
     auto fetch = [&](uint32_t &pc, FqSlots &S_) -> bool {
         if (e >= end) {
             vs_store_acc(partial + t, S_);
@@ -601,7 +602,8 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
                 return false;
             }
         }
-        pc = VPC_MADD;
+        pc = absorbed == 1 ? VPC_MADD_AFF : VPC_MADD;
+        absorbed++;
         return true;
     };
     uint32_t pc = 0;
