@@ -75,6 +75,30 @@ def test_msm_edge_cases(gpu, ref, group):
     assert np.array_equal(exp2, exp)
 
 
+@pytest.mark.parametrize("group", [1, 2])
+@pytest.mark.parametrize("shape", ["PP", "P-P", "P-PQ", "PPP", "PQ-Q", "infPP"])
+def test_msm_first_pair_special_cases(gpu, ref, group, shape):
+    """The first two points of a bucket chain take the affine-accumulator addition (VM program madd_aff): equal points
+    (-> doubling), opposite points (-> infinity, then the chain goes on), three equal points, a base at infinity in front.
+    Equal scalars put the points into the same bucket of every window (cf. bw6_761_g1.cpp:160-358 special cases)."""
+    pts = ref.bases_mul(ref.fr_rng(606, 2), group)
+    P, Q = pts[0], pts[1]
+    neg = lambda x: ref.group_op(4, x[None, :], None, group)[0]
+    rows = {"PP": [P, P], "P-P": [P, neg(P)], "P-PQ": [P, neg(P), Q], "PPP": [P, P, P], "PQ-Q": [P, Q, neg(Q)],
+            "infPP": [_inf(P[24:36]), P, P]}[shape]
+    bases = np.stack(rows)
+    s = ref.fr_rng(909, 1)
+    scalars = np.repeat(s, len(rows), axis=0)
+    exp, _ = ref.msm(bases, scalars, group)
+    f = gpu.msm_g1 if group == 1 else gpu.msm_g2
+    assert np.array_equal(f(bases, scalars), exp)
+    pin = gpu.pin_bases(bases, group=group)
+    try:
+        assert np.array_equal(gpu.msm_pinned(pin, scalars), exp)
+    finally:
+        pin.release()
+
+
 def test_msm_heavy_buckets(gpu, ref):
     """Aggregator-like scalars: many zeros / ones / small values -> very uneven buckets."""
     n = 5000

@@ -26,6 +26,7 @@
 #include <condition_variable>
 #include <cstdlib>
 #include <cstring>
+#include <future>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -593,11 +594,21 @@ struct evaluations_t {
 };
 
 /// One proof in flight on the fused path (prove_async .. collect).
+/// The part of the proof assembly that does not depend on the device results: four of the six scalar
+/// multiplications of r1cs_gg_ppzksnark.tcc:582-599 (about 1.5 ms each on the host). Computed between enqueue
+/// and collect, i.e. while the device works.
+struct blinding_t {
+    G1 r_delta, s_delta, rs_delta;
+    G2 s_delta2;
+    bool ready = false;
+};
+
 struct ticket_t {
     size_t slot;
     const proving_key_t *pk;
     size_t nnz_b;
     libff::bw6_761_Fr r, s;
+    blinding_t blind;
     unsigned char pt[5][288];
 };
 
@@ -745,13 +756,31 @@ inline void evaluate_sequential(
         pk.L_query.begin(), pk.L_query.end(), padded.begin() + qap_wit.num_inputs() + 1, padded.begin() + nv + 1, 1);
 }
 
-/// Proof assembly: the reference's formulae (r1cs_gg_ppzksnark.tcc:582-599) on its own CPU group arithmetic.
-inline proof_t assemble(const proving_key_t &pk, const evaluations_t &e, const Fr &r, const Fr &s)
+inline void make_blinding(const proving_key_t &pk, const Fr &r, const Fr &s, blinding_t &b)
 {
-    G1 g1_A = pk.alpha_g1 + e.At + r * pk.delta_g1;
-    G1 g1_B = pk.beta_g1 + e.Bt_h + s * pk.delta_g1;
-    G2 g2_B = pk.beta_g2 + e.Bt_g + s * pk.delta_g2;
-    G1 g1_C = e.Ht + e.Lt + s * g1_A + r * g1_B - (r * s) * pk.delta_g1;
+    b.r_delta = r * pk.delta_g1;
+    b.s_delta = s * pk.delta_g1;
+    b.s_delta2 = s * pk.delta_g2;
+    b.rs_delta = (r * s) * pk.delta_g1;
+    b.ready = true;
+}
+
+/// Proof assembly: the reference's formulae (r1cs_gg_ppzksnark.tcc:582-599) on its own CPU group arithmetic. The same
+/// group elements whatever the order of evaluation, so the serialised proof is the reference's. The two scalar
+/// multiplications that need the device results (s * A, r * B) run on two host threads.
+inline proof_t assemble(const proving_key_t &pk, const evaluations_t &e, const Fr &r, const Fr &s, const blinding_t *pre = nullptr)
+{
+    blinding_t local;
+    if (!pre || !pre->ready) {
+        make_blinding(pk, r, s, local);
+        pre = &local;
+    }
+    G1 g1_A = pk.alpha_g1 + e.At + pre->r_delta;
+    G1 g1_B = pk.beta_g1 + e.Bt_h + pre->s_delta;
+    G2 g2_B = pk.beta_g2 + e.Bt_g + pre->s_delta2;
+    std::future<G1> r_b = std::async(std::launch::async, [&]() { return r * g1_B; });
+    const G1 s_a = s * g1_A;
+    G1 g1_C = e.Ht + e.Lt + s_a + r_b.get() - pre->rs_delta;
     return proof_t(std::move(g1_A), std::move(g2_B), std::move(g1_C));
 }
 
@@ -768,11 +797,16 @@ inline proof_t prove_with_rs(
     evaluations_t *evaluations_out = nullptr)
 {
     evaluations_t e;
-    if (!evaluate_fused(pk, primary_input, auxiliary_input, force_pow_2_domain, e)) {
+    blinding_t blind;
+    ticket_t *t = evaluate_fused_async(pk, primary_input, auxiliary_input, force_pow_2_domain);
+    if (t) {
+        make_blinding(pk, r, s, blind); // overlaps the device work
+        collect_evaluations(t, e);
+    } else {
         evaluate_sequential(pk, primary_input, auxiliary_input, force_pow_2_domain, e);
     }
     if (evaluations_out) *evaluations_out = e;
-    return assemble(pk, e, r, s);
+    return assemble(pk, e, r, s, &blind);
 }
 
 /// Pipelined use of the fused prover from one thread: prove_async enqueues a proof on a free slot and
@@ -791,6 +825,7 @@ inline ticket_t *prove_async(
     if (t) {
         t->r = r;
         t->s = s;
+        make_blinding(pk, r, s, t->blind);
     }
     return t;
 }
@@ -799,10 +834,11 @@ inline proof_t collect(ticket_t *t, evaluations_t *evaluations_out = nullptr)
 {
     const proving_key_t &pk = *t->pk;
     const Fr r = t->r, s = t->s;
+    const blinding_t blind = t->blind; // the ticket is freed by collect_evaluations
     evaluations_t e;
     collect_evaluations(t, e);
     if (evaluations_out) *evaluations_out = e;
-    return assemble(pk, e, r, s);
+    return assemble(pk, e, r, s, &blind);
 }
 
 } // namespace zecale_gpu_hooks
