@@ -55,23 +55,50 @@ madd_accinf:
     ONE  ZZ
     ONE  ZZZ
     HOOK 0
-; acc = (X, Y) with ZZ = ZZZ = 1 (what madd_accinf leaves: the first point of a chain) += (QX, QY): U2 = QX, S2 = QY,
-; ZZ3 = PP, ZZZ3 = PPP - 6 products and 5 reductions instead of 10 and 9
+; ---------------------------------------------------------------- k_accumulate's variants of madd: the point slots double as
+; temporaries (QX <- U2, P, PPP; QY <- S2, R), so a chain touches 8 slots + the wide pair instead of 10 + 2 and the per-thread
+; state that has to stay in L2 shrinks by a fifth. The point is gone afterwards: P == Q doubles the accumulator (dbl), which
+; is the same group element as doubling the point.
+madd_acc:
+    JZ   ZZ, madd_accinf
+    MUL  QX, QX, ZZ         ; U2
+    MUL  QY, QY, ZZZ        ; S2
+    SUB  QX, QX, X          ; P = U2 - X1
+    SUB  QY, QY, Y          ; R = S2 - Y1
+    JZ   QX, madd_acc_samex
+    MUL  T2, QX, QX         ; PP
+    MUL  QX, QX, T2         ; PPP
+    MUL  T3, X, T2          ; Q = X1*PP
+    MUL  ZZ, ZZ, T2         ; ZZ3
+    MUL  ZZZ, ZZZ, QX       ; ZZZ3
+    MUL  T2, QY, QY         ; R^2
+    SUB  T2, T2, QX
+    SUB  T2, T2, T3
+    SUB  X, T2, T3          ; X3 = R^2 - PPP - 2Q
+    SUB  T3, T3, X
+    MULW Y, QX
+    MULFIN Y, QY, T3        ; Y3 = R(Q - X3) - Y1*PPP
+    HOOK 0
+; the same with ZZ = ZZZ = 1 (what madd_accinf leaves: the first point of a chain): U2 = QX, S2 = QY, ZZ3 = PP, ZZZ3 = PPP -
+; 6 products and 5 reductions instead of 10 and 9
 madd_aff:
-    SUB  T0, QX, X          ; P
-    SUB  T1, QY, Y          ; R
-    JZ   T0, madd_samex
-    MUL  ZZ, T0, T0         ; PP = ZZ3
-    MUL  ZZZ, T0, ZZ        ; PPP = ZZZ3
+    SUB  QX, QX, X          ; P
+    SUB  QY, QY, Y          ; R
+    JZ   QX, madd_acc_samex
+    MUL  ZZ, QX, QX         ; PP = ZZ3
+    MUL  ZZZ, QX, ZZ        ; PPP = ZZZ3
     MUL  T3, X, ZZ          ; Q = X1*PP
-    MUL  T2, T1, T1         ; R^2
+    MUL  T2, QY, QY         ; R^2
     SUB  T2, T2, ZZZ
     SUB  T2, T2, T3
     SUB  X, T2, T3          ; X3 = R^2 - PPP - 2Q
     SUB  T3, T3, X
     MULW Y, ZZZ
-    MULFIN Y, T1, T3        ; Y3 = R(Q - X3) - Y1*PPP
+    MULFIN Y, QY, T3        ; Y3 = R(Q - X3) - Y1*PPP
     HOOK 0
+madd_acc_samex:
+    JZ   QY, dbl
+    JMP  set_inf
 madd_samex:
     JZ   T1, mdbl
     JMP  set_inf
@@ -291,7 +318,7 @@ PROGRAM += ADD_TEMPLATE.format(S="", BX="QX", BY="QY", BZZ="QZZ", BZZZ="QZZZ", *
 # second accumulator R += acc (running-sum bucket reduction)
 PROGRAM += ADD_TEMPLATE.format(S="_r", AX="RX", AY="RY", AZZ="RZZ", AZZZ="RZZZ", BX="X", BY="Y", BZZ="ZZ", BZZZ="ZZZ")
 
-ENTRY_POINTS = ["tfwd", "tfwd_go", "tinv", "tbwd", "tbwd_dbl", "madd", "madd_aff", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep", "inv_fermat"]
+ENTRY_POINTS = ["tfwd", "tfwd_go", "tinv", "tbwd", "tbwd_dbl", "madd", "madd_acc", "madd_aff", "mdbl", "add", "dbl", "toaff", "fromproj", "movqa", "set_inf", "add_r", "dbl_r", "prodstep", "invprod", "unstep", "inv_fermat"]
 
 
 def slot(x):

@@ -109,6 +109,17 @@ __device__ __forceinline__ void vs_set(SF &S, uint32_t slot, const Fq *src)
     for (int k = 0; k < 6; k++) p[k] = s[k];
 }
 
+// the same for data read once (base points gathered by bucket order): ld.global.cs, evict-first, so that the stream of
+// bases does not push the threads' slot files out of L2
+template <class SF>
+__device__ __forceinline__ void vs_set_stream(SF &S, uint32_t slot, const Fq *src)
+{
+    const uint4 *s = reinterpret_cast<const uint4 *>(src);
+    uint4 *p = S.w + slot * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) p[k] = __ldcs(s + k);
+}
+
 template <class SF>
 __device__ __forceinline__ void vs_get(Fq *dst, const SF &S, uint32_t slot)
 {
@@ -148,14 +159,14 @@ __device__ __forceinline__ bool vs_is_zero(const SF &S, uint32_t slot)
 }
 
 // slot <- -(*src) mod q (0 stays 0); cf. fp.tcc:617-630
-template <class SF>
+template <bool STREAM = false, class SF>
 __device__ __forceinline__ void vs_set_neg(SF &S, uint32_t slot, const Fq *src)
 {
     uint32_t a[24], z[24], r[24];
     const uint4 *s = reinterpret_cast<const uint4 *>(src);
 #pragma unroll
     for (int k = 0; k < 6; k++) {
-        uint4 v = s[k];
+        uint4 v = STREAM ? __ldcs(s + k) : s[k];
         a[4 * k] = v.x;
         a[4 * k + 1] = v.y;
         a[4 * k + 2] = v.z;

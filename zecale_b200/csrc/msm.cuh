@@ -590,11 +590,11 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
             uint32_t ent = entries[e++];
             ZG_CHECK((ent & 0x7fffffffu) < p.n_bases);
             const Affine *pt = bases + (ent & 0x7fffffffu);
-            vs_set(S_, VS_QX, &pt->x);
+            vs_set_stream(S_, VS_QX, &pt->x); // each base copy entry is read once per MSM: keep it out of the way of the slot files
             if (ent >> 31)
-                vs_set_neg(S_, VS_QY, &pt->y);
+                vs_set_neg<true>(S_, VS_QY, &pt->y);
             else
-                vs_set(S_, VS_QY, &pt->y);
+                vs_set_stream(S_, VS_QY, &pt->y);
             // (0,0) encodes infinity in the affine image (only an expanded copy of a 2-torsion point)
             if (!(vs_is_zero(S_, VS_QX) && vs_is_zero(S_, VS_QY))) break;
             if (e >= end) {
@@ -602,7 +602,7 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
                 return false;
             }
         }
-        pc = absorbed == 1 ? VPC_MADD_AFF : VPC_MADD;
+        pc = absorbed == 1 ? VPC_MADD_AFF : VPC_MADD_ACC;
         absorbed++;
         return true;
     };
