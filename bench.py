@@ -486,9 +486,20 @@ def run_b200(args, rank, world, local_rank):
             t0 = time.perf_counter()
             ctx.msm_pinned(pin, h_sc)
             th.append((time.perf_counter() - t0) * 1e3)
-        msm20 = {"device_resident_ms": min(ts[1:]), "host_to_host_pinned_key_ms": min(th), "c": ctx.msm_last_stats()["c"]}
+        import hashlib
+        msm20 = {"device_resident_ms": min(ts[1:]), "host_to_host_pinned_key_ms": min(th), "c": ctx.msm_last_stats()["c"],
+                 "point_digest": hashlib.sha256(ctx.msm_pinned(pin, h_sc).tobytes()).hexdigest()[:16]}
         pin.release()
         del sc, pts
+
+    # ---- the two exchange paths north_star names, one process per GPU over NCCL (N > 1 only): the same 2^20 MSM with its
+    # points sharded over the ranks (288-byte partial sums all-gathered) and a 4-step NTT of 2^22 with one all-to-all
+    nccl = None
+    if world > 1 and not args.skip_msm20:
+        try:
+            nccl = nccl_block(ctx, wl.z, rank, world, local_rank, barrier)
+        except Exception as e:  # noqa: BLE001 - the headline line must still be printed
+            nccl = {"error": repr(e)}
 
     if world > 1:
         tt = torch.tensor([t_res, t_e2e, t_d1], dtype=torch.float64, device="cuda")
@@ -557,6 +568,7 @@ def run_b200(args, rank, world, local_rank):
                                           "NTT is integer-multiply bound (SURVEY.md 8(d)), the HBM fraction is what north_star asks to see",
                              "transforms_ms": iso_ntt_ms, "share_of_step": ntt_s / step_s, "traffic": None},
             "msm_g1_2e20": msm20,
+            "nccl_paths": nccl,
         }
     wl.close()
     del wl
@@ -576,6 +588,77 @@ def run_b200(args, rank, world, local_rank):
             dist.barrier(group=cpu_group)
     if world > 1:
         dist.destroy_process_group()
+    return out
+
+
+def nccl_block(ctx, z, rank, world, local_rank, barrier):
+    """One process per GPU, torch.distributed over NCCL (zecale_b200/dist.py): (1) G1 MSM of 2^20 points sharded by points
+    like libff::multi_exp shards over threads (multiexp.tcc:663-685), partial sums all-gathered and added in rank order -
+    the digest equals msm_g1_2e20.point_digest of the N = 1 line; (2) forward and inverse-coset 4-step NTT of 2^22 elements,
+    layouts A <-> B with ONE all-to-all each (zecale_gpu_ntt_dist_phase), checked by a forward / inverse round trip.
+    Times are CUDA events around the calls, max over ranks, best of three. All ranks must call this."""
+    import hashlib
+    import torch
+    import torch.distributed as dist
+    from zecale_b200 import dist as D
+    dev = torch.device("cuda", local_rank)
+
+    def timed_max(fn, reps=3):
+        best, res = None, None
+        for _ in range(reps):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            res = fn()
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            best = float(t.item()) if best is None else min(best, float(t.item()))
+        return best, res
+
+    out = {"world": world}
+    n = 1 << 20
+    lo, hi = D.msm_chunk_range(n, world, rank)
+    pts = ctx.synth_bases(n, z.G1, seed=77)[lo:hi]
+    pin = ctx.pin_bases(np.ascontiguousarray(pts))
+    del pts
+    sc = torch.from_numpy(random_fr(np.random.default_rng(5), n)[lo:hi].view(np.int64).copy()).to(dev)
+    ms, total = timed_max(lambda: D.msm_sharded(lambda: ctx.msm_pinned_dev(pin, sc.data_ptr(), hi - lo)[0], ctx.point_sum, world,
+                                                device=dev))
+    pin.release()
+    out["msm_g1_2e20_point_sharded"] = {"ms": ms, "points_per_rank": hi - lo, "exchange": "all_gather of one 288-byte point per rank",
+                                        "point_digest": hashlib.sha256(total.tobytes()).hexdigest()[:16]}
+    log_m = 22
+    g = fr_generator()
+    drv = D.DistNtt(D.gpu_phase_fn(ctx), D.nccl_exchange_fn(), world, rank)
+    x = random_fr(np.random.default_rng(log_m), 1 << log_m)[D.layout_a_indices(log_m, world, rank)]
+    keep = torch.from_numpy(x.view(np.int64).copy()).to(dev)
+    buf, scratch = keep.clone(), torch.empty_like(keep)
+    drv.transform(buf, scratch, log_m, 0)                                  # warm-up: twiddle tables
+    res = {"log_m": log_m, "exchange": "all_to_all_single of m/world elements per rank, once per transform"}
+
+    def fwd():
+        buf.copy_(keep)
+        return drv.transform(buf, scratch, log_m, 0)
+
+    # the copy is inside the bracket on purpose only for simplicity of the closure; it is 1/20 of the transform
+    res["fft_ms"], (y, other) = timed_max(fwd)
+    back, _ = drv.transform(y, other, log_m, 1)                            # inverse: layout B -> A, must restore the input
+    ok = torch.tensor([int(torch.equal(back, keep))], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    res["round_trip_ok"] = bool(ok.item())
+    xb = torch.from_numpy(random_fr(np.random.default_rng(log_m + 1), 1 << log_m)[D.layout_b_indices(log_m, world, rank)]
+                          .view(np.int64).copy()).to(dev)
+    bufb = xb.clone()
+
+    def icoset():
+        bufb.copy_(xb)
+        return drv.transform(bufb, scratch, log_m, 3, g)
+
+    drv.transform(bufb, scratch, log_m, 3, g)
+    res["icoset_fft_ms"], _ = timed_max(icoset)
+    out["ntt_4step"] = res
     return out
 
 
