@@ -81,7 +81,9 @@ def main():
     with open(dst, "w") as f:
         f.write("# SASS summary of zecale_b200/libzecale_gpu.so (sm_100a), per kernel\n\n")
         f.write("Source: `cuobjdump -sass` / `cuobjdump -res-usage` on the shipped library; counts are static instructions.\n")
-        f.write("One Fq Montgomery product body = 1152 IMAD.WIDE (+24 IMAD for m = t0*inv); one Fr body = 288 (+12).\n")
+        f.write("One Fq Montgomery product = 432 IMAD.WIDE (Karatsuba product, fq_mulw_regs) + 576 (reduction, fq_redc_regs: 552 IMAD.WIDE + 24 "
+                "IMAD.HI for the first column) + 24 IMAD for m = t0*inv; one Fr body = 288 (+12). The IMAD column counts every "
+                "other IMAD.* form (IMAD, IMAD.HI, IMAD.X, IMAD.MOV, IMAD.IADD): all of them occupy the multiply pipe.\n")
         f.write("No tensor-core or TMA instruction appears in any kernel (the path is carry-chain integer arithmetic).\n\n")
         f.write("| kernel | regs | stack B | total | " + " | ".join(COLS) + " | tensor/TMA |\n")
         f.write("|---|---|---|---|" + "---|" * (len(COLS) + 1) + "\n")
