@@ -283,7 +283,8 @@ unsigned zecale_gpu_msm_window_bits_pinned(size_t n);
 /* ---- unit-test / microbenchmark hooks (not used by the prover) --------------------
  * Element-wise field and group operations on host arrays, executed by the same
  * device functions the MSM/NTT kernels use. op codes:
- *   field: 0 add, 1 sub, 2 mul, 3 sqr, 4 inverse, 5 neg, 6 from-Montgomery
+ *   field: 0 add, 1 sub, 2 mul, 3 sqr, 4 inverse, 5 neg, 6 from-Montgomery, 7 inverse by the Fermat ladder (Fq),
+ *          8 mul by the interleaved CIOS body (Fq; the product path uses the Karatsuba body of op 2)
  *   group: 0 add (xyzz_add), 1 mixed add, 2 double, 3 normalise (to special)
  * Points are 288-byte libff projective points in and (special form) out. */
 int zecale_gpu_test_fq(zecale_gpu_ctx *ctx, int op, const void *a, const void *b, void *out, size_t n);

@@ -28,6 +28,14 @@ def test_field_ops_exact(gpu, field):
     assert limbs_to_ints(f(0, A, B)) == [(x + y) % p for x, y in zip(a, b)]
     assert limbs_to_ints(f(1, A, B)) == [(x - y) % p for x, y in zip(a, b)]
     assert limbs_to_ints(f(2, A, B)) == [x * y * Rinv % p for x, y in zip(a, b)]
+    if field == "fq":  # op 2 = Karatsuba product + separate reduction (the product path), op 8 = the interleaved CIOS body
+        assert np.array_equal(f(8, A, B), f(2, A, B))
+        # operands around the 384-bit split of the Karatsuba level: equal halves, halves that differ by one, all-ones halves
+        h = (1 << 384) - 1
+        s_ = [h, h << 377 & (p - 1), (h << 384 | h) % p, ((h - 1) << 384 | h) % p, (1 << 384) % p, ((1 << 384) + 1) % p, (h << 384) % p]
+        sa = [x for x in s_ for _ in s_]
+        sb = [y for _ in s_ for y in s_]
+        assert limbs_to_ints(f(2, ints_to_limbs(sa, n64), ints_to_limbs(sb, n64))) == [x * y * Rinv % p for x, y in zip(sa, sb)]
     assert limbs_to_ints(f(3, A)) == [x * x * Rinv % p for x in a]
     assert limbs_to_ints(f(5, A)) == [(-x) % p for x in a]
     assert limbs_to_ints(f(6, A)) == [x * Rinv % p for x in a]

@@ -564,6 +564,7 @@ __global__ void __launch_bounds__(64, 1) k_test_fq(int op, const Fq *a, const Fq
     case 1: fq_sub_regs(r, x, y); break;
     case 2: fq_mul_regs(r, x, y); break;
     case 3: fq_sqr_regs(r, x); break;
+    case 8: fq_mul_cios_regs(r, x, y); break; // the interleaved r01 body: cross-check of the Karatsuba product on the device
     case 5: {
 #pragma unroll
         for (int k = 0; k < 24; k++) y[k] = 0;
