@@ -100,3 +100,24 @@ def test_generated_wide_product_difference():
     for w, t in ((0, (P - 1) ** 2), ((P - 1) ** 2, 0), (0, 0)):
         d = do(wsubk, (2 * N, 0), w=(w, 2 * N, 0), p=(t, 2 * N, 2 * N))
         assert do(redc, (N, 0), p=(d, 2 * N, N)) == (w - t) * rinv % P
+
+
+def test_generated_fr_product_with_inv_operand():
+    """The shipped Fr body takes inv = -r^-1 mod 2^32 as an operand (through the constant bank on the device) instead of as
+    an immediate; same values."""
+    N, P, K = C.FR_LIMBS32, C.R, C.FR
+    r_op = lambda k: "%%%d" % k
+    a_op = lambda k: "%%%d" % (N + k)
+    b_op = lambda k: "%%%d" % (2 * N + k)
+    em = G.gen_mul(N, P, K["inv32"], a_op, b_op, r_op, q_op=lambda k: "%%%d" % (3 * N), inv_only=True)
+    assert G.n_wide(em) == 2 * N * N + N
+    rinv = pow(1 << (32 * N), -1, P)
+    xs = _cases(P, 60, 17)
+    for i, a in enumerate(xs):
+        b = xs[(5 * i + 1) % len(xs)]
+        regs = {"%%%d" % (3 * N): K["inv32"]}
+        for k in range(N):
+            regs["%%%d" % (N + k)] = (a >> (32 * k)) & 0xFFFFFFFF
+            regs["%%%d" % (2 * N + k)] = (b >> (32 * k)) & 0xFFFFFFFF
+        ptx_sim.run(em.lines, regs)
+        assert sum(regs["%%%d" % k] << (32 * k) for k in range(N)) == a * b * rinv % P
