@@ -406,8 +406,9 @@ def kara_product(em, A, B, levels):
     return out
 
 
-def gen_redc(em, N, q, inv, Pw, r_op):
-    """r = Pw / R mod p for a 2N-limb Pw < p*R (names), canonical. N*N wide MADs + N MULs."""
+def gen_redc(em, N, q, inv, Pw, r_op, inv_opnd=None):
+    """r = Pw / R mod p for a 2N-limb Pw < p*R (names), canonical. N*N wide MADs + N MULs. inv_opnd: operand that holds
+    inv (default: an immediate)."""
     E = list(Pw[:N])
     O = [None] * N
     x = None
@@ -418,7 +419,7 @@ def gen_redc(em, N, q, inv, Pw, r_op):
             nw = em.fresh()
             em.op("add.cc.u32 %s, %s, %s;" % (nw, E[0], x))       # carry enters the odd chain
             E[0] = nw
-        em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], imm(inv)))
+        em.op("mul.lo.u32 %s, %s, %s;" % (m, E[0], inv_opnd or imm(inv)))
         for j in range(1, N, 2):
             lo, hi = em.fresh(), em.fresh()
             if O[j - 1] is None and i == 0:
@@ -459,11 +460,11 @@ def gen_redc(em, N, q, inv, Pw, r_op):
     gen_final_sub(em, N, q, U, r_op)
 
 
-def gen_mul_kara(N, P, inv, a_op, b_op, r_op, levels):
+def gen_mul_kara(N, P, inv, a_op, b_op, r_op, levels, inv_opnd=None):
     q = C.limbs32(P, N)
     em = Emit()
     Pw = kara_product(em, [a_op(j) for j in range(N)], [b_op(j) for j in range(N)], levels)
-    gen_redc(em, N, q, inv, Pw, r_op)
+    gen_redc(em, N, q, inv, Pw, r_op, inv_opnd)
     return em
 
 
@@ -569,7 +570,14 @@ def gen_field(tag, N, P, inv):
     b_op = lambda k: "%%%d" % (2 * N + k)
     s = []
     lv = KARA_LEVELS.get(tag, 0)
-    if lv:
+    if lv and Q_FROM_REGS.get(tag):
+        # Karatsuba product + separate reduction with inv as an operand (see the Q_FROM_REGS branch below)
+        em = gen_mul_kara(N, P, inv, a_op, b_op, r_op, lv, inv_opnd="%%%d" % (3 * N))
+        s.append(wrap_io("%s_mul_q_regs" % tag, em, [("r", N)], [("a", N), ("b", N), ("q", 1)], [],
+                         "r = a*b/R mod p: Karatsuba product (spec %s) + word-serial reduction, %d wide MADs; q = {inv}." % (lv, n_wide(em) - N)))
+        s.append("__device__ __forceinline__ void %s_mul_regs(uint32_t (&r)[%d], const uint32_t (&a)[%d], const uint32_t (&b)[%d])\n"
+                 "{\n    uint32_t q[1];\n    q[0] = %s_INV32_DEV;\n    %s_mul_q_regs(r, a, b, q);\n}\n" % (tag, N, N, N, tag.upper(), tag))
+    elif lv:
         em = gen_mul_kara(N, P, inv, a_op, b_op, r_op, lv)
         s.append(wrap("%s_mul_regs" % tag, N, em, 2,
                       "r = a*b/R mod p  (Montgomery product, fully reduced): Karatsuba product (spec %s) + word-serial "

@@ -313,8 +313,11 @@ __device__ __forceinline__ void fq_inv_plain(uint32_t (&r)[24], const uint32_t (
 // Run from `pc` until the hook returns false. hook(id, pc, S) may change pc.
 // Slot operands with bit 7 set are relative: slot = (operand & 0x7f) + rel (the hook moves `rel`
 // to walk an array of per-chain slot groups with one program).
+// `wide` (optional): where MULW parks the unreduced 1536-bit product until MULFIN, as 12 uint4 `wide_stride` elements apart
+// - shared memory in k_accumulate (one column per thread); nullptr = the W0/W1 slot pair of the thread's own slot file.
 template <bool REL, bool INV, class SF, class Hook>
-__device__ __forceinline__ void fqvm_run_impl(SF &S, uint32_t pc, Hook &&hook, const uint32_t &rel)
+__device__ __forceinline__ void fqvm_run_impl(SF &S, uint32_t pc, Hook &&hook, const uint32_t &rel, uint4 *wide = nullptr,
+                                              uint32_t wide_stride = 1)
 {
     uint32_t ret = 0, cnt = 0;
     auto rs = [&](uint32_t s) -> uint32_t { return (REL && (s & 0x80u)) ? (s & 0x7fu) + rel : s; };
@@ -335,17 +338,18 @@ __device__ __forceinline__ void fqvm_run_impl(SF &S, uint32_t pc, Hook &&hook, c
                 // MULW c, e stashes the unreduced c*e in the wide slot pair; MULFIN d, a, b reduces a*b - c*e + q^2 ONCE.
                 uint32_t w[48];
                 fq_mulw_regs(w, x, y);
-                uint4 *ws = S.w + VS_W0 * 6;
+                uint4 *ws = wide ? wide : S.w + VS_W0 * 6;
+                const uint32_t wst = wide ? wide_stride : 1u;
                 if (op == VOP_MULW) {
 #pragma unroll
-                    for (int k = 0; k < 12; k++) ws[k] = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+                    for (int k = 0; k < 12; k++) ws[k * wst] = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
                     continue;
                 }
                 if (op == VOP_MULFIN) {
                     uint32_t t[48];
 #pragma unroll
                     for (int k = 0; k < 12; k++) {
-                        const uint4 v = ws[k];
+                        const uint4 v = ws[k * wst];
                         t[4 * k] = v.x;
                         t[4 * k + 1] = v.y;
                         t[4 * k + 2] = v.z;
@@ -422,10 +426,10 @@ __device__ __forceinline__ void fqvm_run(SF &S, uint32_t pc, Hook &&hook)
 }
 // for kernels that only run point additions / doublings (no INVP in their programs)
 template <class SF, class Hook>
-__device__ __forceinline__ void fqvm_run_noinv(SF &S, uint32_t pc, Hook &&hook)
+__device__ __forceinline__ void fqvm_run_noinv(SF &S, uint32_t pc, Hook &&hook, uint4 *wide = nullptr, uint32_t wide_stride = 1)
 {
     const uint32_t rel0 = 0;
-    fqvm_run_impl<false, false>(S, pc, hook, rel0);
+    fqvm_run_impl<false, false>(S, pc, hook, rel0, wide, wide_stride);
 }
 
 // ---------------------------------------------------------------- Fr (register form)

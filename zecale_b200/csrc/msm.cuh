@@ -38,6 +38,11 @@ namespace zecale {
 #ifndef ZG_ACC_CTAS
 #define ZG_ACC_CTAS 3
 #endif
+// k_accumulate parks the unreduced product of MULW / MULFIN in shared memory (24 KB per CTA) instead of the thread's
+// local-memory slot file: same speed, DRAM writes of a launch 1.00 -> 0.40 GB (profiles/r02_traffic.json). 0 = slot file.
+#ifndef ZG_ACC_SHARED_STASH
+#define ZG_ACC_SHARED_STASH 1
+#endif
 
 static constexpr int FR_SCALAR_BITS = 377;
 static constexpr uint32_t MSM_MAX_TASKS_PER_BUCKET = 256;
@@ -572,6 +577,9 @@ __global__ void __launch_bounds__(128, ZG_ACC_CTAS)
 k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint32_t *order, const uint32_t *task_start,
              const uint32_t *task_len, const uint32_t *entries, XYZZ *partial)
 {
+#if ZG_ACC_SHARED_STASH
+    __shared__ uint4 stash[12 * 128]; // the wide product of MULW / MULFIN: column threadIdx.x, conflict-free 16-byte accesses
+#endif
     uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= *n_tasks) return;
     const uint32_t t = order[pos];
@@ -608,7 +616,11 @@ k_accumulate(MsmPlan p, const Affine *bases, const uint32_t *n_tasks, const uint
     };
     uint32_t pc = 0;
     if (!fetch(pc, S)) return;
+#if ZG_ACC_SHARED_STASH
+    fqvm_run_noinv(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); }, stash + threadIdx.x, 128);
+#else
     fqvm_run_noinv(S, pc, [&](uint32_t, uint32_t &pc_, FqSlots &S_) { return fetch(pc_, S_); });
+#endif
 }
 
 // ------------------------------------------------------------------ accumulate: batched affine pair tree
