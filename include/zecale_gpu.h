@@ -138,6 +138,46 @@ int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *handl
 int zecale_gpu_ntt_dev(zecale_gpu_ctx *ctx, void *d_a, unsigned log_m, unsigned flags, const void *coset_g,
                        float *elapsed_ms);
 
+/* ---- NTT for callers that may not allocate device memory ---------------------------
+ * This entry point has no counterpart in the reference (libfqfft works in host memory and knows no
+ * such restriction); it exists for two kinds of host program:
+ *   - one whose own memory pool took (nearly) all of the GPU's memory when it started, so that a
+ *     cudaMalloc made on its behalf by a library fails with "out of memory";
+ *   - one that serves requests under a latency bound and forbids cudaMalloc / cudaFree on that path,
+ *     because both wait for the whole device and stall every other stream of the process.
+ * Neither can create a zecale_gpu_ctx (zecale_gpu_init allocates), so this call takes no context.
+ * It performs the same transform as zecale_gpu_ntt_dev - same flags, same coset_g (HOST pointer to
+ * one 48-byte Fr, needed with COSET), in place on the DEVICE vector d_a[0 .. 2^log_m), identical
+ * result bits - enqueued on the caller's `stream` (a cudaStream_t; NULL = the default stream) and
+ * NOT synchronised: the result is there once the stream has reached this point. The device that is
+ * current when it is called must be the one that owns `stream` and `d_a`.
+ *
+ * Where the working memory comes from: the twiddle table, the scale table and the second vector the
+ * passes alternate with sit in a fixed array inside the library's device image. It is
+ * ZECALE_GPU_NTT_STATIC_BYTES (about 7.5 MiB) on every GPU that loads the library, from load until
+ * the process ends, whether or not this function is ever called. That bounds the size:
+ *   log_m <= ZECALE_GPU_NTT_STATIC_MAX_LOG_M (2^16 elements, the batch-1 aggregator domain);
+ * anything larger is refused with ZECALE_GPU_E_DOMAIN and a message naming the limit. The call
+ * itself runs no cudaMalloc, cudaFree, cudaMallocHost or other allocating routine.
+ *
+ * Sharing rules. There is ONE such array per GPU and every call uses it. A call does not depend on
+ * what the previous call left in it: it recomputes the tables on `stream` before it reads them
+ * (which makes it slower than zecale_gpu_ntt_dev on a warm context), and nothing in it has to be
+ * zero beforehand. But two calls that execute on the same GPU at the same time - issued on two
+ * streams with no event or synchronisation between them, or from two threads - overwrite each
+ * other's tables and both results are garbage. Keep the calls of one GPU in one stream order.
+ *
+ * First call: the first call made on each device looks up where the driver put the array on that
+ * device (and, with lazy module loading, makes the driver load the kernels). Make that first call
+ * during start-up, on a stream that is not being captured.
+ *
+ * Errors: returns ZECALE_GPU_OK or a ZECALE_GPU_E_* code; because there is no context to hold the
+ * text, the message is written to `err` (at most err_cap bytes, NUL-terminated) when err != NULL. */
+#define ZECALE_GPU_NTT_STATIC_MAX_LOG_M 16u
+#define ZECALE_GPU_NTT_STATIC_BYTES ((((size_t)1 << ZECALE_GPU_NTT_STATIC_MAX_LOG_M) * 5 / 2 + 4) * 48)
+int zecale_gpu_ntt_static(void *stream, void *d_a, unsigned log_m, unsigned flags, const void *coset_g, char *err,
+                          size_t err_cap);
+
 /* ---- H polynomial: the device part of libsnark::r1cs_to_qap_witness_map ----------
  * (r1cs_to_qap.tcc:252-330 with d1 = d2 = d3 = 0, as r1cs_gg_ppzksnark_prover calls it,
  * r1cs_gg_ppzksnark.tcc:477-484). Inputs are the evaluations aA[i] = <A_i,w>,

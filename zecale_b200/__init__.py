@@ -10,6 +10,8 @@ from .capi import (  # noqa: F401
     PinnedBases,
     ZecaleGpuError,
     msm_window_bits,
+    ntt_static,
+    NTT_STATIC_MAX_LOG_M,
     NTT_INVERSE,
     NTT_COSET,
     G1,

@@ -51,6 +51,7 @@ EXPORTS = {
     "zecale_gpu_msm_pinned": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _vp]),
     "zecale_gpu_msm_pinned_dev": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _vp, ctypes.POINTER(ctypes.c_float)]),
     "zecale_gpu_ntt_dev": (_i, [_vp, _vp, _u, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
+    "zecale_gpu_ntt_static": (_i, [_vp, _vp, _u, _u, _vp, ctypes.c_char_p, _sz]),
     "zecale_gpu_qap_h": (_i, [_vp, _vp, _vp, _vp, _u, _vp, _vp]),
     "zecale_gpu_qap_h_dev": (_i, [_vp, _vp, _vp, _vp, _u, _vp, ctypes.POINTER(ctypes.c_float)]),
     "zecale_gpu_point_sum": (_i, [_vp, _vp, _sz, _vp]),
@@ -104,6 +105,19 @@ def _ptr(a):
         return ctypes.c_void_p(a)
     assert a.flags["C_CONTIGUOUS"], "array must be C-contiguous"
     return a.ctypes.data_as(ctypes.c_void_p)
+
+
+NTT_STATIC_MAX_LOG_M = 16
+
+
+def ntt_static(d_ptr, log_m, flags=0, coset_g=None, stream=0):
+    """zecale_gpu_ntt_static: the transform of Context.ntt_dev for callers that may not allocate device memory
+    (no context, working memory inside the library image, log_m <= NTT_STATIC_MAX_LOG_M). d_ptr: device address of
+    2^log_m Fr, transformed in place on `stream` (a cudaStream_t value, 0 = default stream); not synchronised."""
+    err = ctypes.create_string_buffer(512)
+    rc = _lib.zecale_gpu_ntt_static(ctypes.c_void_p(stream), ctypes.c_void_p(d_ptr), log_m, flags, _ptr(coset_g), err, len(err))
+    if rc != 0:
+        raise ZecaleGpuError(rc, err.value.decode())
 
 
 class PinnedBases:

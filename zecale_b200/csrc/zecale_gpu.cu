@@ -1997,3 +1997,191 @@ int zecale_gpu_bench_imad(zecale_gpu_ctx *ctx, unsigned blocks, unsigned tpb, un
 }
 
 } // extern "C"
+
+// =====================================================================================================
+// Allocation-free NTT: zecale_gpu_ntt_static. Nothing above this line is used differently because of it.
+//
+// Some programs that want this transform are not allowed to obtain device memory while they run:
+//   * a prover embedded in a service whose own pool reserved (almost) all of the HBM at start-up, so a
+//     cudaMalloc issued by anybody else comes back "out of memory";
+//   * a request path with a latency budget, where cudaMalloc / cudaFree are banned because they
+//     synchronise the whole device and stall every other stream of the process.
+// Such a caller cannot even create a zecale_gpu_ctx (zecale_gpu_init allocates), and the context's NTT
+// needs three pieces of global memory that are neither input nor output: the twiddle table, the coset /
+// 1/m scale table and a second vector the passes ping-pong through. Here those three live in one
+// file-scope device array that is part of the library image: the driver places it when the module is
+// loaded on a device and it stays there until the process exits (ZG_STATIC_BYTES on EVERY device that
+// loads the library, used or not), which is why the largest size is kept modest.
+//
+// The array is shared by every call on a device and is never cleared: a call first rewrites, on the
+// caller's stream, every entry it is going to read (root, seeds, both tables) and only then runs the
+// passes, so what an earlier call left behind is never consumed and nothing has to start at zero.
+// The price is that the tables are recomputed per call. Two calls that are in flight on one device at
+// the same time (different streams without an ordering between them, or two host threads) overwrite
+// each other's tables: results are then undefined. Serialise them.
+// =====================================================================================================
+#define ZG_STATIC_MAX_LOG_M ZECALE_GPU_NTT_STATIC_MAX_LOG_M
+#define ZG_STATIC_M ((size_t)1 << ZG_STATIC_MAX_LOG_M)
+// [ second vector: M Fr | twiddles w^k: M/2 Fr | scale table: M Fr | root, g^(+-1), 1 or 1/m, spare: 4 Fr ]
+#define ZG_STATIC_BYTES ((ZG_STATIC_M * 5 / 2 + 4) * sizeof(Fr))
+static_assert(ZG_STATIC_BYTES == ZECALE_GPU_NTT_STATIC_BYTES, "header and library disagree on the scratch size");
+
+static __device__ __align__(256) unsigned char zg_static_scratch[ZG_STATIC_BYTES];
+
+// table[i] = scale * base^i for i < n, with base and scale read from device memory (scale == nullptr: one),
+// so the seeds computed by a preceding kernel on the same stream never travel through the host.
+__global__ void k_fr_powers_from(const Fr *base, const Fr *scale, Fr *table, size_t n, uint32_t chunk)
+{
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t i0 = t * chunk;
+    if (i0 >= n) return;
+    uint32_t b[12], cur[12], s[12];
+    fr_load(b, base);
+    if (scale)
+        fr_load(s, scale);
+    else
+        fr_set_const(s, FR_ONE);
+    fr_pow_u64(cur, b, (uint64_t)i0);
+    fr_mul_regs(cur, cur, s);
+    for (uint32_t k = 0; k < chunk && i0 + k < n; k++) {
+        fr_store(table + i0 + k, cur);
+        fr_mul_regs(cur, cur, b);
+    }
+}
+
+namespace {
+
+std::mutex zg_static_mu;
+constexpr int ZG_STATIC_MAX_DEVICES = 64;
+// Device address of zg_static_scratch on each device, filled on the first call made with that device current.
+// In host code the name `zg_static_scratch` is only a handle for the runtime, not a pointer a kernel could use:
+// the real address is a per-device fact and comes from cudaGetSymbolAddress.
+unsigned char *zg_static_addr[ZG_STATIC_MAX_DEVICES] = {};
+
+int static_fail(char *err, size_t cap, int code, const char *fmt, ...)
+{
+    if (err && cap) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, cap, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+#define CKS(call)                                                                                              \
+    do {                                                                                                       \
+        cudaError_t e_ = (call);                                                                               \
+        if (e_ != cudaSuccess)                                                                                 \
+            return static_fail(err, err_cap, ZECALE_GPU_E_CUDA, "zecale_gpu_ntt_static: %s:%d %s: %s", __FILE__, \
+                               __LINE__, #call, cudaGetErrorString(e_));                                       \
+    } while (0)
+
+} // namespace
+
+extern "C" int zecale_gpu_ntt_static(void *stream, void *d_a, unsigned log_m, unsigned flags, const void *coset_g, char *err,
+                                     size_t err_cap)
+{
+    if (err && err_cap) err[0] = 0;
+    if (!d_a || (flags & ~3u) || ((flags & ZECALE_GPU_NTT_COSET) && !coset_g))
+        return static_fail(err, err_cap, ZECALE_GPU_E_ARG, "zecale_gpu_ntt_static: bad argument (null vector, unknown flag bits, "
+                                                           "or COSET without coset_g)");
+    if (log_m < 1 || log_m > ZG_STATIC_MAX_LOG_M)
+        return static_fail(err, err_cap, ZECALE_GPU_E_DOMAIN,
+                           "zecale_gpu_ntt_static: log_m = %u is outside [1, %u]; the built-in scratch array holds tables for at most "
+                           "2^%u elements (use zecale_gpu_ntt_dev on a context for larger transforms)",
+                           log_m, ZG_STATIC_MAX_LOG_M, ZG_STATIC_MAX_LOG_M);
+    int dev = -1;
+    CKS(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= ZG_STATIC_MAX_DEVICES)
+        return static_fail(err, err_cap, ZECALE_GPU_E_ARG, "zecale_gpu_ntt_static: device ordinal %d not supported (max %d)", dev,
+                           ZG_STATIC_MAX_DEVICES - 1);
+    unsigned char *base = nullptr;
+    {
+        // set-up, once per device, with that device current
+        std::lock_guard<std::mutex> lk(zg_static_mu);
+        if (!zg_static_addr[dev]) {
+            void *p = nullptr;
+            CKS(cudaGetSymbolAddress(&p, zg_static_scratch));
+            if (!p) return static_fail(err, err_cap, ZECALE_GPU_E_CUDA, "zecale_gpu_ntt_static: cudaGetSymbolAddress returned null");
+            zg_static_addr[dev] = (unsigned char *)p;
+        }
+        base = zg_static_addr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const uint32_t inverse = flags & 1u, coset = (flags >> 1) & 1u;
+    const size_t m = (size_t)1 << log_m;
+    Fr *a = (Fr *)d_a;
+    Fr *tmp = (Fr *)base;
+    Fr *tw = tmp + ZG_STATIC_M;
+    Fr *ctab = tw + ZG_STATIC_M / 2;
+    Fr *seed = ctab + ZG_STATIC_M;
+
+    // 1. seeds and tables, rebuilt by every call (see the header of this section)
+    const uint32_t chunk = 64;
+    k_fr_root<<<1, 1, 0, st>>>(seed, log_m, 0);
+    {
+        size_t half = m >> 1, nthreads = (half + chunk - 1) / chunk;
+        k_fr_powers_from<<<(unsigned)((nthreads + 127) / 128), 128, 0, st>>>(seed, nullptr, tw, half, chunk);
+    }
+    if (coset || inverse) {
+        Fr g; // a plain iFFT still needs the 1/m scaling: the table for g = 1
+        memcpy(g.l, coset ? coset_g : (const void *)FR_ONE_HOST, sizeof(Fr));
+        k_fr_coset_seed<<<1, 1, 0, st>>>(seed + 1, g, log_m, inverse); // seed[1] = g^(+-1), seed[2] = 1 or 1/m
+        size_t nthreads = (m + chunk - 1) / chunk;
+        k_fr_powers_from<<<(unsigned)((nthreads + 127) / 128), 128, 0, st>>>(seed + 1, seed + 2, ctab, m, chunk);
+    }
+    CKS(cudaGetLastError());
+
+    // 2. the passes: the factorisations ntt_launch (ntt.cuh) uses for these sizes, on the static tables
+    const Fr *in_tab = (coset && !inverse) ? ctab : nullptr;
+    const Fr *out_tab = inverse ? ctab : nullptr;
+    NttPass p{};
+    p.log_m = log_m;
+    p.inverse = inverse;
+    p.batch_stride = m;
+    if (log_m <= 11) {
+        p.logR = log_m;
+        p.T = 1;
+        p.n_batch = 1;
+        p.n_inner = 1;
+        p.isr = 1;
+        p.osr = 1;
+        p.sub_tw_stride = 1;
+        p.in_scale_tab = in_tab; p.isc_sr = 1;
+        p.scale_tab = out_tab; p.sc_sr = 1;
+        CKS(ntt_run_pass(a, tmp, tw, p, st));
+        CKS(cudaMemcpyAsync(a, tmp, m * sizeof(Fr), cudaMemcpyDeviceToDevice, st));
+    } else {
+        const uint32_t l1 = (log_m + 1) / 2, l2 = log_m - l1;
+        const uint64_t m1 = 1ull << l1, m2 = 1ull << l2;
+        // columns: vector u = j2 < m2, element r = j1, index r*m2 + u; output times w_m^(u*k)
+        p.logR = l1;
+        p.n_batch = 1;
+        p.n_inner = (uint32_t)m2;
+        p.T = ntt_pick_T(l1, p.n_inner);
+        p.isv = 1; p.isr = m2;
+        p.osv = 1; p.osr = m2;
+        p.in_fast_v = 1;
+        p.tw_post = 1;
+        p.tw_mul = 1;
+        p.sub_tw_stride = m2;
+        p.in_scale_tab = in_tab; p.isc_sv = 1; p.isc_sr = m2;
+        CKS(ntt_run_pass(a, tmp, tw, p, st));
+        // rows: vector beta = k1 < m1, element r = j2: in beta*m2 + r, out beta + k*m1
+        p.in_scale_tab = nullptr;
+        p.logR = l2;
+        p.n_batch = (uint32_t)m1;
+        p.n_inner = 1;
+        p.T = ntt_pick_T(l2, p.n_batch);
+        p.tile_over_batch = 1;
+        p.ibs = m2; p.isv = 0; p.isr = 1;
+        p.obs = 1; p.osv = 0; p.osr = m1;
+        p.in_fast_v = 0;
+        p.tw_post = 0;
+        p.sub_tw_stride = m1;
+        p.scale_tab = out_tab; p.sc_bs = 1; p.sc_sr = m1;
+        CKS(ntt_run_pass(tmp, a, tw, p, st));
+    }
+    return 0;
+}
