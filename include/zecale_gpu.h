@@ -73,7 +73,9 @@ enum { ZECALE_GPU_G1 = 1, ZECALE_GPU_G2 = 2 };
  * concurrently, the 384-byte partial sums travelling to devices[0] by peer copies (NVLink) where they
  * are summed and normalised; coefficients_for_H go the other way, one slice per device. The transforms,
  * the sparse mat-vecs and the un-pinned entry points run on devices[0]. The host API is unchanged, so
- * the hooked reference prover gains the extra devices by listing them ($ZECALE_GPU_DEVICES). */
+ * the hooked reference prover gains the extra devices by listing them ($ZECALE_GPU_DEVICES).
+ * Test switch: with ZECALE_GPU_TEST_REPEAT_DEVICES=1 in the environment one ordinal may be listed several times (the
+ * shards then share that GPU), which lets a one-GPU box run the sharded code; it has no use in production. */
 int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **ctx);
 /* Number of devices the context spans. */
 int zecale_gpu_device_count(zecale_gpu_ctx *ctx);

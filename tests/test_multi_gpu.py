@@ -1,8 +1,12 @@
 """Multi-device contexts (zecale_gpu_init with n_devices > 1): pinned MSMs sharded by points over the
 devices - libff::multi_exp's chunks (multiexp.tcc:663-685) - must give the reference's normalised point,
 through the blocking entry point and through the prover-shaped asynchronous lanes (witness map on
-devices[0], H coefficients sliced out to the other devices). Needs >= 2 GPUs: skipped on a one-GPU box,
-run with `gpurun --gpus 2`."""
+devices[0], H coefficients sliced out to the other devices). With >= 2 GPUs (`gpurun --gpus 2`) the shards sit on
+different devices and the partial sums / H slices travel by peer copies; on a one-GPU box the same device is listed
+three times (ZECALE_GPU_TEST_REPEAT_DEVICES=1), which still runs shard_bounds -> per-shard Pippenger -> gather ->
+sum -> normalise."""
+import os
+
 import numpy as np
 import pytest
 
@@ -21,11 +25,24 @@ def multi():
     import zecale_b200 as z
     n = _device_count()
     if n < 2:
-        pytest.skip("needs at least two GPUs")
-    ctx = z.Context(list(range(min(n, 8))))
-    assert ctx.device_count() == min(n, 8)
+        os.environ["ZECALE_GPU_TEST_REPEAT_DEVICES"] = "1"
+        try:
+            ctx = z.Context([0, 0, 0])
+        finally:
+            del os.environ["ZECALE_GPU_TEST_REPEAT_DEVICES"]
+        assert ctx.device_count() == 3
+    else:
+        ctx = z.Context(list(range(min(n, 8))))
+        assert ctx.device_count() == min(n, 8)
     yield ctx
     ctx.close()
+
+
+def test_repeated_devices_need_the_test_switch():
+    import zecale_b200 as z
+    assert "ZECALE_GPU_TEST_REPEAT_DEVICES" not in os.environ
+    with pytest.raises(z.ZecaleGpuError):
+        z.Context([0, 0])
 
 
 @pytest.mark.parametrize("group", [1, 2])

@@ -1063,13 +1063,16 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
         // travel over NVLink, a gather buffer and a high-priority gather stream on devices[0]
         ok = ctx->devices.size() <= (size_t)zecale_gpu_ctx::MAX_DEVICES;
         for (size_t a = 0; ok && a < ctx->devices.size(); a++) {
-            for (size_t b = 0; b < a; b++) ok = ok && ctx->devices[a] != ctx->devices[b];
+            // test switch: with ZECALE_GPU_TEST_REPEAT_DEVICES=1 the same ordinal may be listed more than once, so that the
+            // sharding, the per-shard Pippenger and the gather can be exercised on a one-GPU box (tests/test_multi_gpu.py)
+            const char *rep = getenv("ZECALE_GPU_TEST_REPEAT_DEVICES");
+            for (size_t b = 0; b < a && !(rep && rep[0] == '1'); b++) ok = ok && ctx->devices[a] != ctx->devices[b];
             ok = ok && ctx->devices[a] >= 0 && ctx->devices[a] < count;
         }
         for (size_t a = 0; ok && a < ctx->devices.size(); a++) {
             cudaSetDevice(ctx->devices[a]);
             for (size_t b = 0; b < ctx->devices.size(); b++) {
-                if (a == b) continue;
+                if (a == b || ctx->devices[a] == ctx->devices[b]) continue;
                 cudaError_t pe = cudaDeviceEnablePeerAccess(ctx->devices[b], 0);
                 if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) {
                     // no direct path: cudaMemcpyPeerAsync still works (staged), keep going
