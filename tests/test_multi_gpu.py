@@ -100,3 +100,49 @@ def test_sharded_prover_lanes(multi, ref):
         for p in (pa, ph, pl, pb2, pb1):
             p.release()
         multi.r1cs_free(r1cs)
+
+
+def test_two_witness_maps_in_one_epoch(multi, gpu, ref):
+    """Two witness maps on two lanes between syncs, each followed by its own H MSM (ZECALE_GPU_SCALARS_FROM_QAP): every
+    sharded H MSM must wait for the witness map of ITS lane (a per-lane event), not for whichever was recorded last.
+    Expected values: coefficients_for_H of each assignment from the single-device context (itself compared with
+    libsnark in test_prove_gpu.py) and libff::multi_exp over the H query with those coefficients."""
+    g = ref.fr_from_ints([C.FR_GENERATOR])[0]
+    assert ref.session_synthetic(3000, 10, 400, 5) == 0
+    ref.session_setup(4)
+    zs = ref.session_export()
+    nv, ni, mm = zs["num_variables"], zs["num_inputs"], zs["m"]
+    w0 = zs["assignment"]
+    w1 = w0.copy()
+    w1[ni + 1:] = ref.fr_rng(909, nv - ni)   # another (unsatisfying) assignment: the map is defined for any vector
+    csr = [zs["csr_a"], zs["csr_b"], zs["csr_c"]]
+    exp_h, exp_p = [], []
+    r1 = gpu.r1cs_load(zs["num_constraints"], ni, nv, csr)
+    try:
+        for w in (w0, w1):
+            h = np.zeros((mm + 1, 6), dtype=np.uint64)
+            gpu.qap_h_from_witness_async(0, r1, w, g, out=h)
+            gpu.sync()
+            exp_h.append(h)
+            exp_p.append(ref.msm(zs["H_query"][:mm - 1], np.ascontiguousarray(h[:mm - 1]), 1)[0])
+    finally:
+        gpu.r1cs_free(r1)
+    assert not np.array_equal(exp_h[0], exp_h[1])
+    r1cs = multi.r1cs_load(zs["num_constraints"], ni, nv, csr)
+    ph = multi.pin_bases(zs["H_query"])
+    try:
+        for _ in range(3):
+            out = [np.zeros(36, dtype=np.uint64) for _ in range(2)]
+            h_out = [np.zeros((mm + 1, 6), dtype=np.uint64) for _ in range(2)]
+            multi.qap_h_from_witness_async(0, r1cs, w0, g, out=h_out[0])
+            multi.qap_h_from_witness_async(1, r1cs, w1, g, out=h_out[1])
+            multi.msm_pinned_async(0, ph, None, out[0], n=mm - 1, from_qap=True)
+            multi.msm_pinned_async(1, ph, None, out[1], n=mm - 1, from_qap=True)
+            multi.flush()
+            multi.sync()
+            for k in range(2):
+                assert np.array_equal(h_out[k], exp_h[k]), k
+                assert np.array_equal(out[k], exp_p[k]), k
+    finally:
+        ph.release()
+        multi.r1cs_free(r1cs)

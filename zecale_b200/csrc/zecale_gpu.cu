@@ -74,6 +74,10 @@ struct Lane {
     MsmPlan tail_plan{};
     MsmBuffers tail_buf{};
     cudaEvent_t ev_acc = nullptr; // bucket accumulation of the pending MSM finished
+    // the last witness map enqueued on THIS lane has written its coefficients_for_H into ws_qap (what a
+    // ZECALE_GPU_SCALARS_FROM_QAP MSM of this lane reads, possibly from another stream or device); the context-wide
+    // ev_qap only says that the most recent witness map of any lane is done and is a scheduling hint
+    cudaEvent_t ev_qap = nullptr;
     // shard of a multi-device MSM: the un-normalised partial sum (XYZZ) is copied to this address on
     // device partial_dev instead of being normalised and sent to the host
     XYZZ *partial_dst = nullptr;
@@ -947,7 +951,7 @@ int multi_msm_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_bases *h, co
         if (from_qap) {
             const uint8_t *src = (const uint8_t *)PL.ws_qap.p + lo * sizeof(Fr);
             stride = sizeof(Fr);
-            CK(cudaStreamWaitEvent(WL.stream, ctx->ev_qap, 0));
+            CK(cudaStreamWaitEvent(WL.stream, PL.ev_qap, 0)); // this lane's witness map, not whichever ran last
             if (w->device == ctx->device) {
                 d_sc = src;
             } else {
@@ -1052,6 +1056,7 @@ int zecale_gpu_init(const int *devices, int n_devices, zecale_gpu_ctx **out)
              cudaEventCreateWithFlags(&L.ev_hand, cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&L.ev_back, cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&L.ev_acc, cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&L.ev_qap, cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreate(&L.ev0) == cudaSuccess && cudaEventCreate(&L.ev1) == cudaSuccess &&
              cudaMallocHost((void **)&L.h, sizeof(Lane::Staging)) == cudaSuccess;
     ctx->cur = &ctx->lanes[0];
@@ -1121,6 +1126,7 @@ void zecale_gpu_shutdown(zecale_gpu_ctx *ctx)
         if (L.ev_hand) cudaEventDestroy(L.ev_hand);
         if (L.ev_back) cudaEventDestroy(L.ev_back);
         if (L.ev_acc) cudaEventDestroy(L.ev_acc);
+        if (L.ev_qap) cudaEventDestroy(L.ev_qap);
         if (L.hi) cudaStreamDestroy(L.hi);
         if (L.stream) cudaStreamDestroy(L.stream);
     }
@@ -1665,6 +1671,7 @@ int zecale_gpu_qap_h_async(zecale_gpu_ctx *ctx, int lane, const void *aA, const 
     trace_mark(ctx, "abc_h2d", ctx->cur->stream);
     rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
     if (rc) return rc;
+    CK(cudaEventRecord(ctx->cur->ev_qap, ctx->cur->stream));
     CK(cudaEventRecord(ctx->ev_qap, ctx->cur->stream));
     ctx->qap_in_epoch = true;
     // coefficients_for_H go back on the lane's stream (copy engine; overlaps the MSMs)
@@ -1792,6 +1799,7 @@ int zecale_gpu_qap_h_from_witness_async(zecale_gpu_ctx *ctx, int lane, const zec
     CK(cudaGetLastError());
     rc = qap_h_device(ctx, d, d + m, d + 2 * m, log_m, (const Fr *)coset_g);
     if (rc) return rc;
+    CK(cudaEventRecord(ctx->cur->ev_qap, ctx->cur->stream));
     CK(cudaEventRecord(ctx->ev_qap, ctx->cur->stream));
     ctx->qap_in_epoch = true;
     if (out_h) CK(cudaMemcpyAsync(out_h, d, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
