@@ -94,6 +94,9 @@ struct TreeMeta {
     uint32_t max_count; // largest bucket (set by k_tree_count)
 };
 
+// Window sizes the bucket reduction (k_tail_*) is written for.
+static constexpr uint32_t MSM_MIN_C = 3, MSM_MAX_C = 20;
+
 inline uint32_t msm_default_c(uint32_t n)
 {
     uint32_t lg = 0;
@@ -1491,6 +1494,10 @@ inline cudaError_t msm_launch_gather_batch(const TailJob *jobs, uint32_t n_jobs,
 inline cudaError_t msm_launch_tail_batch(const TailJob *jobs, uint32_t n_jobs, cudaStream_t st, uint64_t *n_launches = nullptr)
 {
     if (n_jobs == 0 || n_jobs > TAIL_MAX_JOBS) return cudaErrorInvalidValue;
+    // the level ping-pong below needs at least two levels (level 0 lives in `partial`, k_tail_scale reads the last two
+    // of lvl[]): window sizes outside [MSM_MIN_C, MSM_MAX_C] are a caller error, not a plan
+    for (uint32_t i = 0; i < n_jobs; i++)
+        if (jobs[i].cm1 + 1 < MSM_MIN_C || jobs[i].cm1 + 1 > MSM_MAX_C) return cudaErrorInvalidValue;
     TailBatch tb{};
     tb.n_jobs = n_jobs;
     uint32_t max_cm1 = 0;

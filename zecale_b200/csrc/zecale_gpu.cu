@@ -366,7 +366,10 @@ int msm_device(zecale_gpu_ctx *ctx, const Affine *d_bases, const uint8_t *d_inf,
         int rc0 = sync_lanes(ctx);
         if (rc0) return rc0;
     }
-    MsmPlan plan = msm_make_plan((uint32_t)n, c ? c : msm_default_c((uint32_t)n), V, copy_stride);
+    const uint32_t c_eff = c ? c : msm_default_c((uint32_t)n);
+    if (c_eff < MSM_MIN_C || c_eff > MSM_MAX_C)
+        return fail(ctx, ZECALE_GPU_E_ARG, "MSM window size %u outside [%u, %u]", c_eff, MSM_MIN_C, MSM_MAX_C);
+    MsmPlan plan = msm_make_plan((uint32_t)n, c_eff, V, copy_stride);
     MsmBuffers lay = msm_layout(plan, nullptr);
     int rc = reserve(ctx, ctx->cur->ws_msm, lay.total);
     if (rc) return rc;
