@@ -146,3 +146,23 @@ def test_two_witness_maps_in_one_epoch(multi, gpu, ref):
     finally:
         ph.release()
         multi.r1cs_free(r1cs)
+
+
+def test_sharded_handle_is_refused_by_a_single_device_context(multi, gpu, ref):
+    """A sharded image owns no device array of its own; a single-device context must refuse it (not fault)."""
+    import zecale_b200 as z
+    n = 256
+    bases = ref.bases_seq(n, 1)
+    scalars = ref.fr_rng(11, n)
+    pin = multi.pin_bases(bases, 1)
+    try:
+        foreign = z.PinnedBases(gpu, pin.handle, n, 1)
+        with pytest.raises(z.ZecaleGpuError) as e:
+            gpu.msm_pinned(foreign, scalars)
+        assert e.value.code == 1 and "sharded" in str(e.value)
+        with pytest.raises(z.ZecaleGpuError):
+            gpu.msm_pinned_async(0, foreign, scalars, np.zeros(36, dtype=np.uint64))
+        assert np.array_equal(multi.msm_pinned(pin, scalars), ref.msm(bases, scalars, 1)[0])  # still usable by its maker
+    finally:
+        pin.release()
+

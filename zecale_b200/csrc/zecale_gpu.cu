@@ -1340,6 +1340,8 @@ int zecale_gpu_msm_pinned(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, const 
         int rc1 = multi_sync(ctx);
         return rc ? rc : rc1;
     }
+    if (!h->shards.empty()) // a sharded image has no device array of its own (d == nullptr): only its maker can use it
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned: the pinned image is sharded over a multi-device context");
     if (n == 0) return msm_device(ctx, nullptr, nullptr, 0, 0, 0, nullptr, 0, nullptr, 0, out_point, nullptr);
     const uint8_t *d_sc;
     const uint64_t *d_idx;
@@ -1359,6 +1361,8 @@ int zecale_gpu_msm_pinned_dev(zecale_gpu_ctx *ctx, const zecale_gpu_bases *h, co
     if (!h || !out_point || n > h->n || (n && !d_scalars) || scalar_stride < sizeof(Fr))
         return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: bad argument");
     if (is_multi(ctx)) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: device-resident scalars belong to one device; use a single-device context");
+    if (!h->shards.empty())
+        return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_msm_pinned_dev: the pinned image is sharded over a multi-device context");
     CK(cudaSetDevice(ctx->device));
     return msm_device(ctx, h->d, h->is_inf, h->c, h->V, (uint32_t)h->n, (const uint8_t *)d_scalars, scalar_stride,
                       d_scalar_index, n, out_point, elapsed_ms);
@@ -1605,6 +1609,8 @@ int zecale_gpu_msm_pinned_async(zecale_gpu_ctx *ctx, int lane, const zecale_gpu_
         return multi_msm_async(ctx, lane, h, scalars, scalar_stride, (const size_t *)scalar_index, n, out_point,
                                (flags & ZECALE_GPU_SCALARS_FROM_QAP) != 0);
     }
+    if (!h->shards.empty())
+        return fail(ctx, ZECALE_GPU_E_ARG, "msm_pinned_async: the pinned image is sharded over a multi-device context");
     const uint8_t *d_sc = (const uint8_t *)scalars;
     const uint64_t *d_idx = (const uint64_t *)scalar_index;
     if (flags & ZECALE_GPU_SCALARS_FROM_QAP) {

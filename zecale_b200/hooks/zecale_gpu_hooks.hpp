@@ -205,6 +205,10 @@ inline void unpin_all()
 {
     state_t &s = state();
     std::lock_guard<std::mutex> lk(s.mu);
+    // the proof slots prove on their own contexts but read the images pinned on s.ctx: unpin only waits for the
+    // pinning context, so drain every slot first
+    for (auto &sl : s.slots)
+        if (sl.ctx) zecale_gpu_sync(sl.ctx);
     for (auto &kv : s.pins) zecale_gpu_unpin_bases(s.ctx, kv.second.handle);
     s.pins.clear();
     for (auto &kv : s.keys) zecale_gpu_r1cs_free(s.ctx, kv.second.r1cs);
