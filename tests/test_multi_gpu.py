@@ -166,3 +166,18 @@ def test_sharded_handle_is_refused_by_a_single_device_context(multi, gpu, ref):
     finally:
         pin.release()
 
+
+def test_kernel_ms_counts_the_workers(multi, ref):
+    """zecale_gpu_kernel_ms on a multi-device context adds the shard MSMs the workers timed (class 0 = accumulate)."""
+    n = 1 << 12
+    bases = ref.bases_seq(n, 1)
+    scalars = ref.fr_rng(12, n)
+    pin = multi.pin_bases(bases, 1)
+    try:
+        multi.kernel_ms(0, reset=True)
+        multi.msm_pinned(pin, scalars)
+        ms, cnt = multi.kernel_ms(0, reset=True)
+        assert cnt == multi.device_count() and ms > 0.0
+        assert multi.kernel_ms(0)[1] == 0
+    finally:
+        pin.release()

@@ -293,26 +293,37 @@ int sync_lanes(zecale_gpu_ctx *ctx)
 // Fold event pairs into the per-class totals. block = true (zecale_gpu_kernel_ms, shutdown) waits
 // for all lanes first; block = false (called from the enqueue paths when many pairs are pending)
 // only harvests the pairs that have already completed and never synchronises.
+static constexpr size_t MAX_PENDING_TIMERS = 4096;
 void drain_timers(zecale_gpu_ctx *ctx, bool block = true)
 {
     if (block) sync_lanes(ctx);
     for (int k = 0; k < 2; k++) {
         auto &v = ctx->ev_pending[k];
-        size_t keep = 0;
-        for (size_t i = 0; i < v.size(); i++) {
-            if (!block && cudaEventQuery(v[i].second) != cudaSuccess) {
-                v[keep++] = v[i];
-                continue;
-            }
+        // Pairs finish roughly in the order they were recorded: the non-blocking harvest stops at the first pair that
+        // is still running instead of querying the whole backlog (a pipelined prover that never blocks calls this on
+        // every enqueue, so the cost per call has to stay O(harvested), not O(pending)).
+        size_t done = 0;
+        for (; done < v.size(); done++) {
+            if (!block && cudaEventQuery(v[done].second) != cudaSuccess) break;
             float ms = 0.f;
-            if (cudaEventElapsedTime(&ms, v[i].first, v[i].second) == cudaSuccess) {
+            if (cudaEventElapsedTime(&ms, v[done].first, v[done].second) == cudaSuccess) {
                 ctx->kernel_ms[k] += ms;
                 ctx->kernel_n[k]++;
             }
-            ctx->ev_pool.push_back(v[i].first);
-            ctx->ev_pool.push_back(v[i].second);
+            ctx->ev_pool.push_back(v[done].first);
+            ctx->ev_pool.push_back(v[done].second);
         }
-        v.resize(keep);
+        v.erase(v.begin(), v.begin() + done);
+        // A caller that never synchronises and whose oldest pair never completes would grow the backlog without bound:
+        // beyond MAX_PENDING_TIMERS the oldest pairs are given up (their events go back to the pool untimed).
+        if (v.size() > MAX_PENDING_TIMERS) {
+            const size_t drop = v.size() - MAX_PENDING_TIMERS;
+            for (size_t i = 0; i < drop; i++) {
+                ctx->ev_pool.push_back(v[i].first);
+                ctx->ev_pool.push_back(v[i].second);
+            }
+            v.erase(v.begin(), v.begin() + drop);
+        }
     }
 }
 
@@ -1928,13 +1939,31 @@ int zecale_gpu_kernel_ms(zecale_gpu_ctx *ctx, int kernel_class, int reset, doubl
     ctx->cur = &ctx->lanes[0];
     if (kernel_class < 0 || kernel_class > 1) return fail(ctx, ZECALE_GPU_E_ARG, "zecale_gpu_kernel_ms: bad class");
     CK(cudaSetDevice(ctx->device));
+    if (is_multi(ctx)) { // deliver what is in flight the regular way before the workers' lanes are drained below
+        int rc = multi_sync(ctx);
+        if (rc) return rc;
+    }
     drain_timers(ctx);
-    if (total_ms) *total_ms = ctx->kernel_ms[kernel_class];
-    if (count) *count = ctx->kernel_n[kernel_class];
+    double ms = ctx->kernel_ms[kernel_class];
+    uint64_t cnt = ctx->kernel_n[kernel_class];
     if (reset) {
         ctx->kernel_ms[kernel_class] = 0;
         ctx->kernel_n[kernel_class] = 0;
     }
+    // multi-device context: the shard MSMs (and their accumulate kernels) are timed by the workers; report them
+    // too, as zecale_gpu_launch_count does. The sum is device time added over devices, not elapsed time.
+    for (zecale_gpu_ctx *w : ctx->workers) {
+        DevGuard dg(w->device);
+        drain_timers(w);
+        ms += w->kernel_ms[kernel_class];
+        cnt += w->kernel_n[kernel_class];
+        if (reset) {
+            w->kernel_ms[kernel_class] = 0;
+            w->kernel_n[kernel_class] = 0;
+        }
+    }
+    if (total_ms) *total_ms = ms;
+    if (count) *count = cnt;
     return 0;
 }
 
