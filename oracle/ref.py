@@ -14,6 +14,7 @@ REF_SO = os.path.join(_HERE, "_ref", "libzecale_ref.so")
 REF_AGG_SO = os.path.join(_HERE, "_ref", "libzecale_ref_agg.so")
 # ref-agg compiled with -include zecale_gpu_hooks.hpp: the reference prover running on the GPU (drop-in demo)
 REF_HOOKED_SO = os.path.join(_HERE, "_ref", "libzecale_ref_hooked.so")
+REF_HOOKED_FULLTABLE_SO = os.path.join(_HERE, "_ref", "libzecale_ref_hooked_fulltable.so")  # hooked="fulltable"
 # ref-agg with -DDEBUG (the reference's shipped default: is_satisfied + a QAP re-evaluation inside every prove)
 REF_DEBUG_SO = os.path.join(_HERE, "_ref", "libzecale_ref_agg_debug.so")
 
@@ -21,7 +22,8 @@ _vp, _sz, _u64, _d, _i = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint64, ctyp
 
 
 def available(aggregator=False, hooked=False, debug=False):
-    return os.path.exists(REF_DEBUG_SO if debug else REF_HOOKED_SO if hooked else REF_AGG_SO if aggregator else REF_SO)
+    return os.path.exists(REF_DEBUG_SO if debug else REF_HOOKED_FULLTABLE_SO if hooked == "fulltable" else REF_HOOKED_SO if hooked
+                          else REF_AGG_SO if aggregator else REF_SO)
 
 
 def _p(a):
@@ -32,7 +34,8 @@ class Ref:
     """One loaded copy of the reference. Use aggregator=True for the zecale circuit."""
 
     def __init__(self, aggregator=False, hooked=False, debug=False):
-        path = REF_DEBUG_SO if debug else REF_HOOKED_SO if hooked else REF_AGG_SO if aggregator else REF_SO
+        path = (REF_DEBUG_SO if debug else REF_HOOKED_FULLTABLE_SO if hooked == "fulltable" else REF_HOOKED_SO if hooked
+                else REF_AGG_SO if aggregator else REF_SO)
         if not os.path.exists(path):
             raise FileNotFoundError(path + " (run `make -C oracle ref ref-agg` where /root/reference exists)")
         L = ctypes.CDLL(path)

@@ -177,3 +177,23 @@ def test_hooked_reference_prover_aggregator_batch32(pair, capsys, tmp_path):
                                              cpu.threads, exp["timings"]["total"], t_fused))
     finally:
         hooked.hooks_unpin()
+
+
+def test_default_build_keeps_libffs_window_table(pair):
+    """The hooks WITHOUT -DZECALE_GPU_SLIM_WINDOW_TABLE (what `-include` alone gives a maintainer): libff's own
+    get_window_table builds its full table on the CPU and the specialised batch_exp / kc_batch_exp readers take the base
+    point table[0][1] from it. Setup from the same secrets and the proof must equal the CPU build's, as they do for the
+    slim-table build above."""
+    from oracle import ref as R
+    if not R.available(hooked="fulltable"):
+        pytest.skip("oracle/_ref/libzecale_ref_hooked_fulltable.so not present")
+    cpu, _ = pair
+    full = R.Ref(hooked="fulltable")
+    assert full.is_hooked()
+    r, s, exp = _same_session(cpu, full, lambda lib: lib.session_synthetic(3000, 10, 400, 21))
+    _check(full, r, s, exp)
+    assert full.hooks_pin_pk() == 0
+    try:
+        _check_fused(full, r, s, exp)
+    finally:
+        full.hooks_unpin()

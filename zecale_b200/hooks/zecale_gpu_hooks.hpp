@@ -365,6 +365,17 @@ private:
     size_t log_m_;
 };
 
+// The base point of a libff window table: powers_of_g[0][1] = 1 * 2^0 * g (multiexp.tcc:826-842), present in the
+// reference's full table and in the two-entry one of ZECALE_GPU_SLIM_WINDOW_TABLE alike. Any other shape is refused.
+template<typename GroupT>
+inline const GroupT &table_base(const std::vector<std::vector<GroupT>> &table)
+{
+    if (table.empty() || table[0].size() < 2) {
+        throw std::invalid_argument("zecale_gpu_hooks: window table without a base point (table[0][1])");
+    }
+    return table[0][1];
+}
+
 // out[i] = (coeff * v[i]) * g on the device (zecale_gpu_batch_exp), special-form points.
 template<typename GroupT>
 inline std::vector<GroupT> batch_exp(int group, const GroupT &g, const std::vector<Fr> &v, size_t n, const Fr *coeff)
@@ -453,11 +464,20 @@ ZECALE_GPU_MSM_SPECIALISE(multi_exp_filter_one_zero, bw6_761_G2, ZECALE_GPU_G2)
 
 // Fixed-base exponentiations of the trusted setup (r1cs_gg_ppzksnark_generator, r1cs_gg_ppzksnark.tcc:
 // 349-398: A, H, L queries and gamma_ABC): batch_exp (multiexp.tcc:887-916) and batch_exp_with_coeff
-// (:918-947). The device builds its own window table, so the CPU one (get_window_table,
-// multiexp.tcc:809-845: millions of serial point additions per setup) shrinks to {0, g}: every reader
-// of a window_table in the reference - batch_exp, batch_exp_with_coeff, kc_batch_exp and windowed_exp -
-// is specialised here and only needs the base point table[0][1]. Points come back in special form,
-// which the generator's following batch_to_special leaves unchanged.
+// (:918-947). The device builds its own window table; the specialised readers below (batch_exp,
+// batch_exp_with_coeff, kc_batch_exp<G2,G1,Fr>) only take the base point table[0][1] = 1 * 2^0 * g from the
+// CPU table (get_window_table, multiexp.tcc:809-845), which is there whatever the table's shape.
+//
+// ZECALE_GPU_SLIM_WINDOW_TABLE (opt-in, -D on the command line): also specialise get_window_table to the
+// two-entry table {0, g} and windowed_exp to pow * g, which removes the millions of serial point additions
+// the CPU spends on tables the device never reads (batch-8 setup 7.9 s -> 1.2 s). It is NOT the default
+// because these are weak inline symbols: if any translation unit of the final binary instantiates the
+// GENERIC batch_exp / windowed_exp / kc_batch_exp for bw6_761 without this header (e.g. the -include was
+// added to one target only), the linker may pair that generic reader with the two-entry table and it then
+// reads past its end - wrong keys, silently. And a reader this header does not specialise (kc_batch_exp<G1,
+// G1,Fr> of the PGHR13 generator) would fall back to a double-and-add per element. Define it only when
+// every TU that touches libff's multiexp code for bw6_761 is compiled with the -include.
+#ifdef ZECALE_GPU_SLIM_WINDOW_TABLE
 #define ZECALE_GPU_WINDOW_TABLE_SPECIALISE(GROUP)                                                       \
     template<>                                                                                         \
     inline window_table<GROUP> get_window_table<GROUP>(const size_t, const size_t, const GROUP &g)     \
@@ -468,11 +488,12 @@ ZECALE_GPU_MSM_SPECIALISE(multi_exp_filter_one_zero, bw6_761_G2, ZECALE_GPU_G2)
     inline GROUP windowed_exp<GROUP, bw6_761_Fr>(                                                      \
         const size_t, const size_t, const window_table<GROUP> &table, const bw6_761_Fr &pow)           \
     {                                                                                                  \
-        return pow * table[0][1];                                                                      \
+        return pow * zecale_gpu_hooks::table_base(table);                                              \
     }
 ZECALE_GPU_WINDOW_TABLE_SPECIALISE(bw6_761_G1)
 ZECALE_GPU_WINDOW_TABLE_SPECIALISE(bw6_761_G2)
 #undef ZECALE_GPU_WINDOW_TABLE_SPECIALISE
+#endif
 
 #define ZECALE_GPU_BATCH_EXP_SPECIALISE(GROUP, GID)                                                    \
     template<>                                                                                         \
@@ -480,14 +501,14 @@ ZECALE_GPU_WINDOW_TABLE_SPECIALISE(bw6_761_G2)
         const size_t, const size_t, const window_table<GROUP> &table, const std::vector<bw6_761_Fr> &v, \
         size_t num_entries)                                                                            \
     {                                                                                                  \
-        return zecale_gpu_hooks::batch_exp<GROUP>(GID, table[0][1], v, num_entries, nullptr);          \
+        return zecale_gpu_hooks::batch_exp<GROUP>(GID, zecale_gpu_hooks::table_base(table), v, num_entries, nullptr);          \
     }                                                                                                  \
     template<>                                                                                         \
     inline std::vector<GROUP> batch_exp_with_coeff<GROUP, bw6_761_Fr>(                                 \
         const size_t, const size_t, const window_table<GROUP> &table, const bw6_761_Fr &coeff,         \
         const std::vector<bw6_761_Fr> &v)                                                              \
     {                                                                                                  \
-        return zecale_gpu_hooks::batch_exp<GROUP>(GID, table[0][1], v, v.size(), &coeff);              \
+        return zecale_gpu_hooks::batch_exp<GROUP>(GID, zecale_gpu_hooks::table_base(table), v, v.size(), &coeff);              \
     }
 ZECALE_GPU_BATCH_EXP_SPECIALISE(bw6_761_G1, ZECALE_GPU_G1)
 ZECALE_GPU_BATCH_EXP_SPECIALISE(bw6_761_G2, ZECALE_GPU_G2)
@@ -568,9 +589,9 @@ inline knowledge_commitment_vector<libff::bw6_761_G2, libff::bw6_761_G1> kc_batc
         }
     }
     const std::vector<libff::bw6_761_G2> g2 = zecale_gpu_hooks::batch_exp<libff::bw6_761_G2>(
-        ZECALE_GPU_G2, T1_table[0][1], nz, nz.size(), &T1_coeff);
+        ZECALE_GPU_G2, zecale_gpu_hooks::table_base(T1_table), nz, nz.size(), &T1_coeff);
     const std::vector<libff::bw6_761_G1> g1 = zecale_gpu_hooks::batch_exp<libff::bw6_761_G1>(
-        ZECALE_GPU_G1, T2_table[0][1], nz, nz.size(), &T2_coeff);
+        ZECALE_GPU_G1, zecale_gpu_hooks::table_base(T2_table), nz, nz.size(), &T2_coeff);
     res.values.reserve(nz.size());
     for (size_t i = 0; i < nz.size(); ++i) {
         res.values.emplace_back(knowledge_commitment<libff::bw6_761_G2, libff::bw6_761_G1>(g2[i], g1[i]));
