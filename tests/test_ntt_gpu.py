@@ -10,7 +10,8 @@ from oracle.ref import limbs_to_ints, ints_to_limbs
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("log_m", [1, 2, 3, 4, 7, 10, 11, 12, 13, 15, 16, 18])
+# 17 and 19 are the real batch-2/4 and batch-16 aggregator domains; odd sizes take the uneven R1 * R2 split
+@pytest.mark.parametrize("log_m", [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19])
 def test_ntt_all_modes(gpu, ref, log_m):
     m = 1 << log_m
     a = ref.fr_rng(7 * m, m)
